@@ -1,0 +1,241 @@
+#!/usr/bin/env python
+"""Headline benchmark: federation round time + aggregated params/sec (BASELINE.json).
+
+Config #2 of BASELINE.json: CIFAR-10-shaped ResNet-18, one learner per B200, synchronous FedAvg,
+bf16.  One *step* = one full federation round on every GPU:
+
+    local training (``--local-steps`` SGD steps of ``--batch`` synthetic 32x32 images: forward,
+    backward, fused optimizer step; the last step publishes into the peer-visible slot)
+    -> fused cross-GPU weighted aggregation (reduce-scatter + all-gather + fp32 install, one launch)
+
+``value`` is learners x parameters aggregated per second over the whole job (weak scaling: one
+learner per GPU).  Two timings are taken, each over exactly K rounds after W warm-up rounds,
+bracketed by barrier + synchronize, max over ranks:
+
+* device: inputs already resident, CUDA events around the K rounds;
+* e2e:    ``FederationEngine.run_round`` (the public API) with every step's batch copied from
+          pinned host memory and the round's losses read back to the host.
+
+``--impl reference`` would run the unmodified reference; it cannot be installed offline (needs
+Bazel + network, Python <= 3.10), so that arm reports ``unavailable``.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+REF_WHY = ("reference needs Bazel 4.2.1 + network fetches (protobuf/gRPC/PALISADE) and Python<=3.10; "
+           "pip install from /root/reference fails at setup.py (see DESIGN.md)")
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--local-steps", type=int, default=4)
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--model", default="resnet18", choices=["resnet18", "mlp", "gpt2-medium", "gpt2-small"])
+    ap.add_argument("--seq-len", type=int, default=1024)
+    ap.add_argument("--learners-per-gpu", type=int, default=1)
+    ap.add_argument("--no-graph", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f:
+            parts = [c.strip() for c in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1])); mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        if sm:
+            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable": REF_WHY}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "bench.py needs a CUDA device (B200)"}))
+        return 1
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    from metisfl_b200.models import zoo
+    from metisfl_b200.ops import _lib
+    from metisfl_b200.ops.optim import OptimHyper
+    from metisfl_b200.parallel.engine import EngineConfig, FederationEngine
+
+    torch.backends.cudnn.benchmark = True
+    cfg = EngineConfig(learners_per_gpu=args.learners_per_gpu, model_dtype=torch.bfloat16,
+                       optimizer=OptimHyper("MomentumSGD", lr=0.02, momentum=0.9), rule="FedAvg",
+                       scaling="NumTrainingExamples", use_cuda_graph=not args.no_graph)
+    B, S = args.batch, args.local_steps
+    if args.model == "resnet18":
+        factory, loss_fn = zoo.ResNet18, None
+        def make_batch(g):
+            x = torch.randn(B, 3, 32, 32, generator=g).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+            return x.pin_memory(), torch.randint(0, 10, (B,), generator=g).pin_memory()
+    elif args.model == "mlp":
+        factory, loss_fn = zoo.FashionMnistMLP, None
+        def make_batch(g):
+            return (torch.randn(B, 1, 28, 28, generator=g).to(torch.bfloat16).pin_memory(),
+                    torch.randint(0, 10, (B,), generator=g).pin_memory())
+    else:
+        factory = zoo.gpt2_medium if args.model == "gpt2-medium" else zoo.gpt2_small
+        loss_fn = zoo.lm_loss
+        cfg.channels_last = False
+        def make_batch(g):
+            t = torch.randint(0, 50257, (B, args.seq_len), generator=g).pin_memory()
+            return t, t
+    kw = {"loss_fn": loss_fn} if loss_fn is not None else {}
+    eng = FederationEngine(factory, cfg, device=device, **kw)
+    k = cfg.learners_per_gpu
+    g = torch.Generator().manual_seed(1000 + rank)
+    # a small pool of distinct pinned batches per local learner, cycled across rounds
+    pool = [[make_batch(g) for _ in range(S * 2)] for _ in range(k)]
+    def host_batches(r):
+        return [[pool[j][(r * S + s) % len(pool[j])] for s in range(S)] for j in range(k)]
+    dev_pool = [[(x.to(device), y.to(device)) for x, y in pj] for pj in pool]
+    def dev_batches(r):
+        return [[dev_pool[j][(r * S + s) % len(dev_pool[j])] for s in range(S)] for j in range(k)]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_round(r):
+        for j in range(k):
+            eng.train_learner(j, dev_batches(r)[j])
+        eng.aggregate_sync()
+
+    # ---- warm-up (also captures the CUDA graph) -------------------------------------------------
+    for r in range(max(3, args.warmup)):
+        eng.run_round(host_batches(r))
+    for r in range(2):
+        device_round(r)
+    barrier()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    # ---- e2e: public API, H2D every step, loss D2H every round ----------------------------------
+    barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    last = None
+    for r in range(args.steps):
+        last = eng.run_round(host_batches(r))
+    e1.record()
+    barrier()
+    e2e_ms_wall = (time.perf_counter() - t0) * 1e3 / args.steps
+    e2e_ms = e0.elapsed_time(e1) / args.steps
+    e2e_ms = max(e2e_ms, e2e_ms_wall)  # the host read-back is part of the contract
+
+    # ---- device-timed: inputs resident, CUDA events --------------------------------------------
+    barrier()
+    launches0 = _lib.LAUNCHES
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for r in range(args.steps):
+        device_round(r)
+    e1.record()
+    barrier()
+    dev_ms = e0.elapsed_time(e1) / args.steps
+    launches = _lib.LAUNCHES - launches0
+    clocks = sampler.stop() if sampler else None
+
+    t = torch.tensor([dev_ms, e2e_ms], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = t.tolist()
+    n_params = eng.layout.num_params
+    learners = eng.num_learners
+    value = learners * n_params / (dev_ms * 1e-3)
+    e2e_value = learners * n_params / (e2e_ms * 1e-3)
+    x0, y0 = pool[0][0]
+    h2d = k * S * (x0.numel() * x0.element_size() + (y0.numel() * y0.element_size() if y0 is not x0 else 0))
+    d2h = 4 * k
+    peak_mb = torch.cuda.max_memory_allocated(device) / 2**20
+    if rank == 0:
+        print(json.dumps({
+            "metric": "aggregated_params_per_sec (federation round: local training + fused FedAvg)",
+            "value": value, "unit": "params/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": dev_ms, "round_time_s": dev_ms * 1e-3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random CIFAR-shaped batches, random-init weights)",
+            "impl": "ours",
+            "config": {"model": args.model, "params": n_params, "learners": learners,
+                       "learners_per_gpu": k, "protocol": "synchronous", "rule": "FedAvg",
+                       "scaling_factor": "NumTrainingExamples", "local_steps": S, "global_batch": B * learners,
+                       "batch_per_learner": B, "seq_len": args.seq_len if args.model.startswith("gpt2") else None,
+                       "parallelism": f"fed-dp{world}", "optimizer": "MomentumSGD(fused K2)",
+                       "cuda_graph": not args.no_graph,
+                       "l2": f"no flush: per-round working set (peak {peak_mb:.0f} MiB allocated) exceeds the 126 MB L2"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "params/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "api": "FederationEngine.run_round(pinned host batches) -> host losses"},
+            "gpu_launches": launches, "gpu_launches_per_round": launches / args.steps,
+            "last_loss": last["loss"] if last else None,
+        }))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,148 @@
+// K4: tensor quantifier - zeros / non-zeros per model variable in one pass over the flat arena.
+//
+// Behavioural spec: reference QuantifyTensor (controller/common/proto_tensor_serde.h:35-50) counts
+// elements that compare equal to 0 per variable; the controller records the result for every
+// variable of each new community model (controller.cc:952-1004).
+//
+// B200 design: the arena is split into equal contiguous element ranges, one per CTA, independent
+// of variable boundaries, so a 100-element BatchNorm vector and a 50 M-element embedding both keep
+// every SM busy.  A CTA writes the counts of variables that lie entirely inside its range
+// directly; a variable cut by a range boundary yields at most two partial counts per CTA, which go
+// to caller-provided scratch and are folded by a short in-order scan (no float, no atomics, so the
+// result is deterministic).
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace mfl {
+
+constexpr int kQBlocks = 2 * kSMs;  // scratch is sized for this many CTAs
+constexpr int kQThreads = 256;
+
+struct QPartial {          // one per CTA
+  long long var_head;      // variable that began before this CTA's range (or -1)
+  long long var_tail;      // variable that continues past this CTA's range (or -1)
+  unsigned long long nz_head, nz_tail;
+};
+
+template <typename U>
+__device__ __forceinline__ unsigned count_nonzero(const U* p, size_t lo, size_t hi, U mask) {
+  unsigned c = 0;
+  for (size_t i = lo + threadIdx.x; i < hi; i += kQThreads) c += ((p[i] & mask) != 0);
+  return c;
+}
+
+__device__ __forceinline__ unsigned long long block_sum(unsigned c, unsigned long long* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  __syncthreads();  // smem reuse across calls
+  if ((threadIdx.x & 31) == 0) smem[threadIdx.x >> 5] = c;
+  __syncthreads();
+  unsigned long long t = 0;
+  for (int w = 0; w < kQThreads / 32; ++w) t += smem[w];
+  return t;
+}
+
+template <typename U>
+__global__ void __launch_bounds__(kQThreads) quantify_kernel(const U* data, U mask, const uint64_t* offsets,
+                                                             int n_vars, unsigned long long* counts,
+                                                             QPartial* partials) {
+  __shared__ unsigned long long red[kQThreads / 32];
+  const size_t total = offsets[n_vars];
+  const size_t per = (total + gridDim.x - 1) / gridDim.x;
+  const size_t lo = min(total, per * blockIdx.x), hi = min(total, lo + per);
+  QPartial part{-1, -1, 0ull, 0ull};
+  if (lo < hi) {
+    // first variable intersecting [lo, hi): largest v with offsets[v] <= lo
+    int a = 0, b = n_vars;
+    while (b - a > 1) {
+      const int m = (a + b) >> 1;
+      if (offsets[m] <= lo) a = m; else b = m;
+    }
+    for (int v = a; v < n_vars && offsets[v] < hi; ++v) {
+      const size_t vs = offsets[v], ve = offsets[v + 1];
+      if (ve == vs) continue;  // empty variables are reported by the fold kernel
+      const size_t s = max(vs, lo), e = min(ve, hi);
+      const unsigned long long nz = block_sum(count_nonzero(data, s, e, mask), red);
+      if (vs >= lo && ve <= hi) {
+        if (threadIdx.x == 0) { counts[2 * v] = nz; counts[2 * v + 1] = (ve - vs) - nz; }
+      } else if (vs < lo) {
+        part.var_head = v; part.nz_head = nz;
+      } else {
+        part.var_tail = v; part.nz_tail = nz;
+      }
+    }
+  }
+  if (threadIdx.x == 0) partials[blockIdx.x] = part;
+}
+
+// In-order fold of the per-CTA partials: partial pieces of one variable are adjacent in CTA order.
+__global__ void quantify_fold_kernel(const QPartial* partials, int n_blocks, const uint64_t* offsets, int n_vars,
+                                     unsigned long long* counts) {
+  for (int v = threadIdx.x; v < n_vars; v += blockDim.x)
+    if (offsets[v + 1] == offsets[v]) { counts[2 * v] = 0; counts[2 * v + 1] = 0; }
+  if (threadIdx.x != 0) return;
+  long long cur = -1;
+  unsigned long long sum = 0;
+  auto flush = [&]() {
+    if (cur >= 0) {
+      counts[2 * cur] = sum;
+      counts[2 * cur + 1] = (offsets[cur + 1] - offsets[cur]) - sum;
+    }
+  };
+  for (int b = 0; b < n_blocks; ++b) {
+    const QPartial p = partials[b];
+    if (p.var_head >= 0) {
+      if (p.var_head != cur) { flush(); cur = p.var_head; sum = 0; }
+      sum += p.nz_head;
+    }
+    if (p.var_tail >= 0) {
+      if (p.var_tail != cur) { flush(); cur = p.var_tail; sum = 0; }
+      sum += p.nz_tail;
+    }
+  }
+  flush();
+}
+
+// Shared by the allocating and the caller-scratch entry points.
+int quantify_launch(const void* data, int dtype, const uint64_t* offsets, int n_vars,
+                    unsigned long long* counts, void* scratch, cudaStream_t st) {
+  QPartial* parts = reinterpret_cast<QPartial*>(scratch);
+  const int blocks = std::min(kQBlocks, 2 * sm_count());
+  switch (dtype_size(dtype)) {
+    case 1: quantify_kernel<uint8_t><<<blocks, kQThreads, 0, st>>>((const uint8_t*)data, 0xffu, offsets, n_vars, counts, parts); break;
+    case 2: {
+      const uint16_t mask = (dtype == MFL_FLOAT16 || dtype == MFL_BFLOAT16) ? 0x7fffu : 0xffffu;
+      quantify_kernel<uint16_t><<<blocks, kQThreads, 0, st>>>((const uint16_t*)data, mask, offsets, n_vars, counts, parts);
+      break;
+    }
+    case 4: {
+      const uint32_t mask = dtype == MFL_FLOAT32 ? 0x7fffffffu : 0xffffffffu;
+      quantify_kernel<uint32_t><<<blocks, kQThreads, 0, st>>>((const uint32_t*)data, mask, offsets, n_vars, counts, parts);
+      break;
+    }
+    case 8: {
+      const unsigned long long mask = dtype == MFL_FLOAT64 ? 0x7fffffffffffffffull : ~0ull;
+      quantify_kernel<unsigned long long><<<blocks, kQThreads, 0, st>>>((const unsigned long long*)data, mask, offsets, n_vars, counts, parts);
+      break;
+    }
+    default: set_error("quantify: bad dtype %d", dtype); return -1;
+  }
+  if (int rc = check(cudaGetLastError(), "quantify_kernel launch")) return rc;
+  quantify_fold_kernel<<<1, 32, 0, st>>>(parts, blocks, offsets, n_vars, counts);
+  return check(cudaGetLastError(), "quantify_fold_kernel launch");
+}
+
+}  // namespace mfl
+
+using namespace mfl;
+
+extern "C" size_t mfl_quantify_scratch_bytes(int /*n_vars*/) { return sizeof(QPartial) * kQBlocks; }
+
+extern "C" int mfl_quantify(const void* data, int dtype, const uint64_t* offsets, int n_vars,
+                            unsigned long long* counts, void* scratch, void* stream) {
+  MFL_ARG(data && offsets && counts && scratch, "quantify: data, offsets, counts and scratch are required");
+  MFL_ARG(n_vars >= 1, "quantify: n_vars must be >= 1");
+  MFL_ARG((reinterpret_cast<uintptr_t>(scratch) & 15) == 0, "quantify: scratch must be 16-byte aligned");
+  return quantify_launch(data, dtype, offsets, n_vars, counts, scratch, (cudaStream_t)stream);
+}

@@ -1,0 +1,117 @@
+/*
+ * metisfl_b200 — C ABI of the sm_100a kernel library (libmetisfl_b200_kernels.so).
+ *
+ * Every entry point takes raw device pointers and a CUDA stream (as void*; pass
+ * torch.cuda.current_stream().cuda_stream) and only ENQUEUES work: nothing here
+ * synchronises the stream, so the calls can be overlapped and captured by the caller.
+ * Return value: 0 on success, a cudaError_t (>0) or a negative argument-error code
+ * otherwise; mfl_last_error() returns the matching message for the calling thread.
+ *
+ * Tensor element types use the wire-format numbering of metisfl.DType.Type
+ * (reference metisfl/proto/model.proto:16-27, plus FLOAT16/BFLOAT16 extensions).
+ */
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum mfl_dtype {
+  MFL_INT8 = 0, MFL_INT16 = 1, MFL_INT32 = 2, MFL_INT64 = 3,
+  MFL_UINT8 = 4, MFL_UINT16 = 5, MFL_UINT32 = 6, MFL_UINT64 = 7,
+  MFL_FLOAT32 = 8, MFL_FLOAT64 = 9, MFL_FLOAT16 = 10, MFL_BFLOAT16 = 11
+};
+
+#define MFL_MAX_SRC 64      /* sources folded per launch; callers chunk beyond this */
+#define MFL_MAX_PEERS 16    /* GPUs in one NVSwitch domain handled by the fused kernels */
+#define MFL_MAX_SEGMENTS 8  /* dtype-homogeneous segments of one model arena */
+
+const char* mfl_last_error(void);
+int mfl_sm_count(int device);
+
+/* ---- K1: weighted community aggregation (replaces federated_average.cc:15-145) ------------
+ * dst[i] = cast_dst( (accumulate ? acc : 0) + sum_l w[l] * cast_f32(src[l][i]) ) * post_scale
+ * exact != 0 selects the reference's per-term truncation semantics:
+ *   dst_T[i] = sum_l T(double(src_l[i]) * w[l])   accumulated in T  (federated_average.cc:25-35)
+ * acc_f32 (optional) is an fp32 running sum used for streaming aggregation (FedStride-style):
+ *   acc += sum_l w_l x_l ; dst (optional) = cast(acc * post_scale).
+ */
+int mfl_weighted_sum(void* dst, int dst_dtype, const void* const* srcs, const double* weights,
+                     int n_src, int src_dtype, size_t numel, float* acc_f32, int accumulate,
+                     double post_scale, int exact, void* stream);
+
+/* ---- K3: rolling update (federated_rolling_average_base.cc:175-293, FedRec/FedStride) -----
+ * S += w_new * x_new - w_old * x_old (x_old may be NULL); C = cast(S / z).  S is fp32 (or fp64
+ * for FLOAT64 models).  FedAsync mixing: C = (1-a) C + a x is mfl_weighted_sum with 2 sources.
+ */
+int mfl_rolling_update(void* community, int dtype, float* scaled_sum, const void* x_new, double w_new,
+                       const void* x_old, double w_old, double z, size_t numel, void* stream);
+
+/* ---- K1 fused over NVLink: reduce-scatter + all-gather (+ fp32 install) in ONE launch -----
+ * Every rank launches the same call.  Rank r owns shard r of each segment, reads it from every
+ * source slot (peer-mapped pointers), applies weights, and stores the result into EVERY rank's
+ * output buffer; in-kernel flag barriers over the signal pads order the phases.
+ */
+typedef struct {
+  uint64_t offset_bytes;   /* start of the segment inside every slot / output buffer */
+  uint64_t numel;
+  int32_t dtype;           /* element type in the slots and in the outputs */
+  int32_t exact;           /* reference truncation semantics for this segment */
+} mfl_segment;
+
+int mfl_fused_aggregate(const void* const* src_slots, const double* weights, int n_src,
+                        void* const* out_bufs, uint32_t* const* signal_pads, int rank, int world,
+                        const mfl_segment* segments, int n_segments,
+                        float* install_f32, /* optional local fp32 copy of segment 0 */
+                        int n_blocks, void* stream);
+size_t mfl_signal_pad_bytes(int n_blocks);
+
+/* ---- K2: fused optimizer step + publish (keras_model_ops.py:245-283, fed_prox.py:50-60) ---
+ * One launch over the flat parameter arena.  master (fp32) is updated in place; model (working
+ * copy in model_dtype) and, if non-NULL, publish (peer-visible slot) receive the new parameters
+ * scaled by publish_scale (1 for plain FedAvg; n_l for pre-scaled in-switch reduction).
+ */
+typedef struct {
+  int32_t kind;            /* 0 vanilla SGD (+L1/L2), 1 momentum SGD, 2 FedProx, 3 Adam, 4 AdamW */
+  float lr, l1, l2, momentum, mu, beta1, beta2, eps, weight_decay;
+  int32_t step;            /* 1-based Adam step for bias correction */
+  float grad_scale;        /* multiply grads (loss-scale / accumulation) */
+  float publish_scale;
+} mfl_optim_cfg;
+
+int mfl_optimizer_step(float* master, void* model, int model_dtype, const void* grad, int grad_dtype,
+                       float* state1, float* state2, const float* anchor /* FedProx theta* */,
+                       void* publish, int publish_dtype, size_t numel, const mfl_optim_cfg* cfg,
+                       int zero_grad, void* stream);
+
+/* ---- K4: tensor quantifier (proto_tensor_serde.h:35-50) ------------------------------------
+ * counts[2*v] = non-zeros, counts[2*v+1] = zeros of variable v = elements [offsets[v], offsets[v+1]).
+ * offsets is a DEVICE array of n_vars+1 uint64 element offsets; partials is caller scratch of
+ * mfl_quantify_scratch_bytes(n_vars) bytes (per-block partial counts, reduced deterministically).
+ */
+size_t mfl_quantify_scratch_bytes(int n_vars);
+int mfl_quantify(const void* data, int dtype, const uint64_t* offsets, int n_vars,
+                 unsigned long long* counts, void* scratch, void* stream);
+
+/* ---- K12: device pack/unpack between wire bytes and typed arenas ---------------------------
+ * Batched cast/copy: for each tensor t, dst+dst_off[t] <- cast(src+src_off[t]) over numel[t]
+ * elements (tables are DEVICE arrays).  byte_swap != 0 reverses element bytes (BIG_ENDIAN wire).
+ */
+int mfl_pack_cast(void* dst, int dst_dtype, const void* src, int src_dtype,
+                  const uint64_t* dst_off_bytes, const uint64_t* src_off_bytes,
+                  const uint64_t* numel, int n_tensors, int byte_swap, void* stream);
+
+/* ---- Peer-memory fabric (cudaIpc): symmetric arena shared by the GPU processes of one box --- */
+int mfl_fabric_alloc(void** ptr, size_t bytes, void* ipc_handle_out /* 64 bytes */);
+int mfl_fabric_open(void** ptr, const void* ipc_handle /* 64 bytes */);
+int mfl_fabric_close(void* ptr);
+int mfl_fabric_free(void* ptr);
+int mfl_fabric_enable_peers(int device, int world);
+/* cross-GPU barrier as its own launch (K13); same signal pads as the fused kernels */
+int mfl_fabric_barrier(uint32_t* const* signal_pads, int rank, int world, int channel, void* stream);
+
+#ifdef __cplusplus
+}
+#endif

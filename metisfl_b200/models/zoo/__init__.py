@@ -1,0 +1,4 @@
+"""Model zoo used by the examples, tests and benchmarks."""
+from metisfl_b200.models.zoo.gpt2 import GPT2, gpt2_medium, gpt2_small, lm_loss  # noqa: F401
+from metisfl_b200.models.zoo.mlp import FashionMnistMLP, HousingMLP  # noqa: F401
+from metisfl_b200.models.zoo.resnet import ResNet18  # noqa: F401

@@ -1,0 +1,69 @@
+"""GPT-2 decoder (medium = 24 layers, d=1024, 16 heads, vocab 50257, ctx 1024: ~355 M parameters with
+tied embeddings) — north-star config #5.  The reference ships no transformer (largest sequence model:
+a 2-layer BiLSTM, ``examples/keras/models/imdb_lstm.py:21-26``).  Attention uses PyTorch SDPA
+(flash kernels); the linears are the GEMM hot spots targeted by the tcgen05 kernel (K10).
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class Block(nn.Module):
+    def __init__(self, d, heads):
+        super().__init__()
+        self.ln1 = nn.LayerNorm(d)
+        self.qkv = nn.Linear(d, 3 * d)
+        self.proj = nn.Linear(d, d)
+        self.ln2 = nn.LayerNorm(d)
+        self.fc = nn.Linear(d, 4 * d)
+        self.out = nn.Linear(4 * d, d)
+        self.heads = heads
+
+    def forward(self, x):
+        B, T, D = x.shape
+        q, k, v = self.qkv(self.ln1(x)).view(B, T, 3, self.heads, D // self.heads).permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        x = x + self.proj(a.transpose(1, 2).reshape(B, T, D))
+        return x + self.out(F.gelu(self.fc(self.ln2(x)), approximate="tanh"))
+
+
+class GPT2(nn.Module):
+    def __init__(self, vocab=50257, ctx=1024, d=1024, layers=24, heads=16):
+        super().__init__()
+        self.wte = nn.Embedding(vocab, d)
+        self.wpe = nn.Embedding(ctx, d)
+        self.blocks = nn.ModuleList([Block(d, heads) for _ in range(layers)])
+        self.ln_f = nn.LayerNorm(d)
+        self.apply(self._init)
+        for b in self.blocks:  # GPT-2 residual scaling
+            for lin in (b.proj, b.out):
+                nn.init.normal_(lin.weight, std=0.02 / math.sqrt(2 * layers))
+
+    @staticmethod
+    def _init(m):
+        if isinstance(m, (nn.Linear, nn.Embedding)):
+            nn.init.normal_(m.weight, std=0.02)
+            if isinstance(m, nn.Linear) and m.bias is not None:
+                nn.init.zeros_(m.bias)
+
+    def forward(self, idx):
+        B, T = idx.shape
+        x = self.wte(idx) + self.wpe(torch.arange(T, device=idx.device))
+        for b in self.blocks:
+            x = b(x)
+        return F.linear(self.ln_f(x), self.wte.weight)  # tied LM head
+
+
+def gpt2_medium(**kw):
+    return GPT2(d=1024, layers=24, heads=16, **kw)
+
+
+def gpt2_small(**kw):
+    return GPT2(d=768, layers=12, heads=12, **kw)
+
+
+def lm_loss(logits, tokens):
+    """Next-token cross entropy; ``tokens`` are the inputs themselves."""
+    return F.cross_entropy(logits[:, :-1].reshape(-1, logits.size(-1)).float(), tokens[:, 1:].reshape(-1))

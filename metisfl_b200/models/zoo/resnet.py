@@ -1,0 +1,47 @@
+"""ResNet-18 for 32x32 inputs (CIFAR-10 variant: 3x3 stem, no max-pool), 11 173 962 parameters
+plus BatchNorm running statistics.  The reference's closest model is a 1.6 M-parameter Keras CNN
+with BatchNorm (``examples/keras/models/cifar_cnn.py:21-53``); ResNet-18 is the north-star config
+#2 (BASELINE.json).  ``channels_last`` keeps convolutions on the NHWC tensor-core path.
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class BasicBlock(nn.Module):
+    expansion = 1
+
+    def __init__(self, cin, cout, stride):
+        super().__init__()
+        self.conv1 = nn.Conv2d(cin, cout, 3, stride, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(cout)
+        self.conv2 = nn.Conv2d(cout, cout, 3, 1, 1, bias=False)
+        self.bn2 = nn.BatchNorm2d(cout)
+        self.shortcut = None
+        if stride != 1 or cin != cout:
+            self.shortcut = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
+
+    def forward(self, x):
+        out = F.relu(self.bn1(self.conv1(x)), inplace=True)
+        out = self.bn2(self.conv2(out))
+        return F.relu(out + (x if self.shortcut is None else self.shortcut(x)), inplace=True)
+
+
+class ResNet18(nn.Module):
+    def __init__(self, num_classes=10, width=64):
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, width, 3, 1, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(width)
+        cfg = [(width, 1), (width * 2, 2), (width * 4, 2), (width * 8, 2)]
+        blocks, cin = [], width
+        for cout, stride in cfg:
+            blocks += [BasicBlock(cin, cout, stride), BasicBlock(cout, cout, 1)]
+            cin = cout
+        self.layers = nn.Sequential(*blocks)
+        self.fc = nn.Linear(cin, num_classes)
+
+    def forward(self, x):
+        x = F.relu(self.bn1(self.conv1(x)), inplace=True)
+        x = self.layers(x)
+        x = F.adaptive_avg_pool2d(x, 1).flatten(1)
+        return self.fc(x)

@@ -1,0 +1,386 @@
+"""On-box federation engine: the device-resident fast path of a federation round.
+
+Reference round: RunTask fan-out of the whole model over gRPC -> local training ->
+MarkTaskCompleted upload -> CPU weighted average -> EvaluateModel fan-out
+(``controller.cc:428-518,696-759,571-647``; ``learner.py:376-396``).  On one NVSwitch box the same
+round is: every GPU process trains its learner(s) on an arena-backed module, the last optimizer
+step publishes into a peer-visible slot (K2), and ONE fused kernel per GPU (K1) reads all slots over
+NVLink, applies the per-learner scaling factors and writes the new community model - and its fp32
+master copy - into every GPU.  No tensor crosses the host.
+
+Protocols / rules supported here: synchronous FedAvg and FedStride (streaming blocks), semi-synchronous
+task sizing, asynchronous FedRec (recency swap) and FedAsync (staleness-weighted mixing, extension).
+Scaling factors follow ``batches_scaler.cc`` / ``participants_scaler.cc`` /
+``train_dataset_size_scaler.cc`` semantics.
+"""
+from __future__ import annotations
+
+import math
+import time
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from metisfl_b200.models.trainer import LocalTrainer, cross_entropy_loss
+from metisfl_b200.ops import aggregation as agg_ops
+from metisfl_b200.ops.optim import OptimHyper
+from metisfl_b200.parallel.arena import ArenaLayout, ModelArena
+from metisfl_b200.parallel.fabric import Fabric
+
+
+def staleness_factor(kind: str, staleness: float, a: float = 0.5, b: float = 4.0) -> float:
+    """FedAsync staleness functions s(t - tau): constant, polynomial (1+d)^-a, hinge."""
+    d = max(0.0, float(staleness))
+    if kind in ("constant", "CONSTANT", 0):
+        return 1.0
+    if kind in ("polynomial", "POLYNOMIAL", 1):
+        return (1.0 + d) ** (-a)
+    if kind in ("hinge", "HINGE", 2):
+        return 1.0 if d <= b else 1.0 / (a * (d - b) + 1.0)
+    raise ValueError(f"unknown staleness function {kind}")
+
+
+def scaling_factors(kind: str, examples: Sequence[float], batches: Sequence[float], federation_size: int):
+    """Normalised contribution weights of the participating learners (SURVEY §9.2 'Scalers')."""
+    n = len(examples)
+    if federation_size == 1:
+        return [1.0] * n
+    if kind in ("NumParticipants", "NUM_PARTICIPANTS"):
+        return [1.0 / n] * n
+    raw = list(examples) if kind in ("NumTrainingExamples", "NUM_TRAINING_EXAMPLES") else list(batches)
+    if n == 1:
+        return [float(raw[0])]
+    tot = float(sum(raw))
+    return [float(r) / tot for r in raw]
+
+
+@dataclass
+class EngineConfig:
+    learners_per_gpu: int = 1
+    model_dtype: torch.dtype = torch.bfloat16
+    optimizer: OptimHyper = field(default_factory=lambda: OptimHyper("MomentumSGD", lr=0.05, momentum=0.9))
+    rule: str = "FedAvg"                 # FedAvg | FedStride | FedRec | FedAsync
+    scaling: str = "NumTrainingExamples"
+    stride_length: int = 0
+    num_train_examples: int = 6400       # per learner (can be overridden per learner)
+    persist_optimizer_state: bool = False
+    quantify: bool = False
+    fedasync_alpha: float = 0.6
+    staleness_fn: str = "polynomial"
+    staleness_a: float = 0.5
+    staleness_b: float = 4.0
+    channels_last: bool = True
+    use_cuda_graph: Optional[bool] = None
+    fused_blocks: int = 148
+    seed: int = 1234
+
+
+class FederationEngine:
+    """One instance per GPU process (``torch.distributed`` initialised by the launcher, or world 1)."""
+
+    def __init__(self, model_factory: Callable[[], nn.Module], cfg: EngineConfig = None,
+                 loss_fn: Callable = cross_entropy_loss, device=None, group=None,
+                 examples_per_learner: Optional[Sequence[int]] = None):
+        self.cfg = cfg = cfg or EngineConfig()
+        self.fabric = Fabric(device, group)
+        self.device = self.fabric.device
+        self.rank, self.world = self.fabric.rank, self.fabric.world
+        self.k = cfg.learners_per_gpu
+        self.num_learners = self.world * self.k
+        torch.manual_seed(cfg.seed)  # identical initial community model on every rank
+        module = model_factory()
+        if cfg.channels_last and self.device.type == "cuda":
+            module = module.to(memory_format=torch.channels_last)
+        self.layout = ArenaLayout.from_module(module, cfg.model_dtype)
+        nb = self.layout.total_bytes
+        # symmetric buffers: community model + k publish slots per rank
+        self.community = self.fabric.alloc(nb)
+        self.slots = self.fabric.alloc(nb * self.k)
+        self.pads = self.fabric.signal_pads(cfg.fused_blocks)
+        sync_rule = cfg.rule in ("FedAvg", "FedStride")
+        self.direct_install = sync_rule and self.k == 1
+        storage = self.community.local if self.direct_install else None
+        self.arena = ModelArena(module, self.device, cfg.model_dtype, storage=storage)
+        if not self.direct_install:
+            self.community.local[:nb].copy_(self.arena.state[:nb])
+        self.trainer = LocalTrainer(self.arena, cfg.optimizer, loss_fn, cfg.use_cuda_graph)
+        self.slot_views = [self.layout.views(self.slots.local[j * nb:(j + 1) * nb]) for j in range(self.k)]
+        self.community_views = self.layout.views(self.community.local)
+        ex = list(examples_per_learner) if examples_per_learner is not None else \
+            [cfg.num_train_examples] * self.num_learners
+        assert len(ex) == self.num_learners
+        self.examples = ex
+        self.completed_batches = [0] * self.num_learners
+        self.global_iteration = 0
+        self.quantifier = None
+        self.gpu_launches = 0
+        # async state (FedRec / FedAsync)
+        self.learner_version = [0] * self.num_learners       # community iteration a learner started from
+        self.contributed = [False] * self.num_learners
+        self.rec_z = 0.0
+        self.rec_w = [0.0] * self.num_learners
+        self._rec_S = None
+        self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self._pinned_loss = None
+        self.fabric.host_barrier()
+
+    # ------------------------------------------------------------------------------------------
+    def learner_id(self, local_index: int) -> int:
+        return self.rank * self.k + local_index
+
+    def _slot_ptr(self, rank: int, j: int) -> int:
+        return self.slots.ptrs[rank] + j * self.layout.total_bytes
+
+    def _publish_buffers(self, j: int):
+        """Non-trainable segments (BatchNorm statistics ...) are copied into the slot after the task."""
+        for i, s in enumerate(self.layout.segments):
+            if not s.trainable:
+                self.slot_views[j][i].copy_(self.arena.seg[i], non_blocking=True)
+                self.gpu_launches += 1
+
+    def _publish_all(self, j: int):
+        nb = self.layout.total_bytes
+        self.slots.local[j * nb:(j + 1) * nb].copy_(self.arena.state[:nb], non_blocking=True)
+        self.gpu_launches += 1
+
+    # ------------------------------------------------------------------------------------------
+    def train_learner(self, j: int, batches: Sequence, publish_scale: float = 1.0):
+        """Run one learning task for local learner ``j``; returns the device loss of the last step.
+
+        ``batches`` is a sequence of ``(x, y)``; pinned host tensors are copied with a prefetching
+        side stream into the CUDA graph's static inputs.
+        """
+        tr, arena = self.trainer, self.arena
+        nb = self.layout.total_bytes
+        if not self.direct_install:
+            arena.load_state_bytes(self.community.local[:nb])
+            self.gpu_launches += 1 + sum(1 for s, m, v in zip(self.layout.segments, arena.master, arena.seg)
+                                         if s.trainable and m is not v)
+        if not self.cfg.persist_optimizer_state:
+            tr.reset_optimizer_state()
+        if tr.hyper.kind == 2:
+            tr.snapshot_anchor()
+        loss = None
+        n = len(batches)
+        if n == 0:
+            self._publish_all(j)
+            return None
+        on_cuda = self.device.type == "cuda"
+        for s, (x, y) in enumerate(batches):
+            last = s == n - 1
+            if on_cuda and not x.is_cuda:
+                sx, sy = tr.input_buffers(x, y)
+                if sx is not None:
+                    sx.copy_(x, non_blocking=True)
+                    sy.copy_(y, non_blocking=True)
+                    x, y = sx, sy
+                else:
+                    x, y = x.to(self.device, non_blocking=True), y.to(self.device, non_blocking=True)
+                if self.cfg.channels_last and x.dim() == 4 and sx is None:
+                    x = x.contiguous(memory_format=torch.channels_last)
+            loss = tr.forward_backward(x, y)
+            self.gpu_launches += 1
+            self.gpu_launches += tr.apply_optimizer(self.slot_views[j] if last else None, publish_scale)
+        self._publish_buffers(j)
+        self.completed_batches[self.learner_id(j)] += n
+        return loss
+
+    # ------------------------------------------------------------------------------------------
+    def aggregate_sync(self, participants: Optional[Sequence[int]] = None):
+        """FedAvg / FedStride over all (or the given) learners: ONE fused launch per GPU."""
+        cfg = self.cfg
+        ids = list(range(self.num_learners)) if participants is None else list(participants)
+        w = scaling_factors(cfg.scaling, [self.examples[i] for i in ids],
+                            [max(1, self.completed_batches[i]) for i in ids], self.num_learners)
+        stride = cfg.stride_length if (cfg.rule == "FedStride" and cfg.stride_length > 0) else len(ids)
+        stride = min(stride, 64)
+        install = self.arena.master[0] if (self.direct_install and self.arena.master[0] is not self.arena.seg[0]) else None
+        if self.device.type != "cuda" or not self.fabric.peer_mapped:
+            return self._aggregate_host(ids, w)
+        if stride >= len(ids):
+            srcs = [self._slot_ptr(i // self.k, i % self.k) for i in ids]
+            agg_ops.fused_aggregate(srcs, w, self.community.ptrs, self.pads.ptrs, self.rank, self.world,
+                                    self.layout.segment_table(), install_f32=install, n_blocks=cfg.fused_blocks)
+            self.gpu_launches += 1
+        else:
+            # FedStride: memory-bounded blocks; every block is a fused launch whose partial result
+            # is folded into the running community model by giving it weight 1 as an extra source.
+            first = True
+            for b in range(0, len(ids), stride):
+                blk = ids[b:b + stride]
+                srcs = [self._slot_ptr(i // self.k, i % self.k) for i in blk]
+                ws = w[b:b + stride]
+                if not first:
+                    srcs = [self.community.ptrs[self.rank]] + srcs
+                    ws = [1.0] + list(ws)
+                lastb = b + stride >= len(ids)
+                agg_ops.fused_aggregate(srcs, ws, self.community.ptrs, self.pads.ptrs, self.rank, self.world,
+                                        self.layout.segment_table(), install_f32=install if lastb else None,
+                                        n_blocks=cfg.fused_blocks)
+                self.gpu_launches += 1
+                first = False
+        self.global_iteration += 1
+        if not self.direct_install:
+            pass  # learners install the community model at the start of their next task
+        if cfg.quantify:
+            self.quantify_community()
+
+    def _aggregate_host(self, ids, w):
+        """CPU / non-peer-mapped path (gloo): gather slots, run the same math with the CPU ops."""
+        import torch.distributed as dist
+        nb = self.layout.total_bytes
+        if self.world > 1:
+            gathered = [torch.empty_like(self.slots.local) for _ in range(self.world)]
+            dist.all_gather(gathered, self.slots.local, group=self.fabric.group)
+        else:
+            gathered = [self.slots.local]
+        for si, s in enumerate(self.layout.segments):
+            srcs = []
+            for i in ids:
+                r, j = divmod(i, self.k)
+                buf = gathered[r][j * nb:(j + 1) * nb]
+                srcs.append(buf[s.byte_offset:s.byte_offset + s.nbytes].view(s.dtype))
+            out = self.community_views[si]
+            agg_ops.weighted_sum(srcs, w, out=out, exact=s.exact)
+            if self.device.type == "cuda":
+                self.gpu_launches += 1
+        self.global_iteration += 1
+        if self.direct_install:
+            self.arena.sync_master_from_model()
+        if self.cfg.quantify:
+            self.quantify_community()
+
+    # ------------------------------------------------------------------------------------------
+    def fold_async(self, learner: int):
+        """Asynchronous update after learner ``learner`` (global index, hosted on THIS rank when
+        world == 1, else any rank) published: FedRec recency swap or FedAsync mixing (K3)."""
+        cfg = self.cfg
+        r, j = divmod(learner, self.k)
+        nb = self.layout.total_bytes
+        assert self.world == 1 or self.fabric.peer_mapped, "async folding needs peer-mapped slots"
+        staleness = self.global_iteration - self.learner_version[learner]
+        if cfg.rule == "FedAsync":
+            a = cfg.fedasync_alpha * staleness_factor(cfg.staleness_fn, staleness, cfg.staleness_a, cfg.staleness_b)
+            for si, s in enumerate(self.layout.segments):
+                x = self.slot_views[j][si] if r == self.rank else None
+                assert x is not None, "remote async folds are issued by the owning rank"
+                c = self.community_views[si]
+                if s.exact:
+                    c.copy_(x)  # integer bookkeeping variables: take the newest
+                else:
+                    agg_ops.weighted_sum([c, x], [1.0 - a, a], out=c)
+                self.gpu_launches += 1
+        elif cfg.rule == "FedRec":
+            w_new = float(self.examples[learner]) if cfg.scaling != "NumParticipants" else 1.0
+            if self._rec_S is None:
+                self._rec_S = [torch.zeros(s.numel, dtype=torch.float32, device=self.device)
+                               if not s.exact else None for s in self.layout.segments]
+                self._rec_prev = [None] * self.num_learners
+            prev = self._rec_prev[learner]
+            w_old = self.rec_w[learner]
+            self.rec_z += w_new - (w_old if prev is not None else 0.0)
+            for si, s in enumerate(self.layout.segments):
+                x = self.slot_views[j][si]
+                c = self.community_views[si]
+                if s.exact:
+                    c.copy_(x)
+                else:
+                    agg_ops.rolling_update(c, self._rec_S[si], x, w_new,
+                                           prev[si] if prev is not None else None, w_old, self.rec_z)
+                self.gpu_launches += 1
+            # keep this contribution: it is what gets swapped out next time (lineage length 2)
+            self._rec_prev[learner] = [v.clone() for v in self.slot_views[j]]
+            self.rec_w[learner] = w_new
+        else:
+            raise ValueError(f"fold_async: rule {cfg.rule} is synchronous")
+        self.contributed[learner] = True
+        self.global_iteration += 1
+        self.learner_version[learner] = self.global_iteration
+
+    # ------------------------------------------------------------------------------------------
+    def quantify_community(self):
+        if self.quantifier is None:
+            self.quantifier = []
+            for si, s in enumerate(self.layout.segments):
+                vs = [v for v in self.layout.variables if v.segment == si]
+                # offsets incl. padding gaps as pseudo-variables so counts map 1:1 to real variables
+                offs, keep, cur = [], [], 0
+                for v in vs:
+                    if v.elem_offset > cur:
+                        offs.append(cur); keep.append(False)
+                    offs.append(v.elem_offset); keep.append(True)
+                    cur = v.elem_offset + v.numel
+                offs.append(cur)
+                self.quantifier.append((agg_ops.Quantifier(offs, self.device), keep, vs))
+        out = []
+        for si, (q, keep, vs) in enumerate(self.quantifier):
+            counts = q(self.community_views[si])
+            if self.device.type == "cuda":
+                self.gpu_launches += 2
+            out.append((counts, keep, vs))
+        self._last_quant = out
+        return out
+
+    def quantifier_report(self):
+        """Host-side dict name -> (non_zeros, zeros, bytes) of the last quantified community model."""
+        rep = {}
+        for counts, keep, vs in getattr(self, "_last_quant", []):
+            c = counts.cpu().tolist()
+            it = iter(vs)
+            for row, k in zip(c, keep):
+                if k:
+                    v = next(it)
+                    rep[v.name] = (row[0], row[1], v.numel * v.dtype.itemsize)
+        return rep
+
+    # ------------------------------------------------------------------------------------------
+    def run_round(self, batches_per_learner: Sequence[Sequence], evaluate_batch=None) -> Dict:
+        """One synchronous federation round over the learners hosted by this rank.
+
+        ``batches_per_learner[j]`` = list of ``(x, y)`` for local learner j (host-pinned or device).
+        Returns the per-learner last-step losses (host floats) and, if requested, the community
+        model's evaluation on ``evaluate_batch`` - both read back through pinned memory.
+        """
+        assert self.cfg.rule in ("FedAvg", "FedStride"), "run_round drives the synchronous rules"
+        losses = []
+        for j in range(self.k):
+            losses.append(self.train_learner(j, batches_per_learner[j]))
+        self.aggregate_sync()
+        ev = None
+        if evaluate_batch is not None:
+            if not self.direct_install:
+                self.arena.load_state_bytes(self.community.local[:self.layout.total_bytes])
+            x, y = evaluate_batch
+            ev = self.trainer.evaluate(x.to(self.device, non_blocking=True), y.to(self.device, non_blocking=True))
+        return self._read_back(losses, ev)
+
+    def _read_back(self, losses, ev):
+        vals = [l for l in losses if l is not None]
+        if ev is not None:
+            vals += [ev[0]] + ([ev[1].float()] if ev[1] is not None else [])
+        if not vals:
+            return {"loss": [], "eval": None}
+        dev = torch.stack([v.float().reshape(()) for v in vals])
+        if self.device.type == "cuda":
+            if self._pinned_loss is None or self._pinned_loss.numel() != dev.numel():
+                self._pinned_loss = torch.empty(dev.numel(), dtype=torch.float32, pin_memory=True)
+            self._pinned_loss.copy_(dev, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            host = self._pinned_loss.tolist()
+            self.gpu_launches += 2
+        else:
+            host = dev.tolist()
+        nl = len([l for l in losses if l is not None])
+        out = {"loss": host[:nl], "eval": None}
+        if ev is not None:
+            out["eval"] = {"loss": host[nl], "correct": host[nl + 1] if ev[1] is not None else None}
+        return out
+
+    def community_state_dict(self) -> Dict[str, torch.Tensor]:
+        views = self.community_views
+        return {v.name: self.layout.var_view(views, v).clone() for v in self.layout.variables}
+
+    def close(self):
+        self.fabric.close()

@@ -1,0 +1,134 @@
+"""Peer-memory fabric: symmetric device buffers shared by the GPU processes of one NVSwitch box.
+
+Reference counterpart: none — the reference ships every model as protobuf bytes over gRPC
+(``controller.cc:696-759``, ``learner.py:197-206``).  Here every rank allocates the same set of
+buffers, exports them with cudaIpc (``csrc/kernels/runtime.cu``), and maps all peers' copies, so the
+aggregation kernels can ``ld.global`` / ``st.global`` any learner's memory over NVLink.
+
+``torch.distributed`` (NCCL on GPUs, gloo on CPU) is used only for bootstrap: exchanging the
+64-byte IPC handles and small metadata.  With ``world == 1`` or on CPU the same API degrades to
+plain local tensors, which is what the CPU test tier runs.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from metisfl_b200.ops import _lib
+
+
+class _CudaMem:
+    """``__cuda_array_interface__`` shim to view raw device memory as a torch tensor."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+class SymmetricBuffer:
+    """One buffer per rank, all mapped into this process. ``ptrs[r]`` is rank r's base address here."""
+
+    def __init__(self, local: torch.Tensor, ptrs: List[int], owner=None):
+        self.local = local
+        self.ptrs = ptrs
+        self._owner = owner
+
+    @property
+    def nbytes(self) -> int:
+        return self.local.numel()
+
+
+class Fabric:
+    def __init__(self, device=None, group=None):
+        self.group = group
+        self.distributed = dist.is_available() and dist.is_initialized()
+        self.rank = dist.get_rank(group) if self.distributed else 0
+        self.world = dist.get_world_size(group) if self.distributed else 1
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() \
+                else torch.device("cpu")
+        self.device = torch.device(device)
+        self.peer_mapped = self.device.type == "cuda"
+        self._allocs = []
+        self._opened = []
+        if self.peer_mapped and self.world > 1:
+            torch.cuda.set_device(self.device)
+        self._pads: Optional[SymmetricBuffer] = None
+
+    # -- collective helpers (bootstrap only) -------------------------------------------------
+    def all_gather_object(self, obj):
+        if not self.distributed or self.world == 1:
+            return [obj]
+        out = [None] * self.world
+        dist.all_gather_object(out, obj, group=self.group)
+        return out
+
+    def host_barrier(self):
+        if self.distributed and self.world > 1:
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+
+    # -- allocation --------------------------------------------------------------------------
+    def alloc(self, nbytes: int) -> SymmetricBuffer:
+        """Collective: every rank must call with the same size, in the same order."""
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        if not self.peer_mapped:
+            t = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+            return SymmetricBuffer(t, [t.data_ptr()] * 1 if self.world == 1 else [0] * self.world)
+        if self.world == 1:
+            t = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+            return SymmetricBuffer(t, [t.data_ptr()])
+        L = _lib.lib()
+        p = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        with torch.cuda.device(self.device):
+            _lib.check(L.mfl_fabric_alloc(C.byref(p), nbytes, handle), "mfl_fabric_alloc")
+        self._allocs.append(p.value)
+        handles = self.all_gather_object(bytes(handle))
+        ptrs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                ptrs.append(p.value)
+                continue
+            q = C.c_void_p()
+            hb = (C.c_ubyte * 64).from_buffer_copy(h)
+            with torch.cuda.device(self.device):
+                _lib.check(L.mfl_fabric_open(C.byref(q), hb), "mfl_fabric_open")
+            self._opened.append(q.value)
+            ptrs.append(q.value)
+        local = torch.as_tensor(_CudaMem(p.value, nbytes), device=self.device)
+        self.host_barrier()
+        return SymmetricBuffer(local, ptrs, owner=self)
+
+    def signal_pads(self, n_blocks: int = 148) -> SymmetricBuffer:
+        if self._pads is None:
+            nbytes = _lib.lib().mfl_signal_pad_bytes(n_blocks) if self.peer_mapped else 256
+            self._pads = self.alloc(nbytes)
+        return self._pads
+
+    def device_barrier(self, channel: int = 0, stream=None):
+        """Cross-GPU barrier enqueued on the stream (K13); a host barrier on CPU."""
+        if not self.peer_mapped:
+            return self.host_barrier()
+        pads = self.signal_pads()
+        rc = _lib.lib().mfl_fabric_barrier(_lib.voidp_array(pads.ptrs), self.rank, self.world, channel,
+                                           _lib.stream_ptr(stream))
+        _lib.check(rc, "mfl_fabric_barrier")
+
+    def close(self):
+        if not self.peer_mapped or self.world == 1:
+            return
+        torch.cuda.synchronize(self.device)
+        self.host_barrier()
+        L = _lib.lib()
+        for q in self._opened:
+            L.mfl_fabric_close(q)
+        self._opened.clear()
+        self.host_barrier()
+        for p in self._allocs:
+            L.mfl_fabric_free(p)
+        self._allocs.clear()
