@@ -185,7 +185,8 @@ class FederationEngine:
             self.gpu_launches += tr.apply_optimizer(self.slot_views[j] if last else None, publish_scale)
         self._publish_buffers(j)
         self.completed_batches[self.learner_id(j)] += n
-        return loss
+        # the CUDA graph writes its loss into one static tensor: detach this task's value from it
+        return loss.clone() if self.k > 1 else loss
 
     # ------------------------------------------------------------------------------------------
     def aggregate_sync(self, participants: Optional[Sequence[int]] = None):
