@@ -11,6 +11,7 @@
 // to caller-provided scratch and are folded by a short in-order scan (no float, no atomics, so the
 // result is deterministic).
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -144,5 +145,61 @@ extern "C" int mfl_quantify(const void* data, int dtype, const uint64_t* offsets
   MFL_ARG(data && offsets && counts && scratch, "quantify: data, offsets, counts and scratch are required");
   MFL_ARG(n_vars >= 1, "quantify: n_vars must be >= 1");
   MFL_ARG((reinterpret_cast<uintptr_t>(scratch) & 15) == 0, "quantify: scratch must be 16-byte aligned");
+  return quantify_launch(data, dtype, offsets, n_vars, counts, scratch, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Quantifier for callers that cannot allocate device memory.
+//
+// Some hosts of this library have no way to get scratch for mfl_quantify(): a controller plug-in
+// written in plain C that only ever sees the buffers its application hands it; a learner process in
+// which a framework's caching allocator has already claimed the GPU's memory, so that a raw
+// cudaMalloc may fail or fragment that pool; and code on the round's critical path, where the
+// device-wide synchronisation hidden in cudaMalloc/cudaFree would stall the training streams.
+// For them the per-CTA partial records live in the fixed array below, which is part of the loaded
+// module: every GPU that loads this library holds these MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES bytes
+// from load until the process exits, whether or not the entry point is ever called.
+//
+// `g_noalloc_scratch` is a device symbol.  In host code that name is only a handle for the runtime,
+// not a device address, so the host asks the runtime for the real address once per device
+// (cudaGetSymbolAddress, with that device current) and passes the result to the kernels.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES];
+
+namespace mfl {
+constexpr int kMaxDevices = 64;
+static void* g_noalloc_ptr[kMaxDevices] = {};
+static std::mutex g_noalloc_mu;
+
+// Device address of the static scratch array on the current device (resolved on first use).
+static int noalloc_scratch(void** out) {
+  int dev = -1;
+  MFL_CUDA(cudaGetDevice(&dev));
+  MFL_ARG(dev >= 0 && dev < kMaxDevices, "quantify_noalloc: device index %d outside [0,%d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    MFL_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    MFL_ARG(p != nullptr, "quantify_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace mfl
+
+extern "C" int mfl_quantify_noalloc(const void* data, int dtype, const uint64_t* offsets, int n_vars,
+                                    unsigned long long* counts, void* stream) {
+  MFL_ARG(data && offsets && counts, "quantify_noalloc: data, offsets and counts are required");
+  MFL_ARG(n_vars >= 1, "quantify_noalloc: n_vars must be >= 1");
+  const size_t need = mfl_quantify_scratch_bytes(n_vars);
+  MFL_ARG(need <= (size_t)MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES,
+          "quantify_noalloc: this call needs %zu bytes of scratch but the built-in array holds %d; "
+          "use mfl_quantify() with caller-provided scratch instead",
+          need, MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (int rc = noalloc_scratch(&scratch)) return rc;
+  // Nothing in the array has to be cleared first: each CTA overwrites its own record in full before
+  // the fold kernel (same stream, later launch) reads it, so contents left by an earlier call are
+  // never observed.
   return quantify_launch(data, dtype, offsets, n_vars, counts, scratch, (cudaStream_t)stream);
 }

@@ -95,6 +95,29 @@ size_t mfl_quantify_scratch_bytes(int n_vars);
 int mfl_quantify(const void* data, int dtype, const uint64_t* offsets, int n_vars,
                  unsigned long long* counts, void* scratch, void* stream);
 
+/* Quantifier variant that allocates nothing (this entry point has no counterpart in the reference).
+ *
+ * For hosts that cannot obtain device scratch: plain-C controller plug-ins that only hold the buffers
+ * their application gave them, processes whose GPU memory is already owned by a framework's caching
+ * allocator (a raw cudaMalloc there can fail or fragment the pool), and code on the round's critical
+ * path that must avoid the device-wide synchronisation inside cudaMalloc/cudaFree.  Same inputs and
+ * outputs as mfl_quantify() minus the scratch argument; the per-CTA partial records go to a
+ * file-scope `static __device__` array of MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES bytes that every GPU
+ * loading this library holds until the process exits.
+ *
+ *  - Limit: a call whose scratch need (mfl_quantify_scratch_bytes) exceeds that array is refused
+ *    with an error; use mfl_quantify() for it.
+ *  - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with
+ *    that device current) and caches it; make that first call outside of any CUDA stream capture.
+ *    No call allocates or frees device memory, and none calls into an allocating library.
+ *  - All calls on a device share the one array, which keeps whatever the previous call left in it.
+ *    Nothing needs clearing (every record is rewritten before it is read), but two calls whose
+ *    kernels overlap on the GPU - different streams, or different host threads on different
+ *    streams - race on it: issue them on one stream or order them with events. */
+#define MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES 16384
+int mfl_quantify_noalloc(const void* data, int dtype, const uint64_t* offsets, int n_vars,
+                         unsigned long long* counts, void* stream);
+
 /* ---- K12: device pack/unpack between wire bytes and typed arenas ---------------------------
  * Batched cast/copy: for each tensor t, dst+dst_off[t] <- cast(src+src_off[t]) over numel[t]
  * elements (tables are DEVICE arrays).  byte_swap != 0 reverses element bytes (BIG_ENDIAN wire).
