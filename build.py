@@ -73,7 +73,8 @@ def build_kernels(force=False, verbose=False):
 
 def build_core(force=False, verbose=False):
     import pybind11
-    srcs = sorted(glob.glob(os.path.join(ROOT, "csrc", "core", "*.cc")))
+    srcs = sorted(glob.glob(os.path.join(ROOT, "csrc", "core", "*.cc")) +
+                  glob.glob(os.path.join(ROOT, "csrc", "ckks", "*.cc")))
     if not srcs:
         return None
     ext = sysconfig.get_config_var("EXT_SUFFIX")

@@ -1,0 +1,508 @@
+#include "core/controller.h"
+
+#include <sys/resource.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <random>
+#include <stdexcept>
+
+#include "core/numeric.h"
+
+namespace mfl::core {
+
+double NowSeconds() {
+  using namespace std::chrono;
+  return duration_cast<duration<double>>(system_clock::now().time_since_epoch()).count();
+}
+
+long MaxRssKb() {
+  rusage u{};
+  getrusage(RUSAGE_SELF, &u);
+  return u.ru_maxrss;
+}
+
+std::string RandomToken(size_t n) {
+  static const char kHex[] = "0123456789abcdef";
+  std::random_device rd;
+  std::string s(n, '0');
+  for (size_t i = 0; i < n; i += 8) {
+    uint32_t r = rd();
+    for (size_t j = i; j < std::min(n, i + 8); ++j, r >>= 4) s[j] = kHex[r & 15];
+  }
+  return s;
+}
+
+static double ElapsedMs(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+static void Log(const char* fmt, const std::string& a = "", const std::string& b = "") {
+  std::fprintf(stderr, "[metisfl_b200.controller] ");
+  std::fprintf(stderr, fmt, a.c_str(), b.c_str());
+  std::fprintf(stderr, "\n");
+}
+
+// ---------------------------------------------------------------------------------------------
+Controller::Controller(ControllerParams params, std::shared_ptr<Dispatcher> dispatcher)
+    : params_(std::move(params)), dispatcher_(std::move(dispatcher)), pool_(2) {
+  if (params_.batch_size == 0) throw std::invalid_argument("batch_size must be > 0");
+  if (params_.epochs == 0) throw std::invalid_argument("epochs must be > 0");
+  const std::string& r = params_.rule;
+  if (r == "FedAvg") aggregator_ = std::make_unique<FedAvg>();
+  else if (r == "FedStride") aggregator_ = std::make_unique<FedStride>();
+  else if (r == "FedRec") aggregator_ = std::make_unique<FedRec>();
+  else if (r == "FedAsync")
+    aggregator_ = std::make_unique<FedAsync>(params_.fedasync_alpha, params_.staleness_fn, params_.staleness_a,
+                                             params_.staleness_b);
+  else if (r == "PWA")
+    aggregator_ = std::make_unique<PWA>(params_.he_crypto_context_file, params_.he_batch_size, params_.he_scaling_bits);
+  else throw std::invalid_argument("unknown aggregation rule: " + r);
+  if (params_.protocol == Protocol::kAsynchronous) scheduler_ = std::make_unique<AsynchronousScheduler>();
+  else if (params_.protocol == Protocol::kSynchronous || params_.protocol == Protocol::kSemiSynchronous)
+    scheduler_ = std::make_unique<SynchronousScheduler>();
+  else throw std::invalid_argument("unknown communication protocol");
+  if (params_.redis) store_ = std::make_unique<RedisModelStore>(params_.redis_host, params_.redis_port, params_.eviction);
+  else store_ = std::make_unique<HashMapModelStore>(params_.eviction);
+  if (params_.task_deadline_secs > 0) watchdog_ = std::thread([this] { WatchdogLoop(); });
+}
+
+Controller::~Controller() { Shutdown(); }
+
+void Controller::Shutdown() {
+  if (stop_.exchange(true)) return;
+  wd_cv_.notify_all();
+  if (watchdog_.joinable()) watchdog_.join();
+  pool_.Stop();
+  store_->Shutdown();
+}
+
+void Controller::WaitIdle() { pool_.WaitIdle(); }
+
+std::vector<std::string> Controller::ActiveIdsLocked() const {
+  std::vector<std::string> ids;
+  for (auto& kv : learners_) ids.push_back(kv.first);
+  return ids;
+}
+
+// ---------------------------------------------------------------------------------------------
+StatusOr Controller::ReplaceCommunityModel(std::string bytes) {
+  uint32_t contributors, iteration;
+  std::string_view model;
+  if (!wire::ParseFederatedModel(bytes, contributors, iteration, model))
+    return {Status::kInvalidArgument, "malformed FederatedModel"};
+  std::vector<wire::VariableView> vars;
+  if (!wire::ParseModel(model, vars)) return {Status::kInvalidArgument, "malformed Model"};
+  std::vector<std::string> pending;
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    community_model_ = std::make_shared<std::string>(model);
+    community_ = std::make_shared<std::string>(std::move(bytes));
+    if (auto* fa = dynamic_cast<FedAsync*>(aggregator_.get())) fa->SetCommunity(community_model_);
+    community_lineage_.push_back(community_);
+    while (community_lineage_.size() > std::max<uint32_t>(1, params_.community_lineage_length)) community_lineage_.pop_front();
+    pending.swap(pending_initial_);
+  }
+  Log("community model replaced (%s variables)", std::to_string(vars.size()));
+  for (auto& id : pending) pool_.Push([this, id] { ScheduleInitialTask(id); });
+  return {};
+}
+
+StatusOr Controller::AddLearner(const std::string& hostname, int port, std::string server_entity, std::string dataset_spec,
+                                uint32_t n_train, uint32_t n_valid, uint32_t n_test, std::string public_cert,
+                                std::string* learner_id, std::string* auth_token) {
+  if (hostname.empty() || port <= 0) return {Status::kInvalidArgument, "Must provide a valid hostname and port."};
+  if (n_train == 0) return {Status::kInvalidArgument, "Learner training examples <= 0."};
+  const std::string id = hostname + ":" + std::to_string(port);
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    if (learners_.count(id)) return {Status::kAlreadyExists, "Learner has already joined."};
+    LearnerRecord rec;
+    rec.endpoint = {id, hostname, port, std::move(public_cert)};
+    rec.auth_token = RandomToken(64);
+    rec.server_entity = std::move(server_entity);
+    rec.dataset_spec = std::move(dataset_spec);
+    rec.n_train = n_train; rec.n_valid = n_valid; rec.n_test = n_test;
+    rec.num_local_updates = params_.epochs * (uint32_t)std::ceil((double)n_train / (double)params_.batch_size);
+    *learner_id = id;
+    *auth_token = rec.auth_token;
+    learners_.emplace(id, std::move(rec));
+  }
+  Log("learner %s joined the federation", id);
+  pool_.Push([this, id] { ScheduleInitialTask(id); });
+  return {};
+}
+
+StatusOr Controller::RemoveLearner(const std::string& id, const std::string& token) {
+  std::vector<std::string> resume;
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    auto it = learners_.find(id);
+    if (it == learners_.end()) return {Status::kNotFound, "No such learner."};
+    if (it->second.auth_token != token) return {Status::kUnauthenticated, "Incorrect credentials."};
+    EvictLocked(id, "left the federation");
+  }
+  return {};
+}
+
+void Controller::EvictLocked(const std::string& id, const char* why) {
+  learners_.erase(id);
+  local_tasks_.erase(id);
+  store_->EraseModels({id});
+  Log("learner %s %s", id, why);
+  // a shrinking federation may complete a synchronous barrier
+  if (params_.protocol != Protocol::kAsynchronous && !learners_.empty() && !stop_) {
+    pool_.Push([this] {
+      std::lock_guard<std::mutex> l(mu_);
+      auto* sync = dynamic_cast<SynchronousScheduler*>(scheduler_.get());
+      if (!sync) return;
+      auto active = ActiveIdsLocked();
+      if (active.empty()) return;
+      // re-check the barrier by replaying an already-completed learner (idempotent insert)
+      for (auto& a : active) {
+        auto lt = local_tasks_.find(a);
+        if (lt != local_tasks_.end() && !lt->second.empty() &&
+            lt->second.front().global_iteration == global_iteration_) {
+          auto next = scheduler_->ScheduleNext(a, active);
+          if (!next.empty()) AfterBarrier(next, a);
+          return;
+        }
+      }
+    });
+  }
+}
+
+StatusOr Controller::LearnerCompletedTask(const std::string& id, const std::string& token, std::string model_bytes,
+                                          TaskMeta meta) {
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    auto it = learners_.find(id);
+    if (it == learners_.end() || it->second.auth_token != token)
+      return {Status::kUnauthenticated, "Learner does not exist or incorrect credentials."};
+    it->second.task_in_flight = false;
+    // the task's own iteration stamps the metadata slot (falls back to the current round)
+    uint32_t iter = meta.global_iteration ? meta.global_iteration : global_iteration_;
+    if (iter >= 1 && iter <= metadata_.size()) {
+      auto& md = metadata_[iter - 1];
+      md.completed.push_back(id);
+      md.train_received_at[id] = NowSeconds();
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    store_->InsertModel(id, std::make_shared<std::string>(std::move(model_bytes)));
+    if (!metadata_.empty()) metadata_.back().insertion_ms[id] = ElapsedMs(t0);
+    if (!meta.global_iteration) meta.global_iteration = global_iteration_;
+    local_tasks_[id].push_front(std::move(meta));
+  }
+  pool_.Push([this, id] { ScheduleTasks(id); });
+  return {};
+}
+
+void Controller::EvaluationCompleted(const std::string& id, uint32_t eval_index, std::string bytes) {
+  std::lock_guard<std::mutex> l(mu_);
+  if (eval_index < evaluations_.size()) {
+    evaluations_[eval_index].evaluations[id] = std::move(bytes);
+    const uint32_t it = evaluations_[eval_index].global_iteration;
+    if (it >= 1 && it <= metadata_.size()) metadata_[it - 1].eval_received_at[id] = NowSeconds();
+  }
+}
+
+void Controller::TaskFailed(const std::string& id, const std::string& what) {
+  Log("RPC to learner %s failed: %s", id, what);
+}
+
+// ---------------------------------------------------------------------------------------------
+void Controller::ScheduleInitialTask(const std::string& id) {
+  std::lock_guard<std::mutex> l(mu_);
+  if (stop_ || !learners_.count(id)) return;
+  if (!community_model_ || community_model_->empty()) {  // nothing to train on yet (quirk Q5)
+    pending_initial_.push_back(id);
+    return;
+  }
+  if (global_iteration_ == 0) {
+    global_iteration_ = 1;
+    RuntimeMetadata md;
+    md.global_iteration = 1;
+    md.started_at = NowSeconds();
+    metadata_.push_back(std::move(md));
+  }
+  SendRunTasksLocked({id});
+}
+
+void Controller::SendRunTasksLocked(const std::vector<std::string>& ids) {
+  std::vector<TaskItem> items;
+  const double now = NowSeconds();
+  for (auto& id : ids) {
+    auto it = learners_.find(id);
+    if (it == learners_.end()) continue;
+    auto& rec = it->second;
+    rec.task_issued_iteration = global_iteration_;
+    rec.task_issued_at = now;
+    rec.task_in_flight = true;
+    items.push_back({rec.endpoint, global_iteration_, rec.num_local_updates, params_.percent_validation});
+    if (!metadata_.empty()) {
+      metadata_.back().assigned.push_back(id);
+      metadata_.back().train_submitted_at[id] = now;
+    }
+  }
+  if (!items.empty() && dispatcher_) dispatcher_->SendRunTasks(items, community_);
+}
+
+void Controller::SendEvaluationTasksLocked(const std::vector<std::string>& ids, uint32_t eval_index) {
+  std::vector<LearnerEndpoint> eps;
+  const double now = NowSeconds();
+  const uint32_t it = evaluations_[eval_index].global_iteration;
+  for (auto& id : ids) {
+    auto f = learners_.find(id);
+    if (f == learners_.end()) continue;
+    eps.push_back(f->second.endpoint);
+    if (it >= 1 && it <= metadata_.size()) metadata_[it - 1].eval_submitted_at[id] = now;
+  }
+  if (!eps.empty() && dispatcher_)
+    dispatcher_->SendEvaluationTasks(eps, community_model_, params_.batch_size, eval_index, it);
+}
+
+void Controller::ScheduleTasks(const std::string& id) {
+  std::lock_guard<std::mutex> l(mu_);
+  if (stop_ || !learners_.count(id)) return;
+  const auto active = ActiveIdsLocked();
+  auto to_schedule = scheduler_->ScheduleNext(id, active);
+  if (to_schedule.empty()) return;  // synchronous barrier not reached yet
+  AfterBarrier(to_schedule, id);
+}
+
+void Controller::AfterBarrier(const std::vector<std::string>& to_schedule, const std::string& completing) {
+  const auto active = ActiveIdsLocked();
+  const auto selected = ScheduledCardinality::Select(to_schedule, active);
+  if (metadata_.empty()) return;
+  RuntimeMetadata& md = metadata_.back();
+  uint32_t contributors = 0;
+  ModelBytes model;
+  try {
+    model = ComputeCommunityModel(selected, completing, md, &contributors);
+  } catch (const std::exception& e) {
+    Log("aggregation failed: %s", e.what());
+    return;
+  }
+  if (model && !model->empty()) {
+    RecordModelSize(*model, md);
+    community_model_ = model;
+    community_ = std::make_shared<std::string>(wire::BuildFederatedModel(contributors, global_iteration_, *model));
+    if (auto* fa = dynamic_cast<FedAsync*>(aggregator_.get())) fa->SetCommunity(community_model_);
+    community_lineage_.push_back(community_);
+    while (community_lineage_.size() > std::max<uint32_t>(1, params_.community_lineage_length)) community_lineage_.pop_front();
+  }
+  CommunityEvaluation ev;
+  ev.global_iteration = global_iteration_;
+  evaluations_.push_back(std::move(ev));
+  md.completed_at = NowSeconds();
+  if (params_.evaluate_community_model) SendEvaluationTasksLocked(to_schedule, (uint32_t)evaluations_.size() - 1);
+  ++global_iteration_;
+  if (params_.protocol == Protocol::kSemiSynchronous &&
+      (global_iteration_ == 2 || params_.semi_sync_recompute))
+    UpdateTaskTemplates(to_schedule);
+  RuntimeMetadata next;
+  next.global_iteration = global_iteration_;
+  next.started_at = NowSeconds();
+  metadata_.push_back(std::move(next));
+  SendRunTasksLocked(to_schedule);
+}
+
+ModelBytes Controller::ComputeCommunityModel(const std::vector<std::string>& selected, const std::string& completing,
+                                             RuntimeMetadata& md, uint32_t* contributors) {
+  const auto t_start = std::chrono::steady_clock::now();
+  md.aggregation_started_at = NowSeconds();
+  const bool single = params_.rule == "FedRec" || params_.rule == "FedAsync";
+  // participants: the completing learner for per-contribution rules (Q2), otherwise every selected
+  // learner that actually has a stored model (Q14)
+  std::vector<std::string> parts;
+  if (single) parts.push_back(completing);
+  else
+    for (auto& id : selected)
+      if (store_->GetLearnerLineageLength(id) > 0) parts.push_back(id);
+  std::vector<LearnerStats> stats;
+  for (auto& id : parts) {
+    LearnerStats s;
+    s.id = id;
+    auto f = learners_.find(id);
+    if (f != learners_.end()) s.num_training_examples = f->second.n_train;
+    auto lt = local_tasks_.find(id);
+    if (lt != local_tasks_.end() && !lt->second.empty()) s.completed_batches = lt->second.front().completed_batches;  // latest
+    stats.push_back(s);
+  }
+  auto weights = ComputeScalingFactors(params_.scaling, learners_.size(), stats);
+  size_t stride = parts.size();
+  if (params_.rule == "FedStride" && params_.stride_length > 0) stride = params_.stride_length;
+  if (stride == 0) stride = 1;
+  const int need = aggregator_->RequiredLearnerLineageLength();
+  Aggregated result;
+  for (size_t b = 0; b < parts.size(); b += stride) {
+    const auto t_block = std::chrono::steady_clock::now();
+    std::vector<std::pair<std::string, int>> req;
+    for (size_t i = b; i < std::min(parts.size(), b + stride); ++i) {
+      const int have = store_->GetLearnerLineageLength(parts[i]);
+      req.emplace_back(parts[i], std::min(have, need));
+    }
+    const auto t_sel = std::chrono::steady_clock::now();
+    auto models = store_->SelectModels(req);
+    const double sel_ms = ElapsedMs(t_sel);
+    std::vector<LearnerModels> block;
+    for (auto& [id, n] : req) {
+      md.selection_ms[id] = sel_ms / (double)req.size();
+      auto f = models.find(id);
+      if (f == models.end() || f->second.empty()) continue;
+      LearnerModels lm;
+      lm.lineage = f->second;
+      lm.weight = weights[id];
+      auto lr = learners_.find(id);
+      if (lr != learners_.end())
+        lm.staleness = (double)global_iteration_ - (double)lr->second.task_issued_iteration;
+      block.push_back(std::move(lm));
+    }
+    md.block_size.push_back((double)block.size());
+    result = aggregator_->Aggregate(block);
+    md.block_memory_kb.push_back((double)MaxRssKb());
+    md.block_duration_ms.push_back(ElapsedMs(t_block));
+    store_->ResetState();
+  }
+  aggregator_->Reset();
+  md.aggregation_completed_at = NowSeconds();
+  md.aggregation_total_ms = ElapsedMs(t_start);
+  *contributors = result.num_contributors;
+  return std::make_shared<std::string>(std::move(result.model));
+}
+
+template <typename T> static uint32_t CountZeros(const char* p, size_t n) {
+  uint32_t z = 0;
+  for (size_t i = 0; i < n; ++i) z += (double(load_unaligned<T>(reinterpret_cast<const T*>(p) + i)) == 0.0);
+  return z;
+}
+
+void Controller::RecordModelSize(const std::string& model, RuntimeMetadata& md) {
+  std::vector<wire::VariableView> vars;
+  if (!wire::ParseModel(model, vars)) return;
+  md.quantifiers.assign(vars.size(), TensorQuant{});
+#pragma omp parallel for schedule(dynamic)
+  for (long v = 0; v < (long)vars.size(); ++v) {
+    const auto& t = vars[v].t;
+    TensorQuant q;
+    q.bytes = (uint32_t)t.value.size();
+    if (!vars[v].ciphertext && t.value.size() >= (size_t)t.length * wire::DTypeSize(t.dtype)) {
+      uint32_t zeros = 0;
+      try {
+        MFL_HOST_DISPATCH(t.dtype, T, zeros = CountZeros<T>(t.value.data(), t.length));
+      } catch (...) {}
+      q.zeros = zeros;
+      q.non_zeros = t.length - zeros;
+    }
+    md.quantifiers[v] = q;
+  }
+}
+
+void Controller::UpdateTaskTemplates(const std::vector<std::string>& ids) {
+  // semi-synchronous: every learner trains for t_max = lambda * (slowest learner's epoch time)
+  double slowest_epoch_ms = 0;
+  for (auto& id : ids) {
+    auto lt = local_tasks_.find(id);
+    if (lt != local_tasks_.end() && !lt->second.empty())
+      slowest_epoch_ms = std::max(slowest_epoch_ms, (double)lt->second.front().ms_per_epoch);
+  }
+  const double t_max = (double)params_.semi_sync_lambda * slowest_epoch_ms;
+  for (auto& id : ids) {
+    auto lt = local_tasks_.find(id);
+    auto lr = learners_.find(id);
+    if (lt == local_tasks_.end() || lt->second.empty() || lr == learners_.end()) continue;
+    double ms_per_batch = lt->second.front().ms_per_batch;
+    if (ms_per_batch <= 0) ms_per_batch = 1.0;
+    const double n = std::ceil(t_max / ms_per_batch);
+    if (n >= 1) lr->second.num_local_updates = (uint32_t)n;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+void Controller::WatchdogLoop() {
+  while (!stop_) {
+    {
+      std::unique_lock<std::mutex> l(wd_mu_);
+      wd_cv_.wait_for(l, std::chrono::milliseconds(200), [this] { return stop_.load(); });
+    }
+    if (stop_) break;
+    std::lock_guard<std::mutex> l(mu_);
+    const double now = NowSeconds();
+    std::vector<std::string> overdue;
+    for (auto& [id, rec] : learners_)
+      if (rec.task_in_flight && now - rec.task_issued_at > params_.task_deadline_secs) overdue.push_back(id);
+    for (auto& id : overdue) EvictLocked(id, "evicted: task deadline exceeded");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+std::vector<LearnerRecord> Controller::GetLearners() {
+  std::lock_guard<std::mutex> l(mu_);
+  std::vector<LearnerRecord> out;
+  for (auto& kv : learners_) out.push_back(kv.second);
+  return out;
+}
+
+ModelBytes Controller::CommunityModel() {
+  std::lock_guard<std::mutex> l(mu_);
+  return community_;
+}
+
+uint32_t Controller::GlobalIteration() {
+  std::lock_guard<std::mutex> l(mu_);
+  return global_iteration_;
+}
+
+template <typename C> static C Tail(const C& c, int n) {
+  if (n <= 0 || (size_t)n >= c.size()) return c;
+  return C(c.end() - n, c.end());
+}
+
+std::vector<RuntimeMetadata> Controller::GetRuntimeMetadataLineage(int n) {
+  std::lock_guard<std::mutex> l(mu_);
+  return Tail(metadata_, n);
+}
+
+std::vector<CommunityEvaluation> Controller::GetCommunityEvaluationLineage(int n) {
+  std::lock_guard<std::mutex> l(mu_);
+  return Tail(evaluations_, n);
+}
+
+std::map<std::string, std::vector<std::string>> Controller::GetLocalTaskLineage(const std::vector<std::string>& ids, int n) {
+  std::lock_guard<std::mutex> l(mu_);
+  std::map<std::string, std::vector<std::string>> out;
+  auto add = [&](const std::string& id, const std::deque<TaskMeta>& q) {
+    auto& v = out[id];
+    size_t k = 0;
+    for (auto& m : q) {  // newest first
+      if (n > 0 && k++ >= (size_t)n) break;
+      v.push_back(m.serialized);
+    }
+  };
+  if (ids.empty()) for (auto& kv : local_tasks_) add(kv.first, kv.second);
+  else for (auto& id : ids) { auto f = local_tasks_.find(id); if (f != local_tasks_.end()) add(id, f->second); }
+  return out;
+}
+
+std::vector<ModelBytes> Controller::GetCommunityModelLineage(int n) {
+  std::lock_guard<std::mutex> l(mu_);
+  std::vector<ModelBytes> all(community_lineage_.begin(), community_lineage_.end());
+  return Tail(all, n);
+}
+
+std::map<std::string, std::vector<ModelBytes>> Controller::GetLearnerLocalModelLineage(const std::vector<std::string>& ids, int n) {
+  std::vector<std::pair<std::string, int>> req;
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    if (ids.empty()) for (auto& kv : learners_) req.emplace_back(kv.first, 0);
+    else for (auto& id : ids) req.emplace_back(id, 0);
+  }
+  auto all = store_->SelectModels(req);
+  store_->ResetState();
+  for (auto& kv : all) kv.second = Tail(kv.second, n);
+  return all;
+}
+
+}  // namespace mfl::core
