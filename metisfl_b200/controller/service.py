@@ -1,0 +1,303 @@
+"""gRPC face of the controller: ``ControllerService`` (12 RPCs) on top of the native core.
+
+Counterpart of the reference's C++ servicer (``controller/core/controller_servicer.cc:29-390``) and
+of the async RunTask / EvaluateModel fan-out of its core (``controller.cc:571-759``).  The native
+core (``metisfl_b200._core.Controller``) owns all federation state; this layer only (de)serialises
+protobuf, maps status codes, and moves bytes over gRPC.  Unlike the reference, the two lineage RPCs
+that it declares but never implements (``GetCommunityModelLineage``,
+``GetLearnerLocalModelLineage``; reference gives UNIMPLEMENTED) are served.
+"""
+from __future__ import annotations
+
+import concurrent.futures
+import threading
+
+import grpc
+from google.protobuf.timestamp_pb2 import Timestamp
+
+from metisfl_b200 import _core
+from metisfl_b200.proto import (controller_pb2, controller_pb2_grpc, learner_pb2, learner_pb2_grpc, metis_pb2,
+                                model_pb2, service_common_pb2)
+from metisfl_b200.utils.grpc_services import GRPCChannelMaxMsgLength, GRPCServerMaxMsgLength
+from metisfl_b200.utils.metis_logger import MetisLogger
+
+_STATUS_TO_GRPC = {
+    int(_core.Status.INVALID_ARGUMENT): grpc.StatusCode.INVALID_ARGUMENT,
+    int(_core.Status.ALREADY_EXISTS): grpc.StatusCode.ALREADY_EXISTS,
+    int(_core.Status.NOT_FOUND): grpc.StatusCode.NOT_FOUND,
+    int(_core.Status.UNAUTHENTICATED): grpc.StatusCode.UNAUTHENTICATED,
+    int(_core.Status.FAILED_PRECONDITION): grpc.StatusCode.FAILED_PRECONDITION,
+    int(_core.Status.INTERNAL): grpc.StatusCode.INTERNAL,
+}
+
+
+def _ts(seconds: float) -> Timestamp:
+    t = Timestamp()
+    if seconds:
+        t.FromNanoseconds(int(seconds * 1e9))
+    return t
+
+
+def _ack(status=True, message="") -> service_common_pb2.Ack:
+    t = Timestamp()
+    t.GetCurrentTime()
+    return service_common_pb2.Ack(status=status, timestamp=t, message=message)
+
+
+def params_pb_to_core(pb: metis_pb2.ControllerParams) -> "_core.ControllerParams":
+    """``metisfl.ControllerParams`` -> native parameter struct (factories of
+    ``controller_utils.cc:13-70``)."""
+    p = _core.ControllerParams()
+    p.hostname = pb.server_entity.hostname or "localhost"
+    p.port = pb.server_entity.port or 50051
+    rule = pb.global_model_specs.aggregation_rule
+    which = rule.WhichOneof("rule") or "fed_avg"
+    p.rule = {"fed_avg": "FedAvg", "fed_stride": "FedStride", "fed_rec": "FedRec", "pwa": "PWA",
+              "fed_async": "FedAsync"}[which]
+    if which == "fed_stride":
+        p.stride_length = rule.fed_stride.stride_length
+    if which == "fed_async":
+        p.fedasync_alpha = rule.fed_async.alpha or 0.5
+        p.staleness_fn = int(rule.fed_async.staleness_fn)
+        p.staleness_a = rule.fed_async.a or 0.5
+        p.staleness_b = rule.fed_async.b or 4.0
+    if which == "pwa":
+        he = rule.pwa.he_scheme_config
+        p.he_crypto_context_file = he.crypto_context_file
+        if he.WhichOneof("config") == "ckks_scheme_config":
+            p.he_batch_size = he.ckks_scheme_config.batch_size
+            p.he_scaling_bits = he.ckks_scheme_config.scaling_factor_bits
+    p.scaling = int(rule.aggregation_rule_specs.scaling_factor) or 3
+    p.participation_ratio = pb.global_model_specs.learners_participation_ratio or 1.0
+    p.protocol = int(pb.communication_specs.protocol) or 1
+    p.semi_sync_lambda = pb.communication_specs.protocol_specs.semi_sync_lambda
+    p.semi_sync_recompute = pb.communication_specs.protocol_specs.semi_sync_recompute_num_updates
+    p.task_deadline_secs = pb.communication_specs.protocol_specs.task_deadline_secs
+    store = pb.model_store_config
+    kind = store.WhichOneof("config")
+    specs = store.redis_db_store.model_store_specs if kind == "redis_db_store" else store.in_memory_store.model_store_specs
+    if kind == "redis_db_store":
+        p.redis = True
+        p.redis_host = store.redis_db_store.server_entity.hostname or "127.0.0.1"
+        p.redis_port = store.redis_db_store.server_entity.port or 6379
+    if specs.WhichOneof("eviction_policy") == "lineage_length_eviction":
+        p.lineage_length_eviction = True
+        p.lineage_length = specs.lineage_length_eviction.lineage_length
+    # rules that swap a learner's previous model need it to still be stored
+    need = 2 if p.rule == "FedRec" else 1
+    if p.lineage_length_eviction and max(1, p.lineage_length) < need:
+        p.lineage_length = need
+    p.batch_size = pb.model_hyperparams.batch_size
+    p.epochs = pb.model_hyperparams.epochs
+    p.percent_validation = pb.model_hyperparams.percent_validation
+    return p
+
+
+class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
+
+    def __init__(self, params_pb: metis_pb2.ControllerParams, learner_client_workers: int = 16):
+        self.params_pb = params_pb
+        self._hyper = metis_pb2.Hyperparameters(batch_size=params_pb.model_hyperparams.batch_size,
+                                                optimizer=params_pb.model_hyperparams.optimizer)
+        self._rpc_pool = concurrent.futures.ThreadPoolExecutor(max_workers=learner_client_workers,
+                                                               thread_name_prefix="ctrl-fanout")
+        self._channels = {}
+        self._channels_lock = threading.Lock()
+        self.core = _core.Controller(params_pb_to_core(params_pb), self._send_run_tasks, self._send_evaluation_tasks)
+        self._shutdown_event = threading.Event()
+        self._server = None
+        self._evaluation_metrics = metis_pb2.EvaluationMetrics()
+
+    # -- server lifecycle -----------------------------------------------------------------------
+    def start(self, max_workers: int = 16):
+        self._server_holder = GRPCServerMaxMsgLength(max_workers=max_workers, server_entity=self.params_pb.server_entity)
+        self._server = self._server_holder.server
+        controller_pb2_grpc.add_ControllerServiceServicer_to_server(self, self._server)
+        self._server.start()
+        MetisLogger.info("Controller listening on %s:%s", self.params_pb.server_entity.hostname,
+                         self.params_pb.server_entity.port)
+
+    def stop(self, grace=1.0):
+        self.core.shutdown()
+        if self._server is not None:
+            self._server.stop(grace).wait()
+            self._server = None
+        self._rpc_pool.shutdown(wait=False, cancel_futures=True)
+        with self._channels_lock:
+            for ch, _ in self._channels.values():
+                ch.close()
+            self._channels.clear()
+
+    def shutdown_request_received(self):
+        return self._shutdown_event.is_set()
+
+    # -- outbound fan-out (called by the native core) -------------------------------------------
+    def _stub_for(self, learner_id, hostname, port, cert):
+        with self._channels_lock:
+            if learner_id not in self._channels:
+                ssl_pb = None
+                if cert:
+                    ssl_pb = metis_pb2.SSLConfig(enable_ssl=True, ssl_config_stream=metis_pb2.SSLConfigStream(
+                        public_certificate_stream=cert))
+                entity = metis_pb2.ServerEntity(hostname=hostname, port=port, ssl_config=ssl_pb)
+                ch = GRPCChannelMaxMsgLength(entity).channel
+                self._channels[learner_id] = (ch, learner_pb2_grpc.LearnerServiceStub(ch))
+            return self._channels[learner_id][1]
+
+    def _send_run_tasks(self, items, federated_model_bytes):
+        fm = model_pb2.FederatedModel.FromString(federated_model_bytes)
+        for (lid, host, port, cert, iteration, updates, pct_valid) in items:
+            req = learner_pb2.RunTaskRequest(
+                federated_model=fm,
+                task=metis_pb2.LearningTask(global_iteration=iteration, num_local_updates=updates,
+                                            training_dataset_percentage_for_stratified_validation=pct_valid,
+                                            metrics=self._evaluation_metrics),
+                hyperparameters=self._hyper)
+            self._rpc_pool.submit(self._do_run_task, lid, host, port, cert, req)
+
+    def _do_run_task(self, lid, host, port, cert, req):
+        try:
+            self._stub_for(lid, host, port, cert).RunTask(req, timeout=600)
+        except Exception as e:  # grpc.RpcError and friends: the core decides what to do (deadline)
+            self.core.task_failed(lid, f"RunTask: {e}")
+
+    def _send_evaluation_tasks(self, learners, model_bytes, batch_size, eval_index, iteration):
+        model = model_pb2.Model.FromString(model_bytes)
+        E = learner_pb2.EvaluateModelRequest
+        req = E(model=model, batch_size=batch_size, evaluation_dataset=[E.TRAINING, E.VALIDATION, E.TEST],
+                metrics=self._evaluation_metrics)
+        for (lid, host, port, cert) in learners:
+            self._rpc_pool.submit(self._do_evaluate, lid, host, port, cert, req, eval_index)
+
+    def _do_evaluate(self, lid, host, port, cert, req, eval_index):
+        try:
+            resp = self._stub_for(lid, host, port, cert).EvaluateModel(req, timeout=600)
+            self.core.evaluation_completed(lid, eval_index, resp.evaluations.SerializeToString())
+        except Exception as e:
+            self.core.task_failed(lid, f"EvaluateModel: {e}")
+
+    # -- helpers ----------------------------------------------------------------------------------
+    @staticmethod
+    def _abort(context, err):
+        code = _STATUS_TO_GRPC.get(getattr(err, "code", None), grpc.StatusCode.INTERNAL)
+        context.abort(code, str(err))
+
+    @staticmethod
+    def _metadata_pb(d) -> metis_pb2.FederatedTaskRuntimeMetadata:
+        md = metis_pb2.FederatedTaskRuntimeMetadata(
+            global_iteration=d["global_iteration"],
+            assigned_to_learner_id=d["assigned_to_learner_id"],
+            completed_by_learner_id=d["completed_by_learner_id"],
+            model_insertion_duration_ms=d["model_insertion_duration_ms"],
+            model_selection_duration_ms=d["model_selection_duration_ms"],
+            model_aggregation_total_duration_ms=d["model_aggregation_total_duration_ms"],
+            model_aggregation_block_size=d["model_aggregation_block_size"],
+            model_aggregation_block_memory_kb=d["model_aggregation_block_memory_kb"],
+            model_aggregation_block_duration_ms=d["model_aggregation_block_duration_ms"])
+        for name in ("started_at", "completed_at", "model_aggregation_started_at", "model_aggregation_completed_at"):
+            if d[name]:
+                getattr(md, name).CopyFrom(_ts(d[name]))
+        for name in ("train_task_submitted_at", "train_task_received_at", "eval_task_submitted_at",
+                     "eval_task_received_at"):
+            for k, v in d[name].items():
+                getattr(md, name)[k].CopyFrom(_ts(v))
+        for nz, z, nbytes in d["model_tensor_quantifiers"]:
+            md.model_tensor_quantifiers.add(tensor_non_zeros=nz, tensor_zeros=z, tensor_size_bytes=nbytes)
+        return md
+
+    # -- RPC handlers -----------------------------------------------------------------------------
+    def GetServicesHealthStatus(self, request, context):
+        return service_common_pb2.GetServicesHealthStatusResponse(services_status={"controller": True})
+
+    def JoinFederation(self, request, context):
+        se, ds = request.server_entity, request.local_dataset_spec
+        cert = b""
+        if se.ssl_config.enable_ssl and se.ssl_config.WhichOneof("config") == "ssl_config_stream":
+            cert = se.ssl_config.ssl_config_stream.public_certificate_stream
+        try:
+            learner_id, token = self.core.add_learner(
+                se.hostname, se.port, se.SerializeToString(), ds.SerializeToString(), ds.num_training_examples,
+                ds.num_validation_examples, ds.num_test_examples, cert)
+        except _core.ControllerError as e:
+            self._abort(context, e)
+        return controller_pb2.JoinFederationResponse(ack=_ack(), learner_id=learner_id, auth_token=token)
+
+    def LeaveFederation(self, request, context):
+        try:
+            self.core.remove_learner(request.learner_id, request.auth_token)
+        except _core.ControllerError as e:
+            self._abort(context, e)
+        with self._channels_lock:
+            ch = self._channels.pop(request.learner_id, None)
+        if ch:
+            ch[0].close()
+        return controller_pb2.LeaveFederationResponse(ack=_ack())
+
+    def MarkTaskCompleted(self, request, context):
+        md = request.task.execution_metadata
+        try:
+            self.core.learner_completed_task(
+                request.learner_id, request.auth_token, request.task.model.SerializeToString(),
+                md.global_iteration, md.completed_epochs, md.completed_batches, md.batch_size,
+                md.processing_ms_per_epoch, md.processing_ms_per_batch, md.SerializeToString())
+        except _core.ControllerError as e:
+            self._abort(context, e)
+        return controller_pb2.MarkTaskCompletedResponse(ack=_ack())
+
+    def ReplaceCommunityModel(self, request, context):
+        try:
+            self.core.replace_community_model(request.model.SerializeToString())
+        except _core.ControllerError as e:
+            self._abort(context, e)
+        return controller_pb2.ReplaceCommunityModelResponse(ack=_ack())
+
+    def GetParticipatingLearners(self, request, context):
+        resp = controller_pb2.GetParticipatingLearnersResponse()
+        for rec in self.core.get_learners():
+            resp.learner.add(id=rec["id"], server_entity=metis_pb2.ServerEntity.FromString(rec["server_entity"]),
+                             dataset_spec=metis_pb2.DatasetSpec.FromString(rec["dataset_spec"]))
+        return resp
+
+    def GetRuntimeMetadataLineage(self, request, context):
+        resp = controller_pb2.GetRuntimeMetadataLineageResponse()
+        for d in self.core.get_runtime_metadata_lineage(request.num_backtracks):
+            resp.metadata.append(self._metadata_pb(d))
+        return resp
+
+    def GetCommunityModelEvaluationLineage(self, request, context):
+        resp = controller_pb2.GetCommunityModelEvaluationLineageResponse()
+        for iteration, evals in self.core.get_community_evaluation_lineage(request.num_backtracks):
+            ce = resp.community_evaluation.add(global_iteration=iteration)
+            for lid, blob in evals.items():
+                ce.evaluations[lid].CopyFrom(metis_pb2.ModelEvaluations.FromString(blob))
+        return resp
+
+    def GetLocalTaskLineage(self, request, context):
+        resp = controller_pb2.GetLocalTaskLineageResponse()
+        for lid, metas in self.core.get_local_task_lineage(list(request.learner_ids), request.num_backtracks).items():
+            entry = resp.learner_task[lid]
+            for blob in metas:
+                entry.task_metadata.append(metis_pb2.TaskExecutionMetadata.FromString(blob))
+        return resp
+
+    def GetCommunityModelLineage(self, request, context):
+        resp = controller_pb2.GetCommunityModelLineageResponse()
+        for blob in self.core.get_community_model_lineage(request.num_backtracks):
+            resp.federated_models.append(model_pb2.FederatedModel.FromString(blob))
+        return resp
+
+    def GetLearnerLocalModelLineage(self, request, context):
+        ids = ["{}:{}".format(se.hostname, se.port) for se in request.server_entity]
+        by_id = {rec["id"]: rec for rec in self.core.get_learners()}
+        resp = controller_pb2.GetLearnerLocalModelLineageResponse()
+        for lid, models in self.core.get_learner_local_model_lineage(ids, request.num_backtracks).items():
+            entry = resp.learner_local_model.add()
+            if lid in by_id:
+                entry.server_entity.CopyFrom(metis_pb2.ServerEntity.FromString(by_id[lid]["server_entity"]))
+            for blob in models:
+                entry.model.append(model_pb2.Model.FromString(blob))
+        return resp
+
+    def ShutDown(self, request, context):
+        self._shutdown_event.set()
+        return service_common_pb2.ShutDownResponse(ack=_ack())
