@@ -155,21 +155,24 @@ void Controller::EvictLocked(const std::string& id, const char* why) {
   // a shrinking federation may complete a synchronous barrier
   if (params_.protocol != Protocol::kAsynchronous && !learners_.empty() && !stop_) {
     pool_.Push([this] {
-      std::lock_guard<std::mutex> l(mu_);
-      auto* sync = dynamic_cast<SynchronousScheduler*>(scheduler_.get());
-      if (!sync) return;
-      auto active = ActiveIdsLocked();
-      if (active.empty()) return;
-      // re-check the barrier by replaying an already-completed learner (idempotent insert)
-      for (auto& a : active) {
-        auto lt = local_tasks_.find(a);
-        if (lt != local_tasks_.end() && !lt->second.empty() &&
-            lt->second.front().global_iteration == global_iteration_) {
-          auto next = scheduler_->ScheduleNext(a, active);
-          if (!next.empty()) AfterBarrier(next, a);
-          return;
+      {
+        std::lock_guard<std::mutex> l(mu_);
+        auto* sync = dynamic_cast<SynchronousScheduler*>(scheduler_.get());
+        if (!sync) return;
+        auto active = ActiveIdsLocked();
+        if (active.empty()) return;
+        // re-check the barrier by replaying an already-completed learner (idempotent insert)
+        for (auto& a : active) {
+          auto lt = local_tasks_.find(a);
+          if (lt != local_tasks_.end() && !lt->second.empty() &&
+              lt->second.front().global_iteration == global_iteration_) {
+            auto next = scheduler_->ScheduleNext(a, active);
+            if (!next.empty()) AfterBarrier(next, a);
+            break;
+          }
         }
       }
+      FlushOutbox();
     });
   }
 }
@@ -214,7 +217,14 @@ void Controller::TaskFailed(const std::string& id, const std::string& what) {
 
 // ---------------------------------------------------------------------------------------------
 void Controller::ScheduleInitialTask(const std::string& id) {
-  std::lock_guard<std::mutex> l(mu_);
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    ScheduleInitialTaskLocked(id);
+  }
+  FlushOutbox();
+}
+
+void Controller::ScheduleInitialTaskLocked(const std::string& id) {
   if (stop_ || !learners_.count(id)) return;
   if (!community_model_ || community_model_->empty()) {  // nothing to train on yet (quirk Q5)
     pending_initial_.push_back(id);
@@ -246,7 +256,21 @@ void Controller::SendRunTasksLocked(const std::vector<std::string>& ids) {
       metadata_.back().train_submitted_at[id] = now;
     }
   }
-  if (!items.empty() && dispatcher_) dispatcher_->SendRunTasks(items, community_);
+  if (!items.empty() && dispatcher_) {
+    auto d = dispatcher_;
+    auto fm = community_;
+    std::lock_guard<std::mutex> l(outbox_mu_);
+    outbox_.push_back([d, items, fm] { d->SendRunTasks(items, fm); });
+  }
+}
+
+void Controller::FlushOutbox() {
+  std::vector<std::function<void()>> calls;
+  {
+    std::lock_guard<std::mutex> l(outbox_mu_);
+    calls.swap(outbox_);
+  }
+  for (auto& c : calls) c();
 }
 
 void Controller::SendEvaluationTasksLocked(const std::vector<std::string>& ids, uint32_t eval_index) {
@@ -259,17 +283,25 @@ void Controller::SendEvaluationTasksLocked(const std::vector<std::string>& ids, 
     eps.push_back(f->second.endpoint);
     if (it >= 1 && it <= metadata_.size()) metadata_[it - 1].eval_submitted_at[id] = now;
   }
-  if (!eps.empty() && dispatcher_)
-    dispatcher_->SendEvaluationTasks(eps, community_model_, params_.batch_size, eval_index, it);
+  if (!eps.empty() && dispatcher_) {
+    auto d = dispatcher_;
+    auto model = community_model_;
+    const uint32_t bs = params_.batch_size;
+    std::lock_guard<std::mutex> l(outbox_mu_);
+    outbox_.push_back([d, eps, model, bs, eval_index, it] { d->SendEvaluationTasks(eps, model, bs, eval_index, it); });
+  }
 }
 
 void Controller::ScheduleTasks(const std::string& id) {
-  std::lock_guard<std::mutex> l(mu_);
-  if (stop_ || !learners_.count(id)) return;
-  const auto active = ActiveIdsLocked();
-  auto to_schedule = scheduler_->ScheduleNext(id, active);
-  if (to_schedule.empty()) return;  // synchronous barrier not reached yet
-  AfterBarrier(to_schedule, id);
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    if (stop_ || !learners_.count(id)) return;
+    const auto active = ActiveIdsLocked();
+    auto to_schedule = scheduler_->ScheduleNext(id, active);
+    if (to_schedule.empty()) return;  // synchronous barrier not reached yet
+    AfterBarrier(to_schedule, id);
+  }
+  FlushOutbox();
 }
 
 void Controller::AfterBarrier(const std::vector<std::string>& to_schedule, const std::string& completing) {

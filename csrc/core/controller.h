@@ -156,6 +156,7 @@ class Controller {
 
  private:
   void ScheduleInitialTask(const std::string& id);
+  void ScheduleInitialTaskLocked(const std::string& id);
   void ScheduleTasks(const std::string& id);
   void AfterBarrier(const std::vector<std::string>& to_schedule, const std::string& completing);
   ModelBytes ComputeCommunityModel(const std::vector<std::string>& selected, const std::string& completing,
@@ -167,6 +168,11 @@ class Controller {
   std::vector<std::string> ActiveIdsLocked() const;
   void WatchdogLoop();
   void EvictLocked(const std::string& id, const char* why);
+  // Dispatcher calls are queued while mu_ is held and issued after it is released, so a dispatcher
+  // may call straight back into the controller.
+  void FlushOutbox();
+  std::vector<std::function<void()>> outbox_;
+  std::mutex outbox_mu_;
 
   ControllerParams params_;
   std::shared_ptr<Dispatcher> dispatcher_;

@@ -239,19 +239,25 @@ PYBIND11_MODULE(_core, m) {
   m.def("scheduled_cardinality_select", &ScheduledCardinality::Select);
 
   // ---- stores -------------------------------------------------------------------------------
+  // store calls may block on a socket (Redis): never hold the GIL across them
   py::class_<ModelStore>(m, "ModelStore")
-      .def("insert_model", [](ModelStore& s, const std::string& id, const py::bytes& b) { s.InsertModel(id, ToModel(b)); })
+      .def("insert_model", [](ModelStore& s, const std::string& id, const py::bytes& b) {
+        ModelBytes mb = ToModel(b);
+        py::gil_scoped_release rel;
+        s.InsertModel(id, std::move(mb));
+      })
       .def("select_models", [](ModelStore& s, const std::vector<std::pair<std::string, int>>& req) {
-        auto r = s.SelectModels(req);
+        std::map<std::string, std::vector<ModelBytes>> r;
+        { py::gil_scoped_release rel; r = s.SelectModels(req); }
         py::dict d;
         for (auto& kv : r) d[py::str(kv.first)] = ModelsToList(kv.second);
         return d;
       })
-      .def("erase_models", &ModelStore::EraseModels)
-      .def("expunge", &ModelStore::Expunge)
-      .def("reset_state", &ModelStore::ResetState)
-      .def("get_learner_lineage_length", &ModelStore::GetLearnerLineageLength)
-      .def("shutdown", &ModelStore::Shutdown)
+      .def("erase_models", &ModelStore::EraseModels, py::call_guard<py::gil_scoped_release>())
+      .def("expunge", &ModelStore::Expunge, py::call_guard<py::gil_scoped_release>())
+      .def("reset_state", &ModelStore::ResetState, py::call_guard<py::gil_scoped_release>())
+      .def("get_learner_lineage_length", &ModelStore::GetLearnerLineageLength, py::call_guard<py::gil_scoped_release>())
+      .def("shutdown", &ModelStore::Shutdown, py::call_guard<py::gil_scoped_release>())
       .def("name", &ModelStore::Name);
   auto mk_policy = [](bool evict, uint32_t len) { EvictionPolicy p; p.lineage_length_eviction = evict; p.lineage_length = len; return p; };
   py::class_<HashMapModelStore, ModelStore>(m, "HashMapModelStore")
@@ -259,6 +265,7 @@ PYBIND11_MODULE(_core, m) {
            py::arg("lineage_length_eviction") = false, py::arg("lineage_length") = 0);
   py::class_<RedisModelStore, ModelStore>(m, "RedisModelStore")
       .def(py::init([mk_policy](const std::string& host, int port, bool evict, uint32_t len) {
+             py::gil_scoped_release rel;
              return new RedisModelStore(host, port, mk_policy(evict, len));
            }),
            py::arg("hostname") = "127.0.0.1", py::arg("port") = 6379, py::arg("lineage_length_eviction") = false,

@@ -101,6 +101,9 @@ bool RespClient::Connect(const std::string& host, int port, double timeout_s, st
       fcntl(fd, F_SETFL, fl);
       int one = 1;
       setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
+      timeval tv{60, 0};  // a dead server must not block the controller forever
+      setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+      setsockopt(fd, SOL_SOCKET, SO_SNDTIMEO, &tv, sizeof(tv));
       fd_ = fd;
       break;
     }

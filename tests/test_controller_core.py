@@ -1,0 +1,228 @@
+"""Federation state machine of the native core, driven with in-process echo learners (the
+reference's manual load-test learner, ``test/learner_notrain_noeval.py:16-198``, turned into an
+automated protocol test)."""
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from metisfl_b200 import _core
+from helpers import model_arrays, model_bytes
+
+
+class Federation:
+    """Controller + N fake learners that answer RunTask by adding ``delta`` to the model."""
+
+    def __init__(self, rule="FedAvg", protocol=1, n=3, examples=None, stride=0, deadline=0.0, lineage=None,
+                 semi_lambda=0, auto=True):
+        p = _core.ControllerParams()
+        p.rule, p.protocol, p.stride_length = rule, protocol, stride
+        p.batch_size, p.epochs = 10, 2
+        p.task_deadline_secs = deadline
+        p.semi_sync_lambda = semi_lambda
+        if lineage:
+            p.lineage_length_eviction, p.lineage_length = True, lineage
+        self.run_log, self.eval_log = [], []
+        self.lock = threading.Lock()
+        self.auto = auto
+        self.tokens = {}
+        self.delta = {}
+        self.ms_per_batch = {}
+        self.mute = set()
+        self.core = _core.Controller(p, self._run, self._eval)
+        self.examples = examples or [100] * n
+        self.n = n
+
+    def _run(self, items, fm):
+        c, it, model = _core.parse_federated_model(fm)
+        with self.lock:
+            self.run_log.append(([i[0] for i in items], items[0][4], [i[5] for i in items]))
+        if not self.auto:
+            return
+        for (lid, host, port, cert, iteration, updates, pct) in items:
+            if lid in self.mute:
+                continue
+            threading.Thread(target=self._complete, args=(lid, model, iteration, updates), daemon=True).start()
+
+    def _complete(self, lid, model, iteration, updates):
+        x = model_arrays(model)[0]
+        new = model_bytes([x + self.delta.get(lid, 0.0)])
+        self.core.learner_completed_task(lid, self.tokens[lid], new, iteration, 1.0, updates, 10,
+                                         self.ms_per_batch.get(lid, 1.0) * 10, self.ms_per_batch.get(lid, 1.0), b"")
+
+    def _eval(self, learners, model, batch_size, idx, iteration):
+        with self.lock:
+            self.eval_log.append(([l[0] for l in learners], idx, iteration))
+        for l in learners:
+            self.core.evaluation_completed(l[0], idx, b"")
+
+    def join(self, i):
+        lid, tok = self.core.add_learner("127.0.0.1", 9000 + i, b"", b"", self.examples[i], 0, 0)
+        self.tokens[lid] = tok
+        return lid
+
+    def wait_rounds(self, n, timeout=20):
+        t0 = time.time()
+        while time.time() - t0 < timeout:
+            if self.core.global_iteration() > n:
+                return
+            time.sleep(0.01)
+        raise AssertionError(f"only reached iteration {self.core.global_iteration()}")
+
+    def community(self):
+        c, it, model = _core.parse_federated_model(self.core.community_model())
+        return c, it, model_arrays(model)[0]
+
+
+def test_join_validation_and_tokens():
+    f = Federation(auto=False)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    lid = f.join(0)
+    assert lid == "127.0.0.1:9000" and len(f.tokens[lid]) == 64
+    with pytest.raises(_core.ControllerError) as e:
+        f.join(0)
+    assert e.value.code == int(_core.Status.ALREADY_EXISTS)
+    with pytest.raises(_core.ControllerError) as e:
+        f.core.add_learner("", 1, b"", b"", 10, 0, 0)
+    assert e.value.code == int(_core.Status.INVALID_ARGUMENT)
+    with pytest.raises(_core.ControllerError) as e:
+        f.core.add_learner("h", 1, b"", b"", 0, 0, 0)
+    assert e.value.code == int(_core.Status.INVALID_ARGUMENT)
+    with pytest.raises(_core.ControllerError) as e:
+        f.core.learner_completed_task(lid, "wrong", b"", 1, 0, 0, 0, 0, 0, b"")
+    assert e.value.code == int(_core.Status.UNAUTHENTICATED)
+    f.core.wait_idle()
+    # task template: epochs * ceil(n_train / batch) = 2 * ceil(100 / 10)
+    assert f.run_log[0] == ([lid], 1, [20])
+    f.core.remove_learner(lid, f.tokens[lid])
+    assert f.core.get_learners() == []
+    f.core.shutdown()
+
+
+def test_learner_joining_before_the_model_waits_for_it():
+    f = Federation(auto=False)
+    lid = f.join(0)
+    f.core.wait_idle()
+    assert f.run_log == []
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.ones(4, np.float32)])))
+    f.core.wait_idle()
+    assert f.run_log and f.run_log[0][0] == [lid]
+    f.core.shutdown()
+
+
+def test_synchronous_fedavg_rounds_and_metadata():
+    f = Federation(n=3, examples=[100, 300, 600])
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    ids = [f.join(i) for i in range(3)]
+    for lid, d in zip(ids, (1.0, 2.0, 3.0)):
+        f.delta[lid] = d
+    f.wait_rounds(3)
+    f.mute.update(ids)
+    time.sleep(0.1)
+    f.core.wait_idle()
+    md = f.core.get_runtime_metadata_lineage(0)
+    r1 = md[0]
+    assert r1["global_iteration"] == 1 and sorted(r1["completed_by_learner_id"]) == sorted(ids)
+    assert r1["model_aggregation_block_size"] == [3.0] and len(r1["model_tensor_quantifiers"]) == 1
+    assert r1["model_tensor_quantifiers"][0] == (8, 0, 32)
+    assert set(r1["train_task_received_at"]) == set(ids) and set(r1["eval_task_received_at"]) == set(ids)
+    # community after round 1 = weighted mean of deltas: 0.1*1 + 0.3*2 + 0.6*3 = 2.5; then +2.5 per round
+    lineage = f.core.get_community_model_lineage(0)
+    vals = [model_arrays(_core.parse_federated_model(b)[2])[0][0] for b in lineage]
+    assert len(vals) >= 2 and all(abs(v / 2.5 - round(v / 2.5)) < 1e-4 for v in vals) and max(vals) >= 7.5
+    c, it, x = f.community()
+    assert c == 3 and abs(x[0] / 2.5 - round(x[0] / 2.5)) < 1e-5
+    ev = f.core.get_community_evaluation_lineage(0)
+    assert ev[0][0] == 1 and set(ev[0][1]) == set(ids)
+    tasks = f.core.get_local_task_lineage(ids[:1], 2)
+    assert len(tasks[ids[0]]) == 2
+    assert len(f.core.get_runtime_metadata_lineage(2)) == 2
+    f.core.shutdown()
+
+
+def test_fedstride_blocks_give_the_same_average():
+    f = Federation(rule="FedStride", stride=2, n=4, auto=False)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(4)]
+    f.core.wait_idle()
+    for lid, d in zip(ids, (1.0, 2.0, 3.0, 4.0)):
+        f.core.learner_completed_task(lid, f.tokens[lid], model_bytes([np.full(4, d, np.float32)]), 1, 1, 5, 10, 1, 1, b"")
+    f.core.wait_idle()
+    md = f.core.get_runtime_metadata_lineage(0)[0]
+    assert md["model_aggregation_block_size"] == [2.0, 2.0]
+    c, it, x = f.community()
+    assert c == 4 and it == 1
+    np.testing.assert_allclose(x, 2.5, rtol=1e-6)
+    f.core.shutdown()
+
+
+@pytest.mark.parametrize("rule", ["FedRec", "FedAsync"])
+def test_asynchronous_rules_fold_the_completing_learner(rule):
+    f = Federation(rule=rule, protocol=2, n=2, lineage=2, auto=False)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    a, b = f.join(0), f.join(1)
+    f.core.wait_idle()
+    assert sorted(r[0][0] for r in f.run_log) == sorted([a, b])
+    # b (lexicographically second) completes first: quirk Q2 would have folded `a` instead
+    f.core.learner_completed_task(b, f.tokens[b], model_bytes([np.full(4, 8.0, np.float32)]), 1, 1, 5, 10, 1, 1, b"")
+    f.core.wait_idle()
+    c, it, x = f.community()
+    if rule == "FedRec":
+        np.testing.assert_allclose(x, 8.0)
+    else:  # C = (1 - a) * 0 + a * 8 with a = 0.5 * s(staleness 0)
+        np.testing.assert_allclose(x, 4.0)
+    assert f.run_log[-1][0] == [b]          # asynchronous: only the caller is rescheduled
+    f.core.learner_completed_task(a, f.tokens[a], model_bytes([np.full(4, 2.0, np.float32)]), 1, 1, 5, 10, 1, 1, b"")
+    f.core.wait_idle()
+    c, it, x = f.community()
+    if rule == "FedRec":
+        np.testing.assert_allclose(x, 5.0)  # (100*8 + 100*2) / 200
+        f.core.learner_completed_task(b, f.tokens[b], model_bytes([np.full(4, 4.0, np.float32)]), 2, 1, 5, 10, 1, 1, b"")
+        f.core.wait_idle()
+        np.testing.assert_allclose(f.community()[2], 3.0)  # b's 8 swapped for 4: z stays 200
+    else:
+        s = _core.FedAsync.staleness(1, 1.0, 0.5, 4.0)  # a started from iteration 1, community is at 2
+        np.testing.assert_allclose(x, (1 - 0.5 * s) * 4.0 + 0.5 * s * 2.0, rtol=1e-6)
+    f.core.shutdown()
+
+
+def test_semi_synchronous_resizes_tasks_after_first_round():
+    f = Federation(protocol=3, n=2, semi_lambda=2)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(2)]
+    f.ms_per_batch = {ids[0]: 1.0, ids[1]: 4.0}   # ms/epoch = 10x: slowest epoch = 40 ms -> t_max = 80 ms
+    f.wait_rounds(1)
+    f.mute.update(ids)
+    time.sleep(0.1)
+    f.core.wait_idle()
+    round2 = [r for r in f.run_log if r[1] == 2][0]
+    assert dict(zip(round2[0], round2[2])) == {ids[0]: 80, ids[1]: 20}
+    f.core.shutdown()
+
+
+def test_dead_learner_is_evicted_and_the_round_completes():
+    f = Federation(n=2, deadline=0.3)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(2)]
+    f.mute.add(ids[1])  # never answers (reference quirk Q9: the round would hang forever)
+    f.delta[ids[0]] = 1.0
+    f.wait_rounds(2, timeout=10)
+    assert [l["id"] for l in f.core.get_learners()] == [ids[0]]
+    f.core.shutdown()
+
+
+def test_clean_leave_shrinks_the_barrier():
+    f = Federation(n=2, auto=False)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    a, b = f.join(0), f.join(1)
+    f.core.wait_idle()
+    f.core.learner_completed_task(a, f.tokens[a], model_bytes([np.ones(4, np.float32)]), 1, 1, 5, 10, 1, 1, b"")
+    f.core.wait_idle()
+    assert f.core.global_iteration() == 1
+    f.core.remove_learner(b, f.tokens[b])
+    f.core.wait_idle()
+    time.sleep(0.05)
+    f.core.wait_idle()
+    assert f.core.global_iteration() == 2
+    f.core.shutdown()

@@ -1,0 +1,176 @@
+"""End-to-end plumbing on CPU: BASELINE.json config #1 (FashionMNIST-shaped MLP, 2 learners,
+synchronous FedAvg) through DriverSession -> controller gRPC -> learners; YAML parsing; the engine
+on the gloo backend with world size 2."""
+import copy
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import yaml
+
+from metisfl_b200.driver.driver_session import DriverSession
+from metisfl_b200.models.model_dataset import ModelDatasetClassification
+from metisfl_b200.models.zoo import FashionMnistMLP
+from metisfl_b200.utils.fedenv_parser import FederationEnvironment
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ENV = os.path.join(ROOT, "examples", "config", "fashionmnist_2learners_sync_fedavg.yaml")
+
+
+def _free_ports(n):
+    socks = [socket.socket() for _ in range(n)]
+    for s in socks:
+        s.bind(("127.0.0.1", 0))
+    ports = [s.getsockname()[1] for s in socks]
+    for s in socks:
+        s.close()
+    return ports
+
+
+def _env(**over):
+    with open(ENV) as f:
+        d = yaml.safe_load(f)
+    fe = d["FederationEnvironment"]
+    ports = _free_ports(1 + len(fe["Learners"]))
+    fe["Controller"]["GRPCServicer"]["Port"] = ports[0]
+    for l, p in zip(fe["Learners"], ports[1:]):
+        l["GRPCServicer"]["Port"] = p
+    for k, v in over.items():
+        node = fe
+        *path, last = k.split(".")
+        for part in path:
+            node = node[part]
+        node[last] = v
+    return d
+
+
+def _recipe(n, seed):
+    def recipe():
+        rng = np.random.default_rng(seed)
+        y = rng.integers(0, 10, size=n)
+        x = rng.normal(size=(n, 1, 28, 28)).astype(np.float32) + (y[:, None, None, None] / 4.0).astype(np.float32)
+        return ModelDatasetClassification(x=x, y=y.astype(np.int64), size=n,
+                                          examples_per_class={int(c): int((y == c).sum()) for c in range(10)})
+    return recipe
+
+
+def test_fedenv_parser_reads_the_reference_schema():
+    env = FederationEnvironment(ENV)
+    assert env.communication_protocol.is_synchronous and not env.communication_protocol.enable_ssl
+    assert env.termination_signals.federation_rounds == 3
+    assert env.global_model_config.aggregation_rule.aggregation_rule_name == "FedAvg"
+    assert env.global_model_config.aggregation_rule.aggregation_rule_scaling_factor == "NumTrainingExamples"
+    assert env.local_model_config.optimizer_config.optimizer_pb_kwargs == {
+        "learning_rate": 0.05, "name": "VanillaSGD", "l2_reg": 0.0}
+    assert env.model_store_config.name == "InMemory" and env.model_store_config.eviction_lineage_length == 1
+    assert len(env.learners) == 2 and env.learners[0].grpc_servicer.port == 50152
+    d = _env()
+    d["FederationEnvironment"]["HomomorphicEncryption"] = {"Scheme": "CKKS", "BatchSize": 4096, "ScalingFactorBits": 52}
+    with pytest.raises(AssertionError):  # HE requires the PWA rule (fedenv_parser.py:302-309)
+        FederationEnvironment(d)
+    d["FederationEnvironment"]["GlobalModelConfig"]["AggregationRule"]["Name"] = "PWA"
+    assert FederationEnvironment(d).homomorphic_encryption.batch_size == 4096
+
+
+def _check_statistics(stats, n_learners=2, min_rounds=3):
+    assert set(stats) == {"learners_descriptor", "learners_models_results", "federation_runtime_metadata",
+                          "community_model_results"}
+    rounds = stats["federation_runtime_metadata"]["metadata"]
+    assert len(rounds) >= min_rounds
+    assert len(rounds[0]["completed_by_learner_id"]) == n_learners
+    assert len(stats["learners_descriptor"]["learner"]) == n_learners
+    evals = stats["community_model_results"]["community_evaluation"]
+    assert len(evals) >= min_rounds - 1 and len(evals[0]["evaluations"]) == n_learners
+    first = list(evals[0]["evaluations"].values())[0]
+    assert "accuracy" in first["test_evaluation"]["metric_values"]
+    tasks = list(stats["learners_models_results"]["learner_task"].values())[0]["task_metadata"]
+    assert tasks[0]["completed_batches"] > 0 and tasks[0]["processing_ms_per_batch"] > 0
+
+
+def test_config1_inprocess(tmp_path):
+    s = DriverSession(FederationEnvironment(_env()), FashionMnistMLP(), _recipe(320, 1), _recipe(64, 2),
+                      _recipe(64, 3), working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    stats = s.run(request_every_secs=0.5)
+    _check_statistics(stats)
+    losses = [float(list(e["evaluations"].values())[0]["test_evaluation"]["metric_values"]["loss"])
+              for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
+    assert losses[-1] < losses[0]  # the federation actually learns
+
+
+@pytest.mark.parametrize("rule,protocol", [("FedRec", "Asynchronous"), ("FedAsync", "Asynchronous"),
+                                           ("FedStride", "SEMI_SYNCHRONOUS")])
+def test_other_protocols_inprocess(tmp_path, rule, protocol):
+    over = {"GlobalModelConfig.AggregationRule.Name": rule, "CommunicationProtocol.Name": protocol,
+            "ModelStoreConfig.LineageLength": 2}
+    d = _env(**over)
+    if protocol == "SEMI_SYNCHRONOUS":
+        d["FederationEnvironment"]["CommunicationProtocol"]["Specifications"] = {
+            "SemiSynchronousLambda": 1, "SemiSynchronousRecomputeSteps": True}
+        d["FederationEnvironment"]["GlobalModelConfig"]["AggregationRule"]["RuleSpecifications"]["StrideLength"] = 1
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(160, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    stats = s.run(request_every_secs=0.5)
+    assert len(stats["federation_runtime_metadata"]["metadata"]) >= 3
+    assert stats["community_model_results"]["community_evaluation"]
+
+
+def test_config1_secure_aggregation_inprocess(tmp_path):
+    """PWA + CKKS end to end: encrypted initial model, learners decrypt / train / re-encrypt."""
+    d = _env(**{"GlobalModelConfig.AggregationRule.Name": "PWA", "TerminationSignals.FederationRounds": 2,
+                "LocalModelConfig.OptimizerConfig.LearningRate": 0.0005})
+    d["FederationEnvironment"]["HomomorphicEncryption"] = {"Scheme": "CKKS", "BatchSize": 4096, "ScalingFactorBits": 52}
+    model = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 10))
+    s = DriverSession(FederationEnvironment(d), model, _recipe(96, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    stats = s.run(request_every_secs=0.5)
+    assert len(stats["federation_runtime_metadata"]["metadata"]) >= 2
+    ev = [e for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
+    loss = float(list(ev[-1]["evaluations"].values())[0]["test_evaluation"]["metric_values"]["loss"])
+    assert np.isfinite(loss) and loss < 5.0
+
+
+def test_config1_local_subprocess_launcher(tmp_path):
+    """Controller and learners as real child processes (`python -m metisfl_b200.controller|learner`)."""
+    s = DriverSession(FederationEnvironment(_env()), FashionMnistMLP(), _recipe(160, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / "w"), launcher="local", banner=False)
+    stats = s.run(request_every_secs=1)
+    _check_statistics(stats)
+
+
+_GLOO_WORKER = r"""
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, {root!r})
+from metisfl_b200.parallel.engine import EngineConfig, FederationEngine
+from metisfl_b200.models.zoo import FashionMnistMLP
+from metisfl_b200.ops.optim import OptimHyper
+dist.init_process_group("gloo")
+rank = dist.get_rank()
+cfg = EngineConfig(learners_per_gpu=2, model_dtype=torch.float32, optimizer=OptimHyper("VanillaSGD", lr=0.1))
+eng = FederationEngine(FashionMnistMLP, cfg, device="cpu", examples_per_learner=[100, 200, 300, 400])
+g = torch.Generator().manual_seed(rank)
+data = [[(torch.randn(16, 1, 28, 28, generator=g), torch.randint(0, 10, (16,), generator=g)) for _ in range(2)] for _ in range(2)]
+for r in range(2):
+    out = eng.run_round(data)
+sd = eng.community_state_dict()
+flat = torch.cat([v.float().flatten() for v in sd.values()])
+gathered = [torch.empty_like(flat) for _ in range(2)]
+dist.all_gather(gathered, flat)
+assert torch.equal(gathered[0], gathered[1]), "ranks disagree on the community model"
+if rank == 0:
+    print("GLOO_OK", float(flat.abs().sum()), out["loss"])
+dist.destroy_process_group()
+"""
+
+
+def test_engine_world_size_2_gloo(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER.format(root=ROOT))
+    port = _free_ports(1)[0]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                       capture_output=True, text=True, timeout=300)
+    assert "GLOO_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
