@@ -1,0 +1,89 @@
+"""Fused cross-GPU aggregation (K1 over NVLink peer memory) at world size 2/4/8: every rank must end
+with the same community model, equal to the CPU oracle's weighted average of all learners' slots
+(SURVEY §4.4 item 7).  Skipped when fewer GPUs are visible."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r"""
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, {root!r})
+rank = int(os.environ["RANK"]); lr = int(os.environ["LOCAL_RANK"]); world = int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(lr)
+dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+from metisfl_b200.parallel.engine import EngineConfig, FederationEngine
+from metisfl_b200.models.zoo import ResNet18
+from metisfl_b200.ops import aggregation as agg
+k = {k}
+ex = [100 * (i + 1) for i in range(world * k)]
+eng = FederationEngine(ResNet18, EngineConfig(learners_per_gpu=k, use_cuda_graph=False), device=f"cuda:{{lr}}",
+                       examples_per_learner=ex)
+g = torch.Generator().manual_seed(100 + rank)
+for j in range(k):
+    for si, s in enumerate(eng.layout.segments):
+        v = eng.slot_views[j][si]
+        if s.dtype.is_floating_point:
+            v.copy_(torch.randn(v.numel(), generator=g).to(s.dtype))
+        else:
+            v.copy_(torch.randint(0, 50, (v.numel(),), generator=g).to(s.dtype))
+torch.cuda.synchronize(); dist.barrier()
+for it in range(3):          # back-to-back launches reuse the self-resetting signal pads
+    eng.aggregate_sync()
+torch.cuda.synchronize(); dist.barrier()
+# oracle: gather all slots to every rank through NCCL and average on the CPU
+nb = eng.layout.total_bytes
+allslots = [torch.empty_like(eng.slots.local) for _ in range(world)]
+dist.all_gather(allslots, eng.slots.local)
+w = [e / sum(ex) for e in ex]
+ok = True
+for si, s in enumerate(eng.layout.segments):
+    srcs = []
+    for i in range(world * k):
+        r, j = divmod(i, k)
+        buf = allslots[r][j * nb:(j + 1) * nb]
+        srcs.append(buf[s.byte_offset:s.byte_offset + s.nbytes].view(s.dtype).cpu())
+    ref = agg.weighted_sum(srcs, w, exact=s.exact)
+    got = eng.community_views[si].cpu()
+    if s.exact:
+        ok &= bool(torch.equal(got, ref))
+    else:
+        ok &= bool(torch.allclose(got.float(), ref.float(), atol=2e-2, rtol=2e-2))
+if eng.direct_install:
+    ok &= bool(torch.allclose(eng.arena.master[0].cpu(), eng.community_views[0].cpu().float()))
+t = torch.tensor([1.0 if ok else 0.0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
+# one real round as well: train + publish + fused aggregation
+data = [[(torch.randn(32, 3, 32, 32), torch.randint(0, 10, (32,))) for _ in range(2)] for _ in range(k)]
+out = eng.run_round(data)
+flat = eng.community.local[:nb].clone()
+gathered = [torch.empty_like(flat) for _ in range(world)]
+dist.all_gather(gathered, flat)
+same = all(torch.equal(gathered[0], x) for x in gathered)
+if rank == 0:
+    print("MULTIGPU_OK" if (t.item() == 1.0 and same) else f"MULTIGPU_BAD agg={{t.item()}} same={{same}}", out["loss"])
+eng.close()
+dist.destroy_process_group()
+"""
+
+
+def _run(world, k, tmp_path):
+    script = tmp_path / f"worker_{world}_{k}.py"
+    script.write_text(WORKER.format(root=ROOT, k=k))
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                       capture_output=True, text=True, timeout=420)
+    assert "MULTIGPU_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.parametrize("world,k", [(2, 1), (2, 2), (4, 1), (8, 1)])
+def test_fused_aggregation_across_gpus(world, k, tmp_path):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    _run(world, k, tmp_path)
