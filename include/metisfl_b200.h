@@ -135,6 +135,52 @@ int mfl_fabric_enable_peers(int device, int world);
 /* cross-GPU barrier as its own launch (K13); same signal pads as the fused kernels */
 int mfl_fabric_barrier(uint32_t* const* signal_pads, int rank, int world, int channel, void* stream);
 
+/* ---- K5-K9: RNS-CKKS on the GPU (csrc/ckks/ckks_kernels.cu) ----------------------------------
+ * Behavioural spec: encryption/palisade/ckks_scheme.cc:110-252 (Encrypt / ComputeWeightedAverage /
+ * Decrypt) with the ciphertext layout of csrc/ckks/ckks_common.h: [ct][poly 0..1][limb][N] uint64 in
+ * evaluation (NTT) form.  All table pointers are DEVICE pointers prepared once per crypto context
+ * (metisfl_b200/ops/ckks.py); polynomials of one limb (N = 16384 x 8 B = 128 KB) are transformed
+ * entirely in shared memory, one CTA per row. */
+typedef struct {
+  uint64_t q[4], n_inv[4], n_inv_shoup[4];
+  const uint64_t* psi[4];         /* bit-reversed powers of the 2N-th root, per limb */
+  const uint64_t* psi_shoup[4];
+  const uint64_t* ipsi[4];
+  const uint64_t* ipsi_shoup[4];
+  int32_t log_n, n_limbs;
+} mfl_ckks_ctx;
+
+/* K5: in-place negacyclic NTT / inverse NTT of n_rows rows; row r uses limb (r % n_limbs). */
+int mfl_ckks_ntt(const mfl_ckks_ctx* ctx, uint64_t* rows, size_t n_rows, int inverse, void* stream);
+/* K6: canonical-embedding encode: values -> rounded scaled coefficients, coeffs[ct][2*slots]
+ * (re parts then im parts; coefficient i*gap and i*gap + N/2 of the plaintext polynomial). */
+int mfl_ckks_encode(const mfl_ckks_ctx* ctx, const double* values, size_t n_values, uint32_t slots, double scale,
+                    const double* ksi_pows /* (2N+1) x {cos,sin} */, const uint32_t* rot_group, double* coeffs,
+                    void* stream);
+/* K7: RLWE public-key encryption of encoded coefficients; pk = [2][limb][N] with Shoup companions. */
+int mfl_ckks_encrypt(const mfl_ckks_ctx* ctx, const double* coeffs, uint32_t n_ct, uint32_t slots,
+                     const uint64_t* pk, const uint64_t* pk_shoup, uint64_t seed, uint64_t* ct_out, void* stream);
+/* K7: c0 + c1*s per limb, inverse NTT -> residues[ct][limb][N] (coefficient form). */
+int mfl_ckks_decrypt(const mfl_ckks_ctx* ctx, const uint64_t* ct, uint32_t n_ct, const uint64_t* sk,
+                     const uint64_t* sk_shoup, uint64_t* residues, void* stream);
+/* K6: CRT (Garner) combine + canonical-embedding decode -> values. garner_inv[j*4+i] = q_j^-1 mod q_i. */
+int mfl_ckks_decode(const mfl_ckks_ctx* ctx, const uint64_t* residues, uint32_t n_ct, uint32_t slots,
+                    double inv_scale, const uint64_t* garner_inv /* host, 16 */, const double* ksi_pows,
+                    const uint32_t* rot_group, double* values, size_t n_values, void* stream);
+/* K8: out = sum_l ct_l (.) w_l mod q (limb-wise scalar multiply-add of whole ciphertext blobs).
+ * w[l*4+limb], w_shoup likewise (host arrays).  words = n_ct * 2 * n_limbs * N. */
+int mfl_ckks_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
+                          const uint64_t* w_shoup, int n_src, size_t words, uint64_t* out, void* stream);
+/* K8 fused over NVLink: rank r reduces shard r of the ciphertext words from every source (peer loads)
+ * and stores it into every rank's output (peer stores); same barrier protocol as mfl_fused_aggregate. */
+int mfl_ckks_fused_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
+                                const uint64_t* w_shoup, int n_src, size_t words, uint64_t* const* outs,
+                                uint32_t* const* signal_pads, int rank, int world, int n_blocks, void* stream);
+/* K9: rescale - drop the last limb: out_l = (c_l - [c_last]_{q_l}) * q_last^-1 mod q_l.
+ * qlast_inv / qlast_inv_shoup: host arrays per remaining limb. */
+int mfl_ckks_rescale(const mfl_ckks_ctx* ctx, const uint64_t* ct_in, uint32_t n_ct, const uint64_t* qlast_inv,
+                     const uint64_t* qlast_inv_shoup, uint64_t* ct_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
