@@ -57,7 +57,7 @@ def main():
         nbytes = n * 2
         slots = fab.alloc(nbytes * k)
         comm = fab.alloc(nbytes)
-        pads = fab.signal_pads(148)
+        pads = fab.signal_pads(296)
         slots.local.view(torch.bfloat16).copy_(torch.randn(n * k, device=dev).to(torch.bfloat16))
         L = world * k
         w = [1.0 / L] * L
@@ -66,7 +66,7 @@ def main():
         fab.host_barrier()
 
         def ours():
-            agg.fused_aggregate(srcs, w, comm.ptrs, pads.ptrs, rank, world, seg, n_blocks=148)
+            agg.fused_aggregate(srcs, w, comm.ptrs, pads.ptrs, rank, world, seg, n_blocks=296)
 
         flat = slots.local.view(torch.bfloat16)[:n].clone()
 

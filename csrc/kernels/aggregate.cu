@@ -84,7 +84,9 @@ template <int DT> __device__ __forceinline__ void fma_raw(const Raw<DT>& r, floa
 // acc[8] += sum_l w_l * src_l[unit u]; loads are batched kBatch deep for memory-level parallelism.
 template <int DT, bool PEER>
 __device__ __forceinline__ void reduce_unit(const AggArgs& a, size_t byte_off, size_t u, float* acc) {
-  constexpr int kBatch = (DT == MFL_FLOAT32) ? 4 : 8;
+  // the fused kernel runs 2 CTAs x 512 threads per SM under a 64-register cap: half the batch depth,
+  // twice the resident warps, same bytes in flight
+  constexpr int kBatch = (DT == MFL_FLOAT32) ? (PEER ? 2 : 4) : (PEER ? 4 : 8);
   int l = 0;
   for (; l + kBatch <= a.n; l += kBatch) {
     Raw<DT> r[kBatch];
@@ -229,7 +231,7 @@ __device__ __forceinline__ void fused_segment_fast(const FusedArgs& fa, const mf
 }
 
 template <typename T>
-__device__ __forceinline__ void fused_segment_exact(const FusedArgs& fa, const mfl_segment& sg) {
+__device__ __noinline__ void fused_segment_exact(const FusedArgs& fa, const mfl_segment& sg) {
   const size_t per = (sg.numel + fa.world - 1) / fa.world;
   const size_t begin = min((size_t)sg.numel, per * fa.rank), end = min((size_t)sg.numel, begin + per);
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -248,7 +250,7 @@ __device__ __forceinline__ void fused_segment_exact(const FusedArgs& fa, const m
   }
 }
 
-__global__ void __launch_bounds__(512, 1) fused_aggregate_kernel(const __grid_constant__ FusedArgs fa) {
+__global__ void __launch_bounds__(512, 2) fused_aggregate_kernel(const __grid_constant__ FusedArgs fa) {
   const int slot0 = (0 * gridDim.x + blockIdx.x) * MFL_MAX_PEERS;
   const int slot1 = (1 * gridDim.x + blockIdx.x) * MFL_MAX_PEERS;
   // Phase 0: every rank's slots are final (they were written by earlier work on each rank's stream).
@@ -381,8 +383,8 @@ extern "C" int mfl_fused_aggregate(const void* const* src_slots, const double* w
                                    int n_blocks, void* stream) {
   MFL_ARG(n_src >= 1 && n_src <= MFL_MAX_SRC, "fused_aggregate: n_src=%d outside [1,%d]", n_src, MFL_MAX_SRC);
   MFL_ARG(n_segments >= 1 && n_segments <= MFL_MAX_SEGMENTS, "fused_aggregate: n_segments=%d", n_segments);
-  MFL_ARG(n_blocks >= 1 && n_blocks <= sm_count(), "fused_aggregate: n_blocks=%d must be in [1, #SMs] "
-          "(blocks spin on their peers, so all of them must be co-resident)", n_blocks);
+  MFL_ARG(n_blocks >= 1 && n_blocks <= 2 * sm_count(), "fused_aggregate: n_blocks=%d must be in [1, 2 x #SMs] "
+          "(blocks spin on their peers, so all of them must be co-resident: 2 CTAs of 512 threads per SM)", n_blocks);
   FusedArgs local;
   if (int rc = fill_fused(local, signal_pads, rank, world)) return rc;
   local.agg.n = n_src;

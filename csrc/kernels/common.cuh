@@ -58,11 +58,13 @@ __device__ __forceinline__ uint4 ld_stream(const void* p) {
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
-// Coherent load (data written by a peer GPU during this kernel's lifetime or just before it):
-// relaxed.sys bypasses the non-coherent path.
+// Load of data that another GPU (or an earlier phase of this kernel on another GPU) wrote: a plain
+// weak load, ordered by the acquire side of the flag barrier that precedes it, bypassing L1
+// allocation.  (.nc would be wrong here - the data is not read-only for the kernel's lifetime - and a
+// .relaxed.sys load measured ~25% slower for no additional guarantee we need.)
 __device__ __forceinline__ uint4 ld_peer(const void* p) {
   uint4 v;
-  asm volatile("ld.global.relaxed.sys.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }

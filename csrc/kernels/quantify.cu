@@ -26,10 +26,42 @@ struct QPartial {          // one per CTA
   unsigned long long nz_head, nz_tail;
 };
 
+// non-zero lanes of one 16-byte vector holding elements of type U (sign bit masked for floats)
+template <typename U>
+__device__ __forceinline__ unsigned nz_in_vec(const uint4& v, U mask) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  unsigned c = 0;
+  if constexpr (sizeof(U) == 8) {
+    c += (((((unsigned long long)w[1] << 32) | w[0]) & mask) != 0);
+    c += (((((unsigned long long)w[3] << 32) | w[2]) & mask) != 0);
+  } else if constexpr (sizeof(U) == 4) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c += ((w[i] & mask) != 0);
+  } else if constexpr (sizeof(U) == 2) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) c += ((w[i] & mask) != 0) + (((w[i] >> 16) & mask) != 0);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) c += (((w[i] >> (8 * b)) & mask) != 0);
+  }
+  return c;
+}
+
+// CTA-wide count over [lo, hi): scalar head up to a 16-byte boundary, 16-byte vector body, scalar tail
 template <typename U>
 __device__ __forceinline__ unsigned count_nonzero(const U* p, size_t lo, size_t hi, U mask) {
+  constexpr size_t kPer = 16 / sizeof(U);
   unsigned c = 0;
-  for (size_t i = lo + threadIdx.x; i < hi; i += kQThreads) c += ((p[i] & mask) != 0);
+  const uintptr_t addr = reinterpret_cast<uintptr_t>(p + lo);
+  size_t head = ((16 - (addr & 15)) & 15) / sizeof(U);
+  if (head > hi - lo) head = hi - lo;
+  const size_t body_lo = lo + head, n_vec = (hi - body_lo) / kPer, tail_lo = body_lo + n_vec * kPer;
+  if (threadIdx.x < head) c += ((p[lo + threadIdx.x] & mask) != 0);
+  const uint4* v = reinterpret_cast<const uint4*>(p + body_lo);
+  for (size_t i = threadIdx.x; i < n_vec; i += kQThreads) c += nz_in_vec<U>(ld_stream(v + i), mask);
+  if (threadIdx.x < hi - tail_lo) c += ((p[tail_lo + threadIdx.x] & mask) != 0);
   return c;
 }
 
@@ -66,7 +98,7 @@ __global__ void __launch_bounds__(kQThreads) quantify_kernel(const U* data, U ma
       const size_t s = max(vs, lo), e = min(ve, hi);
       const unsigned long long nz = block_sum(count_nonzero(data, s, e, mask), red);
       if (vs >= lo && ve <= hi) {
-        if (threadIdx.x == 0) { counts[2 * v] = nz; counts[2 * v + 1] = (ve - vs) - nz; }
+        if (threadIdx.x == 0) counts[2 * v] = nz;  // zeros are derived by the fold kernel
       } else if (vs < lo) {
         part.var_head = v; part.nz_head = nz;
       } else {
@@ -80,29 +112,32 @@ __global__ void __launch_bounds__(kQThreads) quantify_kernel(const U* data, U ma
 // In-order fold of the per-CTA partials: partial pieces of one variable are adjacent in CTA order.
 __global__ void quantify_fold_kernel(const QPartial* partials, int n_blocks, const uint64_t* offsets, int n_vars,
                                      unsigned long long* counts) {
-  for (int v = threadIdx.x; v < n_vars; v += blockDim.x)
-    if (offsets[v + 1] == offsets[v]) { counts[2 * v] = 0; counts[2 * v + 1] = 0; }
-  if (threadIdx.x != 0) return;
-  long long cur = -1;
-  unsigned long long sum = 0;
-  auto flush = [&]() {
-    if (cur >= 0) {
-      counts[2 * cur] = sum;
-      counts[2 * cur + 1] = (offsets[cur + 1] - offsets[cur]) - sum;
+  __shared__ QPartial sp[kQBlocks];  // parallel load: a serial walk over global memory costs ~0.3 us per record
+  for (int b = threadIdx.x; b < n_blocks; b += blockDim.x) sp[b] = partials[b];
+  __syncthreads();
+  if (threadIdx.x == 0) {  // stores are fire-and-forget, so this scan never waits on global memory
+    long long cur = -1;
+    unsigned long long sum = 0;
+    for (int b = 0; b < n_blocks; ++b) {
+      const QPartial p = sp[b];
+      if (p.var_head >= 0) {
+        if (p.var_head != cur) { if (cur >= 0) counts[2 * cur] = sum; cur = p.var_head; sum = 0; }
+        sum += p.nz_head;
+      }
+      if (p.var_tail >= 0) {
+        if (p.var_tail != cur) { if (cur >= 0) counts[2 * cur] = sum; cur = p.var_tail; sum = 0; }
+        sum += p.nz_tail;
+      }
     }
-  };
-  for (int b = 0; b < n_blocks; ++b) {
-    const QPartial p = partials[b];
-    if (p.var_head >= 0) {
-      if (p.var_head != cur) { flush(); cur = p.var_head; sum = 0; }
-      sum += p.nz_head;
-    }
-    if (p.var_tail >= 0) {
-      if (p.var_tail != cur) { flush(); cur = p.var_tail; sum = 0; }
-      sum += p.nz_tail;
-    }
+    if (cur >= 0) counts[2 * cur] = sum;
   }
-  flush();
+  __syncthreads();
+  for (int v = threadIdx.x; v < n_vars; v += blockDim.x) {
+    const unsigned long long len = offsets[v + 1] - offsets[v];
+    const unsigned long long nz = len ? counts[2 * v] : 0ull;
+    counts[2 * v] = nz;
+    counts[2 * v + 1] = len - nz;
+  }
 }
 
 // Shared by the allocating and the caller-scratch entry points.
@@ -130,7 +165,7 @@ int quantify_launch(const void* data, int dtype, const uint64_t* offsets, int n_
     default: set_error("quantify: bad dtype %d", dtype); return -1;
   }
   if (int rc = check(cudaGetLastError(), "quantify_kernel launch")) return rc;
-  quantify_fold_kernel<<<1, 32, 0, st>>>(parts, blocks, offsets, n_vars, counts);
+  quantify_fold_kernel<<<1, 128, 0, st>>>(parts, blocks, offsets, n_vars, counts);
   return check(cudaGetLastError(), "quantify_fold_kernel launch");
 }
 

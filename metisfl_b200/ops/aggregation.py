@@ -151,4 +151,4 @@ def fused_aggregate(src_slot_ptrs: Sequence[int], weights: Sequence[float], out_
 
 
 def default_fused_blocks() -> int:
-    return 148
+    return 296

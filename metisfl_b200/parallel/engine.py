@@ -73,7 +73,7 @@ class EngineConfig:
     staleness_b: float = 4.0
     channels_last: bool = True
     use_cuda_graph: Optional[bool] = None
-    fused_blocks: int = 148
+    fused_blocks: int = 296
     seed: int = 1234
 
 

@@ -104,7 +104,7 @@ class Fabric:
         self.host_barrier()
         return SymmetricBuffer(local, ptrs, owner=self)
 
-    def signal_pads(self, n_blocks: int = 148) -> SymmetricBuffer:
+    def signal_pads(self, n_blocks: int = 296) -> SymmetricBuffer:
         if self._pads is None:
             nbytes = _lib.lib().mfl_signal_pad_bytes(n_blocks) if self.peer_mapped else 256
             self._pads = self.alloc(nbytes)
