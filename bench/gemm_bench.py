@@ -1,0 +1,53 @@
+#!/usr/bin/env python
+"""tcgen05 GEMM (K10) vs cuBLAS (torch.matmul) on the Linear shapes of GPT-2 medium and the MLP.
+CUDA-event timing after warm-up, L2 flushed between iterations; reports TFLOP/s and the fraction of
+the measured cuBLAS bf16 peak in MEASURED_PEAKS.json."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from metisfl_b200.ops import gemm  # noqa: E402
+
+
+def timeit(fn, iters=20, warmup=5):
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        flush.fill_(0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / iters
+
+
+def main():
+    peak = 1642.2
+    try:
+        peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                           "MEASURED_PEAKS.json")))["bf16_tflops"]
+    except Exception:
+        pass
+    shapes = [(8192, 3072, 1024), (8192, 1024, 1024), (8192, 4096, 1024), (8192, 1024, 4096), (8192, 8192, 8192),
+              (4096, 128, 784), (4096, 128, 128)]
+    rows = []
+    for m, n, k in shapes:
+        a = torch.randn(m, k, device="cuda").to(torch.bfloat16)
+        b = torch.randn(n, k, device="cuda").to(torch.bfloat16)
+        out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+        t_ours = timeit(lambda: gemm.gemm_nt(a, b, out=out))
+        t_cublas = timeit(lambda: torch.matmul(a, b.t(), out=out))
+        fl = 2.0 * m * n * k
+        rows.append({"m": m, "n": n, "k": k, "ours_ms": t_ours, "cublas_ms": t_cublas,
+                     "ours_tflops": fl / t_ours / 1e9, "cublas_tflops": fl / t_cublas / 1e9,
+                     "ours_fraction_of_measured_peak": fl / t_ours / 1e9 / peak})
+    print(json.dumps({"bench": "gemm_bench", "measured_bf16_peak_tflops": peak, "results": rows}))
+
+
+if __name__ == "__main__":
+    main()

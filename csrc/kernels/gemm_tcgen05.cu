@@ -1,0 +1,288 @@
+// K10: bf16 GEMM on 5th-generation tensor cores (tcgen05 + TMEM), operands fed by TMA.
+//
+//   C[M,N] = act( A[M,K] . B[N,K]^T + bias[N] )      A, B K-major bf16, fp32 accumulation in TMEM
+//
+// This is the matmul under the learners' Linear layers (y = x W^T + b): the reference delegates it
+// to TensorFlow / user PyTorch code (keras_model_ops.py:156, examples/pytorch/models/mlp.py:49-68).
+//
+// Structure (one CTA = one 128 x BN output tile, 256 threads, 1 CTA / SM):
+//   warp 0, one lane : TMA producer - cp.async.bulk.tensor 128x64 (A) and BNx64 (B) bf16 boxes with
+//                      128-byte swizzle into a kStages-deep shared-memory ring, mbarrier expect_tx
+//   warp 1, one lane : MMA issuer  - 4 x tcgen05.mma (M128, N=BN, K16) per stage, accumulator in TMEM;
+//                      tcgen05.commit releases the stage / signals the epilogue
+//   warp 2           : TMEM allocator (BN fp32 columns) and deallocator
+//   warps 4-7        : epilogue - tcgen05.ld 32 lanes x 32 columns per warp, bias + activation in
+//                      registers, bf16 / fp32 store
+// Shared-memory operand layout = what TMA's SWIZZLE_128B writes = the canonical K-major SW128 UMMA
+// layout (rows of 128 B, 8-row groups 1024 B apart), so the smem descriptors are just
+// {start, LBO=1, SBO=1024 B, version 1, layout SWIZZLE_128B} and a K step of 16 elements advances the
+// start address by 32 bytes.
+#include <cuda.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace mfl {
+namespace gemm {
+
+constexpr int kBlockM = 128, kBlockN = 128, kBlockK = 64, kUmmaK = 16;
+constexpr int kStages = 6;
+constexpr int kThreads = 256;
+constexpr uint32_t kABytes = kBlockM * kBlockK * 2, kBBytes = kBlockN * kBlockK * 2;
+constexpr uint32_t kStageBytes = kABytes + kBBytes;
+constexpr uint32_t kTmemCols = kBlockN;  // fp32 accumulator: one column per output column
+constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + 256 /*barriers*/;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "LAB_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra DONE;\n\t"
+      "bra LAB_WAIT;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// K-major, 128-byte swizzled operand tile starting at `smem_addr` (1024-byte aligned ring slot)
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);        // start address
+  d |= (uint64_t)1 << 16;                            // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset: 8 rows x 128 B
+  d |= (uint64_t)1 << 46;                            // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                            // layout type SWIZZLE_128B
+  return d;
+}
+// kind::f16, A = B = bf16, D = fp32, both K-major, M = 128, N = kBlockN
+__device__ __forceinline__ uint32_t make_idesc() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBlockN >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct Epilogue {
+  void* c;
+  const void* bias;   // bf16 or fp32 [N], may be null
+  int64_t ldc;
+  int32_t M, N, K;
+  int32_t c_fp32;     // output dtype: 0 bf16, 1 fp32
+  int32_t bias_fp32;
+  int32_t act;        // 0 none, 1 relu, 2 gelu(tanh)
+};
+
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == 1) return fmaxf(x, 0.f);
+  if (act == 2) {
+    const float u = 0.7978845608f * (x + 0.044715f * x * x * x);
+    return 0.5f * x * (1.f + tanhf(u));
+  }
+  return x;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const __grid_constant__ Epilogue ep) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)kStages * kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full_bar = empty_bar + kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * kBlockM, n0 = blockIdx.x * kBlockN;
+  const int num_kb = (ep.K + kBlockK - 1) / kBlockK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  } else if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % kStages;
+        const uint32_t phase = (kb / kStages) & 1;
+        mbar_wait(empty_bar + s, phase ^ 1);
+        mbar_expect_tx(full_bar + s, kStageBytes);
+        uint8_t* a_dst = smem + (size_t)s * kStageBytes;
+        tma_load_2d(a_dst, &tmap_a, full_bar + s, kb * kBlockK, m0);
+        tma_load_2d(a_dst + kABytes, &tmap_b, full_bar + s, kb * kBlockK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      const uint32_t idesc = make_idesc();
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % kStages;
+        const uint32_t phase = (kb / kStages) & 1;
+        mbar_wait(full_bar + s, phase);
+        tcgen05_fence_after();
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * kStageBytes);
+        const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + kABytes);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
+          umma_f16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+        }
+        umma_commit(empty_bar + s);  // frees the smem slot once these MMAs have read it
+      }
+      umma_commit(tmem_full_bar);    // accumulator complete
+    }
+  } else if (warp >= 4) {  // ===== epilogue: TMEM -> registers -> global =====
+    mbar_wait(tmem_full_bar, 0);
+    tcgen05_fence_after();
+    const int wq = warp & 3;                       // TMEM lane quarter this warp may access
+    const int row = m0 + wq * 32 + lane;
+    const bool row_ok = row < ep.M;
+#pragma unroll 1
+    for (int c = 0; c < kBlockN; c += 32) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)c, r);
+      if (n0 + c >= ep.N) continue;               // warp-uniform
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = n0 + c + j;
+        float b = 0.f;
+        if (ep.bias && col < ep.N)
+          b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
+                           : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+        v[j] = apply_act(__uint_as_float(r[j]) + b, ep.act);
+      }
+      if (!row_ok) continue;
+      const bool full = (n0 + c + 32 <= ep.N);
+      if (ep.c_fp32) {
+        float* out = reinterpret_cast<float*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
+        if (full && (ep.ldc % 4 == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+          for (int j = 0; j < 32 && n0 + c + j < ep.N; ++j) out[j] = v[j];
+        }
+      } else {
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
+        if (full && (ep.ldc % 8 == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(out + j) = VecTraits<MFL_BFLOAT16>::pack(v + j);
+        } else {
+          for (int j = 0; j < 32 && n0 + c + j < ep.N; ++j) out[j] = __float2bfloat16_rn(v[j]);
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+
+// ---- host side: tensor maps through the driver entry point (no link-time dependency on libcuda) ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+static int make_map(CUtensorMap* map, const void* base, int rows, int k, int64_t ld, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  MFL_ARG(fn != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {(cuuint64_t)k, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MFL_ARG(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed with CUresult %d (rows=%d k=%d ld=%lld)", (int)r, rows, k,
+          (long long)ld);
+  return 0;
+}
+
+}  // namespace gemm
+}  // namespace mfl
+
+using namespace mfl;
+
+extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
+                             const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream) {
+  using namespace mfl::gemm;
+  MFL_ARG(a && b && c && m > 0 && n > 0 && k > 0, "gemm: null operand or empty shape");
+  MFL_ARG(c_dtype == MFL_BFLOAT16 || c_dtype == MFL_FLOAT32, "gemm: output must be BFLOAT16 or FLOAT32");
+  MFL_ARG(!bias || bias_dtype == MFL_BFLOAT16 || bias_dtype == MFL_FLOAT32, "gemm: bias must be BFLOAT16 or FLOAT32");
+  MFL_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0,
+          "gemm: A and B need 16-byte aligned bases and row pitches that are multiples of 8 elements (TMA)");
+  MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
+  CUtensorMap ta, tb;
+  if (int rc = make_map(&ta, a, m, k, lda, kBlockM)) return rc;
+  if (int rc = make_map(&tb, b, n, k, ldb, kBlockN)) return rc;
+  Epilogue ep{c, bias, ldc, m, n, k, c_dtype == MFL_FLOAT32, bias_dtype == MFL_FLOAT32, act};
+  MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+  dim3 grid((n + kBlockN - 1) / kBlockN, (m + kBlockM - 1) / kBlockM);
+  gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(ta, tb, ep);
+  return check(cudaGetLastError(), "gemm_bf16_tcgen05_kernel launch");
+}

@@ -135,6 +135,13 @@ int mfl_fabric_enable_peers(int device, int world);
 /* cross-GPU barrier as its own launch (K13); same signal pads as the fused kernels */
 int mfl_fabric_barrier(uint32_t* const* signal_pads, int rank, int world, int channel, void* stream);
 
+/* ---- K10: bf16 GEMM on tcgen05 tensor cores, TMEM accumulator, TMA-fed (csrc/kernels/gemm_tcgen05.cu)
+ * C[m,n] = act(A[m,k] . B[n,k]^T + bias[n]); A and B are K-major (row-major with k contiguous) bf16,
+ * lda/ldb/ldc in elements (lda, ldb multiples of 8); C is bf16 or fp32; act: 0 none, 1 ReLU, 2 GELU(tanh).
+ * Replaces the framework matmul under the learners' Linear layers (keras_model_ops.py:156). */
+int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
+                  const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream);
+
 /* ---- K5-K9: RNS-CKKS on the GPU (csrc/ckks/ckks_kernels.cu) ----------------------------------
  * Behavioural spec: encryption/palisade/ckks_scheme.cc:110-252 (Encrypt / ComputeWeightedAverage /
  * Decrypt) with the ciphertext layout of csrc/ckks/ckks_common.h: [ct][poly 0..1][limb][N] uint64 in

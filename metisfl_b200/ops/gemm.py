@@ -1,0 +1,113 @@
+"""Front-end of the tcgen05 GEMM (K10, ``csrc/kernels/gemm_tcgen05.cu``) and an autograd-aware
+``linear`` built on it.
+
+``y = act(x @ W^T + b)`` runs as ONE kernel (bias and activation fused in the TMEM epilogue).  The
+backward pass reuses the same K-major kernel: ``dX = dY @ W`` is fed ``W^T`` made contiguous, and
+``dW = dY^T @ X`` is fed the two transposes - a stop-gap until MN-major operand descriptors land.
+Reference counterpart: the framework matmuls under ``model.fit`` (``keras_model_ops.py:156``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from metisfl_b200.ops import _lib
+
+ACTS = {None: 0, "none": 0, "relu": 1, "gelu": 2, "gelu_tanh": 2}
+_BOUND = False
+
+
+def _bind():
+    global _BOUND
+    L = _lib.lib()
+    if not _BOUND:
+        vp, i, i64 = C.c_void_p, C.c_int, C.c_int64
+        L.mfl_gemm_bf16.argtypes = [vp, i, i64, vp, i64, vp, i64, vp, i, i, i, i, i, vp]
+        _BOUND = True
+    return L
+
+
+def supported(x: torch.Tensor, w: torch.Tensor) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0
+            and _lib.available())
+
+
+def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
+            out_dtype: torch.dtype = torch.bfloat16, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``act(a @ b.T + bias)`` for 2-D bf16 ``a [M,K]`` and ``b [N,K]`` (K contiguous in both)."""
+    assert a.dim() == 2 and b.dim() == 2 and a.shape[1] == b.shape[1], (a.shape, b.shape)
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    if a.stride(1) != 1 or a.stride(0) % 8 or a.data_ptr() % 16:
+        a = a.contiguous()
+    if b.stride(1) != 1 or b.stride(0) % 8 or b.data_ptr() % 16:
+        b = b.contiguous()
+    m, k = a.shape
+    n = b.shape[0]
+    if out is None:
+        out = torch.empty(m, n, dtype=out_dtype, device=a.device)
+    if bias is not None:
+        assert bias.numel() == n and bias.dtype in (torch.bfloat16, torch.float32) and bias.is_contiguous()
+    rc = _bind().mfl_gemm_bf16(out.data_ptr(), _lib.wire(out), out.stride(0), a.data_ptr(), a.stride(0), b.data_ptr(),
+                               b.stride(0), _lib.ptr(bias), _lib.wire(bias) if bias is not None else 0, m, n, k,
+                               ACTS[act], _lib.stream_ptr())
+    _lib.check(rc, "mfl_gemm_bf16")
+    return out
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        x2 = x.reshape(-1, x.shape[-1])
+        y = gemm_nt(x2, w, bias)
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias = bias is not None
+        ctx.bias_dtype = bias.dtype if bias is not None else None
+        ctx.x_shape = x.shape
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, gy):
+        x2, w = ctx.saved_tensors
+        g2 = gy.reshape(-1, gy.shape[-1])
+        if g2.dtype != torch.bfloat16:
+            g2 = g2.to(torch.bfloat16)
+        gx = gw = gb = None
+        n, k = w.shape
+        if ctx.needs_input_grad[0]:
+            if n % 8 == 0:
+                gx = gemm_nt(g2, w.t().contiguous()).view(ctx.x_shape)      # [M,N] x [K,N]^T
+            else:
+                gx = (g2 @ w).view(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            m = g2.shape[0]
+            if m % 8 == 0:
+                gw = gemm_nt(g2.t().contiguous(), x2.t().contiguous())      # [N,M] x [K,M]^T
+            else:
+                gw = g2.t() @ x2
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g2.float().sum(0).to(ctx.bias_dtype)
+        return gx, gw, gb
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Drop-in for ``F.linear`` that uses the tcgen05 kernel when the operands allow it."""
+    if supported(x, w):
+        return _LinearFn.apply(x, w, bias)
+    return F.linear(x, w, bias)
+
+
+class B200Linear(nn.Linear):
+    def forward(self, x):
+        return linear(x, self.weight, self.bias)
+
+
+def use_b200_linear(module: nn.Module) -> nn.Module:
+    """Re-class every ``nn.Linear`` in ``module`` so its forward/backward run on the tcgen05 kernel."""
+    for m in module.modules():
+        if type(m) is nn.Linear:
+            m.__class__ = B200Linear
+    return module
