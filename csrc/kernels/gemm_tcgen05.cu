@@ -5,7 +5,7 @@
 // This is the matmul under the learners' Linear layers (y = x W^T + b): the reference delegates it
 // to TensorFlow / user PyTorch code (keras_model_ops.py:156, examples/pytorch/models/mlp.py:49-68).
 //
-// Structure (one CTA = one 128 x BN output tile, 256 threads, 1 CTA / SM):
+// Structure (persistent: one CTA per SM walks 128 x BN output tiles, 256 threads):
 //   warp 0, one lane : TMA producer - cp.async.bulk.tensor 128x64 (A) and BNx64 (B) bf16 boxes with
 //                      128-byte swizzle into a kStages-deep shared-memory ring, mbarrier expect_tx
 //   warp 1, one lane : MMA issuer  - 4 x tcgen05.mma (M128, N=BN, K16) per stage, accumulator in TMEM;
@@ -13,6 +13,9 @@
 //   warp 2           : TMEM allocator (BN fp32 columns) and deallocator
 //   warps 4-7        : epilogue - tcgen05.ld 32 lanes x 32 columns per warp, bias + activation in
 //                      registers, bf16 / fp32 store
+// The accumulator is double-buffered in TMEM (2 x BN columns, tmem_full / tmem_empty mbarriers), so the
+// epilogue of tile i overlaps the TMA + MMA main loop of tile i+1; the smem ring runs continuously
+// across tiles.
 // Shared-memory operand layout = what TMA's SWIZZLE_128B writes = the canonical K-major SW128 UMMA
 // layout (rows of 128 B, 8-row groups 1024 B apart), so the smem descriptors are just
 // {start, LBO=1, SBO=1024 B, version 1, layout SWIZZLE_128B} and a K step of 16 elements advances the
@@ -26,13 +29,17 @@
 namespace mfl {
 namespace gemm {
 
-constexpr int kBlockM = 128, kBlockN = 128, kBlockK = 64, kUmmaK = 16;
-constexpr int kStages = 6;
+constexpr int kBlockM = 128, kBlockK = 64, kUmmaK = 16;
 constexpr int kThreads = 256;
-constexpr uint32_t kABytes = kBlockM * kBlockK * 2, kBBytes = kBlockN * kBlockK * 2;
-constexpr uint32_t kStageBytes = kABytes + kBBytes;
-constexpr uint32_t kTmemCols = kBlockN;  // fp32 accumulator: one column per output column
-constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + 256 /*barriers*/;
+constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
+
+template <int BN> struct Cfg {
+  static constexpr int kStages = BN == 256 ? 4 : 6;
+  static constexpr uint32_t kBBytes = BN * kBlockK * 2;
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr uint32_t kTmemCols = 2 * BN;  // two fp32 accumulators of BN columns
+  static constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + 256 /*barriers*/;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -71,9 +78,12 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                            // layout type SWIZZLE_128B
   return d;
 }
-// kind::f16, A = B = bf16, D = fp32, both K-major, M = 128, N = kBlockN
-__device__ __forceinline__ uint32_t make_idesc() {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kBlockN >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+// kind::f16, A = B = bf16, D = fp32, both K-major, M = 128, N = BN
+template <int BN> __device__ __forceinline__ uint32_t make_idesc() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
@@ -118,18 +128,23 @@ __device__ __forceinline__ float apply_act(float x, int act) {
   return x;
 }
 
+template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                          const __grid_constant__ Epilogue ep) {
+  using C = Cfg<BN>;
+  constexpr int kStages = C::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)kStages * kStageBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)kStages * C::kStageBytes);
   uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tmem_full_bar = empty_bar + kStages;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + kStages;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;    // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * kBlockM, n0 = blockIdx.x * kBlockN;
+  const int tiles_n = (ep.N + BN - 1) / BN, tiles_m = (ep.M + kBlockM - 1) / kBlockM;
+  const int num_tiles = tiles_m * tiles_n;
   const int num_kb = (ep.K + kBlockK - 1) / kBlockK;
 
   if (warp == 0 && lane == 0) {
@@ -139,10 +154,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       mbar_init(full_bar + s, 1);
       mbar_init(empty_bar + s, 1);
     }
-    mbar_init(tmem_full_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(tmem_full_bar + b, 1);
+      mbar_init(tmem_empty_bar + b, 128);  // every epilogue thread arrives
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   } else if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(C::kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tcgen05_fence_before();
@@ -152,82 +170,99 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t phase = (kb / kStages) & 1;
-        mbar_wait(empty_bar + s, phase ^ 1);
-        mbar_expect_tx(full_bar + s, kStageBytes);
-        uint8_t* a_dst = smem + (size_t)s * kStageBytes;
-        tma_load_2d(a_dst, &tmap_a, full_bar + s, kb * kBlockK, m0);
-        tma_load_2d(a_dst + kABytes, &tmap_b, full_bar + s, kb * kBlockK, n0);
+      uint32_t it = 0;  // k-block counter across all tiles of this CTA: the ring never drains
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / tiles_n) * kBlockM, n0 = (tile % tiles_n) * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(empty_bar + s, phase ^ 1);
+          mbar_expect_tx(full_bar + s, C::kStageBytes);
+          uint8_t* a_dst = smem + (size_t)s * C::kStageBytes;
+          tma_load_2d(a_dst, &tmap_a, full_bar + s, kb * kBlockK, m0);
+          tma_load_2d(a_dst + kABytes, &tmap_b, full_bar + s, kb * kBlockK, n0);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer =====
-      const uint32_t idesc = make_idesc();
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t phase = (kb / kStages) & 1;
-        mbar_wait(full_bar + s, phase);
+      const uint32_t idesc = make_idesc<BN>();
+      uint32_t it = 0, t = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+        const uint32_t buf = t & 1, use = t >> 1;
+        mbar_wait(tmem_empty_bar + buf, (use & 1) ^ 1);  // epilogue has drained this accumulator
         tcgen05_fence_after();
-        const uint32_t a_addr = smem_u32(smem + (size_t)s * kStageBytes);
-        const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + kABytes);
+        const uint32_t tmem_d = tmem_base + buf * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t phase = (it / kStages) & 1;
+          mbar_wait(full_bar + s, phase);
+          tcgen05_fence_after();
+          const uint32_t a_addr = smem_u32(smem + (size_t)s * C::kStageBytes);
+          const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + kABytes);
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
-          umma_f16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
+            umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+          }
+          umma_commit(empty_bar + s);  // frees the smem slot once these MMAs have read it
         }
-        umma_commit(empty_bar + s);  // frees the smem slot once these MMAs have read it
+        umma_commit(tmem_full_bar + buf);  // accumulator complete
       }
-      umma_commit(tmem_full_bar);    // accumulator complete
     }
   } else if (warp >= 4) {  // ===== epilogue: TMEM -> registers -> global =====
-    mbar_wait(tmem_full_bar, 0);
-    tcgen05_fence_after();
-    const int wq = warp & 3;                       // TMEM lane quarter this warp may access
-    const int row = m0 + wq * 32 + lane;
-    const bool row_ok = row < ep.M;
+    const int wq = warp & 3;  // TMEM lane quarter this warp may access
+    uint32_t t = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+      const int m0 = (tile / tiles_n) * kBlockM, n0 = (tile % tiles_n) * BN;
+      const uint32_t buf = t & 1, use = t >> 1;
+      mbar_wait(tmem_full_bar + buf, use & 1);
+      tcgen05_fence_after();
+      const int row = m0 + wq * 32 + lane;
+      const bool row_ok = row < ep.M;
 #pragma unroll 1
-    for (int c = 0; c < kBlockN; c += 32) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)c, r);
-      if (n0 + c >= ep.N) continue;               // warp-uniform
-      float v[32];
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)c, r);
+        if (n0 + c >= ep.N || !row_ok) continue;
+        float v[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int col = n0 + c + j;
-        float b = 0.f;
-        if (ep.bias && col < ep.N)
-          b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
-                           : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-        v[j] = apply_act(__uint_as_float(r[j]) + b, ep.act);
-      }
-      if (!row_ok) continue;
-      const bool full = (n0 + c + 32 <= ep.N);
-      if (ep.c_fp32) {
-        float* out = reinterpret_cast<float*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
-        if (full && (ep.ldc % 4 == 0)) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-        } else {
-          for (int j = 0; j < 32 && n0 + c + j < ep.N; ++j) out[j] = v[j];
+        for (int j = 0; j < 32; ++j) {
+          const int col = n0 + c + j;
+          float b = 0.f;
+          if (ep.bias && col < ep.N)
+            b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
+                             : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+          v[j] = apply_act(__uint_as_float(r[j]) + b, ep.act);
         }
-      } else {
-        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
-        if (full && (ep.ldc % 8 == 0)) {
+        const bool full = (n0 + c + 32 <= ep.N);
+        if (ep.c_fp32) {
+          float* out = reinterpret_cast<float*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
+          if (full && (ep.ldc % 4 == 0)) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(out + j) = VecTraits<MFL_BFLOAT16>::pack(v + j);
+            for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            for (int j = 0; j < 32 && n0 + c + j < ep.N; ++j) out[j] = v[j];
+          }
         } else {
-          for (int j = 0; j < 32 && n0 + c + j < ep.N; ++j) out[j] = __float2bfloat16_rn(v[j]);
+          __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
+          if (full && (ep.ldc % 8 == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) *reinterpret_cast<uint4*>(out + j) = VecTraits<MFL_BFLOAT16>::pack(v + j);
+          } else {
+            for (int j = 0; j < 32 && n0 + c + j < ep.N; ++j) out[j] = __float2bfloat16_rn(v[j]);
+          }
         }
       }
+      tcgen05_fence_before();
+      mbar_arrive(tmem_empty_bar + buf);  // this thread's TMEM reads of the buffer are done
     }
   }
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 2) {
     tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(C::kTmemCols) : "memory");
   }
 }
 
@@ -278,11 +313,18 @@ extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, i
           "gemm: A and B need 16-byte aligned bases and row pitches that are multiples of 8 elements (TMA)");
   MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
   CUtensorMap ta, tb;
+  const int bn = n > 128 ? 256 : 128;
   if (int rc = make_map(&ta, a, m, k, lda, kBlockM)) return rc;
-  if (int rc = make_map(&tb, b, n, k, ldb, kBlockN)) return rc;
+  if (int rc = make_map(&tb, b, n, k, ldb, bn)) return rc;
   Epilogue ep{c, bias, ldc, m, n, k, c_dtype == MFL_FLOAT32, bias_dtype == MFL_FLOAT32, act};
-  MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-  dim3 grid((n + kBlockN - 1) / kBlockN, (m + kBlockM - 1) / kBlockM);
-  gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(ta, tb, ep);
+  const int tiles = ((n + bn - 1) / bn) * ((m + kBlockM - 1) / kBlockM);
+  const int grid = std::min(tiles, sm_count());
+  if (bn == 256) {
+    MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmemBytes));
+    gemm_bf16_tcgen05_kernel<256><<<grid, kThreads, Cfg<256>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, ep);
+  } else {
+    MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<128>::kSmemBytes));
+    gemm_bf16_tcgen05_kernel<128><<<grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, ep);
+  }
   return check(cudaGetLastError(), "gemm_bf16_tcgen05_kernel launch");
 }
