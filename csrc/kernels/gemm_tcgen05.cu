@@ -38,7 +38,8 @@ template <int BN> struct Cfg {
   static constexpr uint32_t kBBytes = BN * kBlockK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;  // two fp32 accumulators of BN columns
-  static constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + 256 /*barriers*/;
+  static constexpr uint32_t kStoreBytes = 4 * 2 * 4096;  // 4 epilogue warps x 2 staging slabs of 32 rows x 128 B
+  static constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + kStoreBytes + 256 /*barriers*/;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -109,6 +110,11 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t* r) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+
 struct Epilogue {
   void* c;
   const void* bias;   // bf16 or fp32 [N], may be null
@@ -117,6 +123,7 @@ struct Epilogue {
   int32_t c_fp32;     // output dtype: 0 bf16, 1 fp32
   int32_t bias_fp32;
   int32_t act;        // 0 none, 1 relu, 2 gelu(tanh)
+  int32_t tma_store;  // C goes through swizzled smem slabs + cp.async.bulk.tensor stores (needs 16 B row pitch)
 };
 
 __device__ __forceinline__ float apply_act(float x, int act) {
@@ -131,12 +138,13 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                         const __grid_constant__ Epilogue ep) {
+                         const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ Epilogue ep) {
   using C = Cfg<BN>;
   constexpr int kStages = C::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)kStages * C::kStageBytes);
+  uint8_t* store_slabs = smem + (size_t)kStages * C::kStageBytes;  // 1024-byte aligned
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(store_slabs + C::kStoreBytes);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full_bar = empty_bar + kStages;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;    // [2]
@@ -150,6 +158,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_b) : "memory");
+    if (ep.tma_store) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_c) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(full_bar + s, 1);
       mbar_init(empty_bar + s, 1);
@@ -220,6 +229,60 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       tcgen05_fence_after();
       const int row = m0 + wq * 32 + lane;
       const bool row_ok = row < ep.M;
+      if (ep.tma_store) {
+        // Coalesced path: each warp packs 32 rows x 128 B into a swizzled slab and one lane hands it to
+        // the TMA store engine (which also clips the ragged M / N edges).
+        const int cols = ep.c_fp32 ? 32 : 64;  // columns per 128-byte slab row
+        uint8_t* slabs = store_slabs + wq * 8192;
+        uint32_t chunk = 0;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += cols, ++chunk) {
+          uint32_t r[64];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)c, r);
+          if (!ep.c_fp32) tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)(c + 32), r + 32);
+          if (n0 + c >= ep.N) continue;  // warp-uniform
+          uint8_t* slab = slabs + (chunk & 1) * 4096;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // slab used 2 chunks ago is free
+          __syncwarp();
+          uint8_t* my_row = slab + lane * 128;
+#pragma unroll
+          for (int j8 = 0; j8 < 8; ++j8) {  // eight 16-byte pieces per row, XOR-swizzled like TMA's SWIZZLE_128B
+            uint4 piece;
+            if (ep.c_fp32) {
+              float v[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int col = n0 + c + j8 * 4 + j;
+                float b = 0.f;
+                if (ep.bias && col < ep.N)
+                  b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
+                                   : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+                v[j] = apply_act(__uint_as_float(r[j8 * 4 + j]) + b, ep.act);
+              }
+              piece = VecTraits<MFL_FLOAT32>::pack(v);
+            } else {
+              float v[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const int col = n0 + c + j8 * 8 + j;
+                float b = 0.f;
+                if (ep.bias && col < ep.N)
+                  b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
+                                   : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+                v[j] = apply_act(__uint_as_float(r[j8 * 8 + j]) + b, ep.act);
+              }
+              piece = VecTraits<MFL_BFLOAT16>::pack(v);
+            }
+            *reinterpret_cast<uint4*>(my_row + ((j8 ^ (lane & 7)) << 4)) = piece;
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> async proxy
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < BN; c += 32) {
         uint32_t r[32];
@@ -254,10 +317,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
           }
         }
       }
+      }  // direct-store path
       tcgen05_fence_before();
       mbar_arrive(tmem_empty_bar + buf);  // this thread's TMEM reads of the buffer are done
     }
   }
+  if (warp >= 4 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores have left smem
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -283,14 +348,16 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-static int make_map(CUtensorMap* map, const void* base, int rows, int k, int64_t ld, int box_rows) {
+static int make_map(CUtensorMap* map, const void* base, int rows, int k, int64_t ld, int box_rows, bool fp32 = false) {
   EncodeTiledFn fn = encode_fn();
   MFL_ARG(fn != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
+  const int esz = fp32 ? 4 : 2;
   cuuint64_t dims[2] = {(cuuint64_t)k, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)box_rows};  // 128-byte inner extent
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = fn(map, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MFL_ARG(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed with CUresult %d (rows=%d k=%d ld=%lld)", (int)r, rows, k,
@@ -312,19 +379,26 @@ extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, i
   MFL_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0,
           "gemm: A and B need 16-byte aligned bases and row pitches that are multiples of 8 elements (TMA)");
   MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc;
   const int bn = n > 128 ? 256 : 128;
   if (int rc = make_map(&ta, a, m, k, lda, kBlockM)) return rc;
   if (int rc = make_map(&tb, b, n, k, ldb, bn)) return rc;
-  Epilogue ep{c, bias, ldc, m, n, k, c_dtype == MFL_FLOAT32, bias_dtype == MFL_FLOAT32, act};
+  const bool c32 = c_dtype == MFL_FLOAT32;
+  const bool tma_store = ((uintptr_t)c & 15) == 0 && (ldc * (c32 ? 4 : 2)) % 16 == 0;
+  if (tma_store) {
+    if (int rc = make_map(&tc, c, m, n, ldc, 32, c32)) return rc;
+  } else {
+    tc = ta;  // unused by the kernel
+  }
+  Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store};
   const int tiles = ((n + bn - 1) / bn) * ((m + kBlockM - 1) / kBlockM);
   const int grid = std::min(tiles, sm_count());
   if (bn == 256) {
     MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmemBytes));
-    gemm_bf16_tcgen05_kernel<256><<<grid, kThreads, Cfg<256>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, ep);
+    gemm_bf16_tcgen05_kernel<256><<<grid, kThreads, Cfg<256>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, tc, ep);
   } else {
     MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<128>::kSmemBytes));
-    gemm_bf16_tcgen05_kernel<128><<<grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, ep);
+    gemm_bf16_tcgen05_kernel<128><<<grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, tc, ep);
   }
   return check(cudaGetLastError(), "gemm_bf16_tcgen05_kernel launch");
 }
