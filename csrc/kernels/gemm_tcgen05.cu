@@ -39,7 +39,8 @@ template <int BN> struct Cfg {
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;  // two fp32 accumulators of BN columns
   static constexpr uint32_t kStoreBytes = 4 * 2 * 4096;  // 4 epilogue warps x 2 staging slabs of 32 rows x 128 B
-  static constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + kStoreBytes + 256 /*barriers*/;
+  static constexpr uint32_t kBiasBytes = 256 * 4;        // fp32 bias of the current tile's columns
+  static constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + kStoreBytes + kBiasBytes + 128 /*barriers*/;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -126,16 +127,16 @@ struct Epilogue {
   int32_t tma_store;  // C goes through swizzled smem slabs + cp.async.bulk.tensor stores (needs 16 B row pitch)
 };
 
-__device__ __forceinline__ float apply_act(float x, int act) {
-  if (act == 1) return fmaxf(x, 0.f);
-  if (act == 2) {
+template <int ACT> __device__ __forceinline__ float apply_act(float x) {
+  if constexpr (ACT == 1) return fmaxf(x, 0.f);
+  if constexpr (ACT == 2) {
     const float u = 0.7978845608f * (x + 0.044715f * x * x * x);
     return 0.5f * x * (1.f + tanhf(u));
   }
   return x;
 }
 
-template <int BN>
+template <int BN, int ACT, bool C_FP32>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                          const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ Epilogue ep) {
@@ -144,7 +145,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* store_slabs = smem + (size_t)kStages * C::kStageBytes;  // 1024-byte aligned
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(store_slabs + C::kStoreBytes);
+  float* sbias = reinterpret_cast<float*>(store_slabs + C::kStoreBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(store_slabs + C::kStoreBytes + C::kBiasBytes);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full_bar = empty_bar + kStages;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;    // [2]
@@ -229,50 +231,42 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       tcgen05_fence_after();
       const int row = m0 + wq * 32 + lane;
       const bool row_ok = row < ep.M;
+      // stage this tile's bias (zero where there is none / past N) so the inner loops are branch-free
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // previous tile's readers are done
+      for (int j = threadIdx.x - 128; j < BN; j += 128) {
+        const int col = n0 + j;
+        float b = 0.f;
+        if (ep.bias && col < ep.N)
+          b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
+                           : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
+        sbias[j] = b;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
       if (ep.tma_store) {
         // Coalesced path: each warp packs 32 rows x 128 B into a swizzled slab and one lane hands it to
         // the TMA store engine (which also clips the ragged M / N edges).
-        const int cols = ep.c_fp32 ? 32 : 64;  // columns per 128-byte slab row
+        constexpr int cols = C_FP32 ? 32 : 64;  // columns per 128-byte slab row
         uint8_t* slabs = store_slabs + wq * 8192;
         uint32_t chunk = 0;
 #pragma unroll 1
         for (int c = 0; c < BN; c += cols, ++chunk) {
-          uint32_t r[64];
+          uint32_t r[cols];
           tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)c, r);
-          if (!ep.c_fp32) tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)(c + 32), r + 32);
+          if constexpr (!C_FP32) tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)(c + 32), r + 32);
           if (n0 + c >= ep.N) continue;  // warp-uniform
           uint8_t* slab = slabs + (chunk & 1) * 4096;
           if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // slab used 2 chunks ago is free
           __syncwarp();
           uint8_t* my_row = slab + lane * 128;
+          constexpr int per = C_FP32 ? 4 : 8;  // elements per 16-byte piece
 #pragma unroll
           for (int j8 = 0; j8 < 8; ++j8) {  // eight 16-byte pieces per row, XOR-swizzled like TMA's SWIZZLE_128B
+            float v[per];
+#pragma unroll
+            for (int j = 0; j < per; ++j) v[j] = apply_act<ACT>(__uint_as_float(r[j8 * per + j]) + sbias[c + j8 * per + j]);
             uint4 piece;
-            if (ep.c_fp32) {
-              float v[4];
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const int col = n0 + c + j8 * 4 + j;
-                float b = 0.f;
-                if (ep.bias && col < ep.N)
-                  b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
-                                   : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-                v[j] = apply_act(__uint_as_float(r[j8 * 4 + j]) + b, ep.act);
-              }
-              piece = VecTraits<MFL_FLOAT32>::pack(v);
-            } else {
-              float v[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const int col = n0 + c + j8 * 8 + j;
-                float b = 0.f;
-                if (ep.bias && col < ep.N)
-                  b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
-                                   : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-                v[j] = apply_act(__uint_as_float(r[j8 * 8 + j]) + b, ep.act);
-              }
-              piece = VecTraits<MFL_BFLOAT16>::pack(v);
-            }
+            if constexpr (C_FP32) piece = VecTraits<MFL_FLOAT32>::pack(v);
+            else piece = VecTraits<MFL_BFLOAT16>::pack(v);
             *reinterpret_cast<uint4*>(my_row + ((j8 ^ (lane & 7)) << 4)) = piece;
           }
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> async proxy
@@ -290,16 +284,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         if (n0 + c >= ep.N || !row_ok) continue;
         float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int col = n0 + c + j;
-          float b = 0.f;
-          if (ep.bias && col < ep.N)
-            b = ep.bias_fp32 ? __ldg(reinterpret_cast<const float*>(ep.bias) + col)
-                             : __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(ep.bias) + col));
-          v[j] = apply_act(__uint_as_float(r[j]) + b, ep.act);
-        }
+        for (int j = 0; j < 32; ++j) v[j] = apply_act<ACT>(__uint_as_float(r[j]) + sbias[c + j]);
         const bool full = (n0 + c + 32 <= ep.N);
-        if (ep.c_fp32) {
+        if constexpr (C_FP32) {
           float* out = reinterpret_cast<float*>(ep.c) + (int64_t)row * ep.ldc + n0 + c;
           if (full && (ep.ldc % 4 == 0)) {
 #pragma unroll
@@ -393,12 +380,25 @@ extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, i
   Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store};
   const int tiles = ((n + bn - 1) / bn) * ((m + kBlockM - 1) / kBlockM);
   const int grid = std::min(tiles, sm_count());
-  if (bn == 256) {
-    MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<256>::kSmemBytes));
-    gemm_bf16_tcgen05_kernel<256><<<grid, kThreads, Cfg<256>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, tc, ep);
-  } else {
-    MFL_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<128>::kSmemBytes));
-    gemm_bf16_tcgen05_kernel<128><<<grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream>>>(ta, tb, tc, ep);
-  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = 0;
+#define MFL_GEMM_LAUNCH(BN_, ACT_, F32_)                                                                          \
+  do {                                                                                                            \
+    auto kern = gemm_bf16_tcgen05_kernel<BN_, ACT_, F32_>;                                                        \
+    rc = check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN_>::kSmemBytes), \
+               "cudaFuncSetAttribute(gemm smem)");                                                                \
+    if (!rc) kern<<<grid, kThreads, Cfg<BN_>::kSmemBytes, st>>>(ta, tb, tc, ep);                                  \
+  } while (0)
+#define MFL_GEMM_ACT(BN_, F32_)                                         \
+  do {                                                                  \
+    if (act == 0) MFL_GEMM_LAUNCH(BN_, 0, F32_);                        \
+    else if (act == 1) MFL_GEMM_LAUNCH(BN_, 1, F32_);                   \
+    else MFL_GEMM_LAUNCH(BN_, 2, F32_);                                 \
+  } while (0)
+  if (bn == 256) { if (c32) MFL_GEMM_ACT(256, true); else MFL_GEMM_ACT(256, false); }
+  else { if (c32) MFL_GEMM_ACT(128, true); else MFL_GEMM_ACT(128, false); }
+#undef MFL_GEMM_ACT
+#undef MFL_GEMM_LAUNCH
+  if (rc) return rc;
   return check(cudaGetLastError(), "gemm_bf16_tcgen05_kernel launch");
 }
