@@ -58,7 +58,7 @@ def main():
         slots = fab.alloc(nbytes * k)
         comm = fab.alloc(nbytes)
         pads = fab.signal_pads(296)
-        slots.local.view(torch.bfloat16).copy_(torch.randn(n * k, device=dev).to(torch.bfloat16))
+        slots.local.view(torch.bfloat16)[:n * k].copy_(torch.randn(n * k, device=dev).to(torch.bfloat16))
         L = world * k
         w = [1.0 / L] * L
         srcs = [slots.ptrs[r] + j * nbytes for r in range(world) for j in range(k)]

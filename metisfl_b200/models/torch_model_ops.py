@@ -134,6 +134,9 @@ class TorchModelOps(ModelOps):
         if loss_fn is None:
             loss_fn = module.loss_fn if _overrides(module, "loss_fn") else cross_entropy_loss
         self.loss_fn = loss_fn
+        if self.device.type == "cuda" and model_dtype == torch.bfloat16:
+            from metisfl_b200.ops import gemm as _gemm
+            _gemm.use_b200_linear(module)  # Linear layers on the tcgen05 GEMM (K10)
         self.arena = ModelArena(module, self.device, model_dtype)
         # variable-shaped last batches: the CUDA graph is used only for full batches
         self.trainer = LocalTrainer(self.arena, OptimHyper("VanillaSGD", lr=0.01), loss_fn,

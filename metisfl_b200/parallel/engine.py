@@ -74,6 +74,7 @@ class EngineConfig:
     channels_last: bool = True
     use_cuda_graph: Optional[bool] = None
     fused_blocks: int = 296
+    use_b200_linear: bool = True         # nn.Linear forward/backward on the tcgen05 GEMM (K10) when bf16 on CUDA
     seed: int = 1234
 
 
@@ -93,6 +94,9 @@ class FederationEngine:
         module = model_factory()
         if cfg.channels_last and self.device.type == "cuda":
             module = module.to(memory_format=torch.channels_last)
+        if cfg.use_b200_linear and self.device.type == "cuda" and cfg.model_dtype == torch.bfloat16:
+            from metisfl_b200.ops import gemm as _gemm
+            _gemm.use_b200_linear(module)
         self.layout = ArenaLayout.from_module(module, cfg.model_dtype)
         nb = self.layout.total_bytes
         # symmetric buffers: community model + k publish slots per rank
@@ -378,6 +382,56 @@ class FederationEngine:
         if ev is not None:
             out["eval"] = {"loss": host[nl], "correct": host[nl + 1] if ev[1] is not None else None}
         return out
+
+    # ------------------------------------------------------------------------------------------
+    def run_round_streaming(self, n_local_learners: int, batches_fn: Callable[[int], Sequence],
+                            examples_fn: Optional[Callable[[int], float]] = None) -> Dict:
+        """Many-learner round (config #5): ``n_local_learners`` logical learners are time-multiplexed on
+        this GPU and their models are folded into an fp32 running sum as soon as they are trained -
+        no per-learner model is ever kept (FedStride's memory-bounded idea taken to stride 1,
+        ``federated_stride.cc:6-48``).  The per-rank partial sums are then combined by ONE fused
+        cross-GPU launch.  ``batches_fn(g)`` yields the batches of global learner ``g``.
+        """
+        assert self.k >= 2, "streaming needs learners_per_gpu >= 2 slots (slot 0: partial sum, slot 1: publish target)"
+        n_total = n_local_learners * self.world
+        ex = examples_fn or (lambda g: 1.0)
+        # every rank needs the global normaliser; weights depend only on the (deterministic) example counts
+        z = float(sum(ex(g) for g in range(n_total)))
+        accs = [torch.zeros(sg.numel, dtype=torch.float32, device=self.device) if not sg.exact else None
+                for sg in self.layout.segments]
+        losses = []
+        first = True
+        for j in range(n_local_learners):
+            g = self.rank * n_local_learners + j
+            loss = self._train_into_slot(1, batches_fn(g))
+            losses.append(loss)
+            w = float(ex(g)) / z
+            last = j == n_local_learners - 1
+            for si, sg in enumerate(self.layout.segments):
+                x = self.slot_views[1][si]
+                if sg.exact:
+                    agg_ops.weighted_sum([x], [w], out=self.slot_views[0][si], exact=True, accumulate=not first)
+                else:
+                    agg_ops.weighted_sum([x], [w], out=self.slot_views[0][si] if last else None, acc=accs[si],
+                                         accumulate=not first, write_out=last)
+                self.gpu_launches += 1
+            first = False
+        srcs = [self._slot_ptr(r, 0) for r in range(self.world)]
+        if self.device.type == "cuda" and self.fabric.peer_mapped:
+            agg_ops.fused_aggregate(srcs, [1.0] * self.world, self.community.ptrs, self.pads.ptrs, self.rank,
+                                    self.world, self.layout.segment_table(), n_blocks=self.cfg.fused_blocks)
+            self.gpu_launches += 1
+            self.global_iteration += 1
+        else:
+            self._aggregate_host([r * self.k for r in range(self.world)], [1.0] * self.world)
+        return self._read_back([l for l in losses[-1:]], None)
+
+    def _train_into_slot(self, j: int, batches: Sequence):
+        """``train_learner`` for multiplexed learners that share slot ``j``."""
+        done = self.completed_batches[self.learner_id(j)]
+        loss = self.train_learner(j, batches)
+        self.completed_batches[self.learner_id(j)] = done
+        return loss
 
     def community_state_dict(self) -> Dict[str, torch.Tensor]:
         views = self.community_views
