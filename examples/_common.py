@@ -43,8 +43,10 @@ def device_time_ms(fn, dev, world):
     return float(t)
 
 
-def finish(rank, world, result):
+def finish(rank, world, result, engine=None):
     if rank == 0:
         print(json.dumps(result))
+    if engine is not None:
+        engine.close()  # unmaps peer memory; needs the process group for its barriers
     if world > 1:
         dist.destroy_process_group()

@@ -39,5 +39,4 @@ finish(rank, world, {
     "gpus": world, "round_time_s": ms * 1e-3 / a.rounds,
     "aggregated_params_per_s": n_learners * eng.layout.num_params / (ms * 1e-3 / a.rounds),
     "peak_mem_gib": torch.cuda.max_memory_allocated(dev) / 2**30 if dev.type == "cuda" else None,
-    "last_loss": out.get("loss")})
-eng.close()
+    "last_loss": out.get("loss")}, engine=eng)

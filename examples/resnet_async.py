@@ -38,5 +38,4 @@ finish(rank, world, {
     "config": "#3 ResNet-18 async", "rule": a.rule, "learners": L, "gpus": world, "community_updates": a.updates,
     "ms_per_update": ms / a.updates, "updates_per_s": a.updates / (ms * 1e-3),
     "aggregated_params_per_s": a.updates * eng.layout.num_params / (ms * 1e-3),
-    "mean_staleness": stats.get("mean_staleness"), "max_staleness": stats.get("max_staleness")})
-eng.close()
+    "mean_staleness": stats.get("mean_staleness"), "max_staleness": stats.get("max_staleness")}, engine=eng)

@@ -62,5 +62,4 @@ ms = device_time_ms(lambda: [secure_round() for _ in range(a.rounds)], dev, worl
 finish(rank, world, {
     "config": "#4 ResNet-18 CKKS secure aggregation", "gpus": world, "learners": world, "encrypted_params": n,
     "ciphertexts_per_model": n_ct, "ciphertext_bytes_per_model": words * 8,
-    "round_time_s": ms * 1e-3 / a.rounds, "max_abs_error_vs_plaintext": err[0]})
-eng.close()
+    "round_time_s": ms * 1e-3 / a.rounds, "max_abs_error_vs_plaintext": err[0]}, engine=eng)

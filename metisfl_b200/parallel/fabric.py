@@ -67,7 +67,7 @@ class Fabric:
         return out
 
     def host_barrier(self):
-        if self.distributed and self.world > 1:
+        if self.distributed and self.world > 1 and dist.is_initialized():
             if self.device.type == "cuda":
                 torch.cuda.synchronize(self.device)
             dist.barrier(group=self.group)
