@@ -7,8 +7,11 @@ class LearnerTrainer(object):
     def __init__(self, model_ops_fn, model_pb):
         self._model_ops = model_ops_fn() if callable(model_ops_fn) else model_ops_fn
         if model_pb is not None and len(model_pb.variables) > 0:
-            names, trainables, values = self._model_ops.get_model_weights_from_variables_pb(model_pb.variables)
-            self._model_ops.set_model_weights(names, trainables, values)
+            if hasattr(self._model_ops, "set_model_weights_from_pb"):  # bulk device unpack (K12)
+                self._model_ops.set_model_weights_from_pb(model_pb)
+            else:
+                names, trainables, values = self._model_ops.get_model_weights_from_variables_pb(model_pb.variables)
+                self._model_ops.set_model_weights(names, trainables, values)
 
     def __enter__(self):
         return self

@@ -159,11 +159,14 @@ class TorchModelOps(ModelOps):
 
     # -- weights ----------------------------------------------------------------------------------
     def get_model_weights(self, *args, **kwargs):
+        # one device->host copy of the whole arena, then per-variable views of the host copy
+        host = self.arena.state.detach().to("cpu")
+        seg = self.arena.layout.views(host)
         names, trainables, values = [], [], []
-        for name, view, trainable in self.arena.named_variables():
-            names.append(name)
-            trainables.append(trainable)
-            values.append(view.detach().cpu())
+        for v in self.arena.layout.variables:
+            names.append(v.name)
+            trainables.append(v.trainable)
+            values.append(self.arena.layout.var_view(seg, v))
         return names, trainables, values
 
     def set_model_weights(self, weights_names: List[str], weights_trainable: List[bool], weights_values, *args,
@@ -181,6 +184,19 @@ class TorchModelOps(ModelOps):
                 src = _as_tensor(by_name[n])
                 view.copy_(src.to(view.device, non_blocking=True).reshape(view.shape).to(view.dtype))
         self.arena.sync_master_from_model()
+
+    def set_model_weights_from_pb(self, model_pb: model_pb2.Model):
+        """Wire model -> arena in bulk: one staging copy + one cast/scatter launch per dtype pair (K12)."""
+        from metisfl_b200.ops import pack
+        if any(v.HasField("ciphertext_tensor") for v in model_pb.variables):
+            names, trainables, values = self.get_model_weights_from_variables_pb(model_pb.variables)
+            return self.set_model_weights(names, trainables, values)
+        pack.unpack_model_into_arena(model_pb, self.arena)
+
+    def get_model_pb(self) -> model_pb2.Model:
+        """Arena -> wire model with a single device->host copy."""
+        from metisfl_b200.ops import pack
+        return pack.arena_to_model_pb(self.arena)
 
     def construct_optimizer(self, optimizer_config_pb: model_pb2.OptimizerConfig = None, *args, **kwargs):
         h = optim_hyper_from_pb(optimizer_config_pb)
