@@ -87,6 +87,22 @@ def build_core(force=False, verbose=False):
     return out
 
 
+def build_tools(force=False, verbose=False):
+    """Standalone native binaries (aggregation micro-benchmark of the controller core)."""
+    srcs = sorted(glob.glob(os.path.join(ROOT, "csrc", "tools", "*.cc")))
+    core = [s for s in sorted(glob.glob(os.path.join(ROOT, "csrc", "core", "*.cc")) +
+                              glob.glob(os.path.join(ROOT, "csrc", "ckks", "*.cc"))) if not s.endswith("pybind.cc")]
+    outs = []
+    os.makedirs(os.path.join(ROOT, "metisfl_b200", "bin"), exist_ok=True)
+    for s in srcs:
+        out = os.path.join(ROOT, "metisfl_b200", "bin", os.path.basename(s)[:-3].replace("_main", ""))
+        if force or _stale(out, [s] + core + _headers()):
+            _run(["g++", "-O3", "-std=c++17", "-fopenmp", "-pthread", "-I", os.path.join(ROOT, "include"),
+                  "-I", os.path.join(ROOT, "csrc"), s] + core + ["-o", out], verbose)
+        outs.append(out)
+    return outs
+
+
 def main(argv):
     what = [a for a in argv if not a.startswith("-")] or ["all"]
     force, verbose = "--force" in argv, "-v" in argv
@@ -94,6 +110,8 @@ def main(argv):
         print("built", build_kernels(force, verbose))
     if "core" in what or "all" in what:
         print("built", build_core(force, verbose))
+    if "tools" in what or "all" in what:
+        print("built", build_tools(force, verbose))
 
 
 if __name__ == "__main__":
