@@ -10,6 +10,8 @@ that it declares but never implements (``GetCommunityModelLineage``,
 from __future__ import annotations
 
 import concurrent.futures
+import json
+import os
 import threading
 
 import grpc
@@ -106,6 +108,14 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         self.core = _core.Controller(params_pb_to_core(params_pb), self._send_run_tasks, self._send_evaluation_tasks)
         self._shutdown_event = threading.Event()
         self._server = None
+        # checkpoint / resume: the durable format is the serialized FederatedModel itself
+        self._snapshot_dir = os.environ.get("METISFL_SNAPSHOT_DIR") or None
+        self._snapshot_every = max(1, int(os.environ.get("METISFL_SNAPSHOT_EVERY", "1")))
+        self._snapshot_iteration = -1
+        self._snapshot_thread = None
+        if self._snapshot_dir:
+            os.makedirs(self._snapshot_dir, exist_ok=True)
+            self._resume_from_snapshot()
         self._evaluation_metrics = metis_pb2.EvaluationMetrics()
 
     # -- server lifecycle -----------------------------------------------------------------------
@@ -114,10 +124,64 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         self._server = self._server_holder.server
         controller_pb2_grpc.add_ControllerServiceServicer_to_server(self, self._server)
         self._server.start()
+        if self._snapshot_dir:
+            self._snapshot_thread = threading.Thread(target=self._snapshot_loop, daemon=True)
+            self._snapshot_thread.start()
         MetisLogger.info("Controller listening on %s:%s", self.params_pb.server_entity.hostname,
                          self.params_pb.server_entity.port)
 
+    # -- snapshots ------------------------------------------------------------------------------------
+    def _resume_from_snapshot(self):
+        state_fp = os.path.join(self._snapshot_dir, "state.json")
+        if not os.path.exists(state_fp):
+            return False
+        with open(state_fp) as f:
+            state = json.load(f)
+        model_fp = os.path.join(self._snapshot_dir, state["community_model_file"])
+        with open(model_fp, "rb") as f:
+            self.core.replace_community_model(f.read())
+        MetisLogger.info("Resumed community model of iteration %s from %s", state.get("global_iteration"), model_fp)
+        return True
+
+    def write_snapshot(self, force=False):
+        """Persist the current community model + lineage metadata (atomic rename)."""
+        if not self._snapshot_dir:
+            return None
+        blob = self.core.community_model()
+        if blob is None:
+            return None
+        iteration = self.core.global_iteration()
+        if not force and (iteration == self._snapshot_iteration or iteration % self._snapshot_every):
+            return None
+        name = "community_model_{:06d}.pb".format(iteration)
+        tmp = os.path.join(self._snapshot_dir, name + ".tmp")
+        with open(tmp, "wb") as f:
+            f.write(blob)
+        os.replace(tmp, os.path.join(self._snapshot_dir, name))
+        state = {"global_iteration": iteration, "community_model_file": name,
+                 "learners": [l["id"] for l in self.core.get_learners()],
+                 "runtime_metadata": self.core.get_runtime_metadata_lineage(8)}
+        tmp = os.path.join(self._snapshot_dir, "state.json.tmp")
+        with open(tmp, "w") as f:
+            json.dump(state, f, default=str)
+        os.replace(tmp, os.path.join(self._snapshot_dir, "state.json"))
+        self._snapshot_iteration = iteration
+        return name
+
+    def _snapshot_loop(self):
+        while not self._shutdown_event.wait(0.5):
+            try:
+                self.write_snapshot()
+            except Exception as e:  # a failed snapshot must never take the controller down
+                MetisLogger.warning("snapshot failed: %r", e)
+
     def stop(self, grace=1.0):
+        self._shutdown_event.set()
+        if self._snapshot_dir:
+            try:
+                self.write_snapshot(force=True)
+            except Exception:
+                pass
         self.core.shutdown()
         if self._server is not None:
             self._server.stop(grace).wait()

@@ -66,6 +66,9 @@ class LearnerServicer(learner_pb2_grpc.LearnerServiceServicer):
             self._refuse(context)
             return LearnerServiceProtoMessages.construct_run_task_response_pb(_ack(False))
         self.__community_models_received += 1
+        from metisfl_b200.utils.fault_injector import FaultInjector
+        if FaultInjector.instance().on_task(self.learner.host_port_identifier(), request.task.global_iteration) == "drop":
+            return LearnerServiceProtoMessages.construct_run_task_response_pb(_ack(True))  # swallowed on purpose
         accepted = self.learner.run_learning_task(
             request.task, request.hyperparameters, request.federated_model.model,
             cancel_running_tasks=True, block=False, verbose=False)

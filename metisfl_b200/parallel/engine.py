@@ -433,6 +433,36 @@ class FederationEngine:
         self.completed_batches[self.learner_id(j)] = done
         return loss
 
+    # -- checkpoint / resume: the durable format is the wire FederatedModel -------------
+    def save_checkpoint(self, path: str):
+        from types import SimpleNamespace
+
+        from metisfl_b200.ops import pack
+        from metisfl_b200.proto import model_pb2
+        model = pack.arena_to_model_pb(SimpleNamespace(state=self.community.local, layout=self.layout))
+        fm = model_pb2.FederatedModel(num_contributors=self.num_learners, global_iteration=self.global_iteration,
+                                      model=model)
+        tmp = path + ".tmp"
+        with open(tmp, "wb") as f:
+            f.write(fm.SerializeToString())
+        import os
+        os.replace(tmp, path)
+
+    def load_checkpoint(self, path: str):
+        from types import SimpleNamespace
+
+        from metisfl_b200.ops import pack
+        from metisfl_b200.proto import model_pb2
+        with open(path, "rb") as f:
+            fm = model_pb2.FederatedModel.FromString(f.read())
+        shim = SimpleNamespace(state=self.community.local, layout=self.layout, device=self.device,
+                               sync_master_from_model=lambda: None)
+        pack.unpack_model_into_arena(fm.model, shim)
+        self.global_iteration = fm.global_iteration
+        if self.direct_install:
+            self.arena.sync_master_from_model()
+        return fm.global_iteration
+
     def community_state_dict(self) -> Dict[str, torch.Tensor]:
         views = self.community_views
         return {v.name: self.layout.var_view(views, v).clone() for v in self.layout.variables}
