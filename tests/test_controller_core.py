@@ -57,6 +57,16 @@ class Federation:
         for l in learners:
             self.core.evaluation_completed(l[0], idx, b"")
 
+    def release(self):
+        """Switch to automatic echo mode and answer the tasks that were issued while it was off."""
+        self.auto = True
+        c, it, model = _core.parse_federated_model(self.core.community_model())
+        with self.lock:
+            pending = list(self.run_log)
+        for ids, iteration, updates in pending:
+            for lid, u in zip(ids, updates):
+                threading.Thread(target=self._complete, args=(lid, model, iteration, u), daemon=True).start()
+
     def join(self, i):
         lid, tok = self.core.add_learner("127.0.0.1", 9000 + i, b"", b"", self.examples[i], 0, 0)
         self.tokens[lid] = tok
@@ -112,11 +122,13 @@ def test_learner_joining_before_the_model_waits_for_it():
 
 
 def test_synchronous_fedavg_rounds_and_metadata():
-    f = Federation(n=3, examples=[100, 300, 600])
+    f = Federation(n=3, examples=[100, 300, 600], auto=False)
     f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
     ids = [f.join(i) for i in range(3)]
     for lid, d in zip(ids, (1.0, 2.0, 3.0)):
         f.delta[lid] = d
+    f.core.wait_idle()
+    f.release()  # everybody has joined before the first task completes
     f.wait_rounds(3)
     f.mute.update(ids)
     time.sleep(0.1)
@@ -188,10 +200,12 @@ def test_asynchronous_rules_fold_the_completing_learner(rule):
 
 
 def test_semi_synchronous_resizes_tasks_after_first_round():
-    f = Federation(protocol=3, n=2, semi_lambda=2)
+    f = Federation(protocol=3, n=2, semi_lambda=2, auto=False)
     f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
     ids = [f.join(i) for i in range(2)]
     f.ms_per_batch = {ids[0]: 1.0, ids[1]: 4.0}   # ms/epoch = 10x: slowest epoch = 40 ms -> t_max = 80 ms
+    f.core.wait_idle()
+    f.release()
     f.wait_rounds(1)
     f.mute.update(ids)
     time.sleep(0.1)
@@ -202,11 +216,14 @@ def test_semi_synchronous_resizes_tasks_after_first_round():
 
 
 def test_dead_learner_is_evicted_and_the_round_completes():
-    f = Federation(n=2, deadline=0.3)
+    f = Federation(n=2, deadline=0.3, auto=False)
     f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
     ids = [f.join(i) for i in range(2)]
     f.mute.add(ids[1])  # never answers (reference quirk Q9: the round would hang forever)
     f.delta[ids[0]] = 1.0
+    f.core.wait_idle()
+    f.auto = True
+    f._complete(ids[0], _core.parse_federated_model(f.core.community_model())[2], 1, 20)
     f.wait_rounds(2, timeout=10)
     assert [l["id"] for l in f.core.get_learners()] == [ids[0]]
     f.core.shutdown()
