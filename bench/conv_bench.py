@@ -1,0 +1,42 @@
+#!/usr/bin/env python
+"""Implicit-GEMM conv (K11) vs cuDNN (F.conv2d) forward on the CIFAR ResNet-18 layer shapes, batch 128."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+import torch.nn.functional as F  # noqa: E402
+
+from metisfl_b200.ops import conv  # noqa: E402
+
+torch.backends.cudnn.benchmark = True
+
+
+def timeit(fn, iters=20, warmup=5):
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        flush.fill_(0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / iters
+
+
+rows = []
+for (c, h, k, r, st, p) in [(64, 32, 64, 3, 1, 1), (64, 32, 128, 3, 2, 1), (128, 16, 128, 3, 1, 1), (128, 16, 256, 3, 2, 1),
+                            (256, 8, 256, 3, 1, 1), (256, 8, 512, 3, 2, 1), (512, 4, 512, 3, 1, 1), (64, 32, 128, 1, 2, 0)]:
+    n = 128
+    x = torch.randn(n, c, h, h, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = torch.randn(k, c, r, r, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    t_ours = timeit(lambda: conv.conv2d_fprop(x, w, st, p))
+    t_cudnn = timeit(lambda: F.conv2d(x, w, None, st, p))
+    oh = (h + 2 * p - r) // st + 1
+    fl = 2.0 * n * oh * oh * k * c * r * r
+    rows.append({"C": c, "HW": h, "K": k, "R": r, "stride": st, "ours_us": t_ours * 1e3, "cudnn_us": t_cudnn * 1e3,
+                 "ours_tflops": fl / t_ours / 1e9, "cudnn_tflops": fl / t_cudnn / 1e9})
+print(json.dumps({"bench": "conv_bench", "batch": 128, "results": rows}))

@@ -34,7 +34,7 @@ constexpr int kThreads = 256;
 constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
 
 template <int BN> struct Cfg {
-  static constexpr int kStages = BN == 256 ? 4 : 6;
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
   static constexpr uint32_t kBBytes = BN * kBlockK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;  // two fp32 accumulators of BN columns
@@ -66,6 +66,16 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+// im2col-mode TMA (K11): 128 consecutive output pixels x 64 channels of an NHWC activation tensor for the
+// filter tap (offset_w, offset_h); padding is zero-filled by the unit
+__device__ __forceinline__ void tma_load_im2col_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c, int w,
+                                                   int h, int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
 }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -125,6 +135,8 @@ struct Epilogue {
   int32_t bias_fp32;
   int32_t act;        // 0 none, 1 relu, 2 gelu(tanh)
   int32_t tma_store;  // C goes through swizzled smem slabs + cp.async.bulk.tensor stores (needs 16 B row pitch)
+  // implicit-GEMM convolution (K11): A rows are output pixels, A columns are (r, s, c) - loaded with im2col TMA
+  int32_t conv, out_h, out_w, stride, pad, filt_s, c_blocks;
 };
 
 template <int ACT> __device__ __forceinline__ float apply_act(float x) {
@@ -190,7 +202,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
           mbar_wait(empty_bar + s, phase ^ 1);
           mbar_expect_tx(full_bar + s, C::kStageBytes);
           uint8_t* a_dst = smem + (size_t)s * C::kStageBytes;
-          tma_load_2d(a_dst, &tmap_a, full_bar + s, kb * kBlockK, m0);
+          if (ep.conv) {
+            const int img = m0 / (ep.out_h * ep.out_w), rem = m0 % (ep.out_h * ep.out_w);
+            const int oh = rem / ep.out_w, ow = rem % ep.out_w;
+            const int rs = kb / ep.c_blocks, cb = kb % ep.c_blocks;
+            tma_load_im2col_4d(a_dst, &tmap_a, full_bar + s, cb * kBlockK, ow * ep.stride - ep.pad,
+                               oh * ep.stride - ep.pad, img, (uint16_t)(rs % ep.filt_s), (uint16_t)(rs / ep.filt_s));
+          } else {
+            tma_load_2d(a_dst, &tmap_a, full_bar + s, kb * kBlockK, m0);
+          }
           tma_load_2d(a_dst + kABytes, &tmap_b, full_bar + s, kb * kBlockK, n0);
         }
       }
@@ -357,30 +377,11 @@ static int make_map(CUtensorMap* map, const void* base, int rows, int k, int64_t
 
 using namespace mfl;
 
-extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
-                             const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream) {
-  using namespace mfl::gemm;
-  MFL_ARG(a && b && c && m > 0 && n > 0 && k > 0, "gemm: null operand or empty shape");
-  MFL_ARG(c_dtype == MFL_BFLOAT16 || c_dtype == MFL_FLOAT32, "gemm: output must be BFLOAT16 or FLOAT32");
-  MFL_ARG(!bias || bias_dtype == MFL_BFLOAT16 || bias_dtype == MFL_FLOAT32, "gemm: bias must be BFLOAT16 or FLOAT32");
-  MFL_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0,
-          "gemm: A and B need 16-byte aligned bases and row pitches that are multiples of 8 elements (TMA)");
-  MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
-  CUtensorMap ta, tb, tc;
-  const int bn = n > 128 ? 256 : 128;
-  if (int rc = make_map(&ta, a, m, k, lda, kBlockM)) return rc;
-  if (int rc = make_map(&tb, b, n, k, ldb, bn)) return rc;
-  const bool c32 = c_dtype == MFL_FLOAT32;
-  const bool tma_store = ((uintptr_t)c & 15) == 0 && (ldc * (c32 ? 4 : 2)) % 16 == 0;
-  if (tma_store) {
-    if (int rc = make_map(&tc, c, m, n, ldc, 32, c32)) return rc;
-  } else {
-    tc = ta;  // unused by the kernel
-  }
-  Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store};
-  const int tiles = ((n + bn - 1) / bn) * ((m + kBlockM - 1) / kBlockM);
+namespace mfl { namespace gemm {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const Epilogue& ep, int bn,
+                       int act, bool c32, cudaStream_t st) {
+  const int tiles = ((ep.N + bn - 1) / bn) * ((ep.M + kBlockM - 1) / kBlockM);
   const int grid = std::min(tiles, sm_count());
-  cudaStream_t st = (cudaStream_t)stream;
   int rc = 0;
 #define MFL_GEMM_LAUNCH(BN_, ACT_, F32_)                                                                          \
   do {                                                                                                            \
@@ -396,9 +397,85 @@ extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, i
     else MFL_GEMM_LAUNCH(BN_, 2, F32_);                                 \
   } while (0)
   if (bn == 256) { if (c32) MFL_GEMM_ACT(256, true); else MFL_GEMM_ACT(256, false); }
-  else { if (c32) MFL_GEMM_ACT(128, true); else MFL_GEMM_ACT(128, false); }
+  else if (bn == 128) { if (c32) MFL_GEMM_ACT(128, true); else MFL_GEMM_ACT(128, false); }
+  else { if (c32) MFL_GEMM_ACT(64, true); else MFL_GEMM_ACT(64, false); }
 #undef MFL_GEMM_ACT
 #undef MFL_GEMM_LAUNCH
   if (rc) return rc;
   return check(cudaGetLastError(), "gemm_bf16_tcgen05_kernel launch");
+}
+
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeIm2colFn encode_im2col_fn() {
+  static EncodeIm2colFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeIm2colFn>(p);
+  }
+  return fn;
+}
+}}  // namespace mfl::gemm
+
+extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
+                             const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream) {
+  using namespace mfl::gemm;
+  MFL_ARG(a && b && c && m > 0 && n > 0 && k > 0, "gemm: null operand or empty shape");
+  MFL_ARG(c_dtype == MFL_BFLOAT16 || c_dtype == MFL_FLOAT32, "gemm: output must be BFLOAT16 or FLOAT32");
+  MFL_ARG(!bias || bias_dtype == MFL_BFLOAT16 || bias_dtype == MFL_FLOAT32, "gemm: bias must be BFLOAT16 or FLOAT32");
+  MFL_ARG(lda % 8 == 0 && ldb % 8 == 0 && ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0,
+          "gemm: A and B need 16-byte aligned bases and row pitches that are multiples of 8 elements (TMA)");
+  MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
+  CUtensorMap ta, tb, tc;
+  const int bn = n > 128 ? 256 : (n > 64 ? 128 : 64);
+  if (int rc = make_map(&ta, a, m, k, lda, kBlockM)) return rc;
+  if (int rc = make_map(&tb, b, n, k, ldb, bn)) return rc;
+  const bool c32 = c_dtype == MFL_FLOAT32;
+  const bool tma_store = ((uintptr_t)c & 15) == 0 && (ldc * (c32 ? 4 : 2)) % 16 == 0;
+  if (tma_store) {
+    if (int rc = make_map(&tc, c, m, n, ldc, 32, c32)) return rc;
+  } else {
+    tc = ta;  // unused by the kernel
+  }
+  Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store, 0, 0, 0, 0, 0, 0, 0};
+  return launch_gemm(ta, tb, tc, ep, bn, act, c32, (cudaStream_t)stream);
+}
+
+// ---- K11: implicit-GEMM convolution forward (also used for stride-1 data gradients) ----------------
+// y[N, OH, OW, K] = conv(x[N, H, W, C], w[K, R, S, C]), NHWC bf16, C % 64 == 0, K % 8 == 0.
+// Replaces the framework convolutions under the learners' training loop (keras_model_ops.py:156).  The A
+// operand is never materialised: the TMA unit gathers 128 output pixels x 64 channels per filter tap
+// straight into the swizzled shared-memory tile the tensor core reads (im2col tensor map).
+extern "C" int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, int r,
+                                     int s, int stride, int pad, void* stream) {
+  using namespace mfl::gemm;
+  MFL_ARG(y && x && w && n > 0 && h > 0 && wd > 0, "conv2d: null operand or empty shape");
+  MFL_ARG(c % 64 == 0 && k % 8 == 0, "conv2d: needs C %% 64 == 0 and K %% 8 == 0 (got C=%d K=%d)", c, k);
+  MFL_ARG(stride >= 1 && stride <= 8 && pad >= 0 && pad < 128 && r >= 1 && s >= 1 && r * s <= 49, "conv2d: bad geometry");
+  const int oh = (h + 2 * pad - r) / stride + 1, ow = (wd + 2 * pad - s) / stride + 1;
+  MFL_ARG(oh > 0 && ow > 0, "conv2d: empty output");
+  EncodeIm2colFn fn = encode_im2col_fn();
+  MFL_ARG(fn != nullptr, "conv2d: cuTensorMapEncodeIm2col is not available from this driver");
+  CUtensorMap ta, tb, tc;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)wd, (cuuint64_t)h, (cuuint64_t)n};
+    cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)wd * c * 2, (cuuint64_t)h * wd * c * 2};
+    int lower[2] = {-pad, -pad};
+    int upper[2] = {pad - (s - 1), pad - (r - 1)};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult res = fn(&ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, lower, upper,
+                      (cuuint32_t)kBlockK, (cuuint32_t)kBlockM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    MFL_ARG(res == CUDA_SUCCESS, "conv2d: cuTensorMapEncodeIm2col failed with CUresult %d", (int)res);
+  }
+  const int m = n * oh * ow, kk = r * s * c;
+  const int bn = k > 128 ? 256 : (k > 64 ? 128 : 64);
+  if (int rc = make_map(&tb, w, k, kk, kk, bn)) return rc;
+  if (int rc = make_map(&tc, y, m, k, k, 32, false)) return rc;
+  Epilogue ep{y, nullptr, k, m, k, kk, 0, 0, 0, 1, 1, oh, ow, stride, pad, s, c / 64};
+  return launch_gemm(ta, tb, tc, ep, bn, 0, false, (cudaStream_t)stream);
 }

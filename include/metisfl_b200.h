@@ -142,6 +142,13 @@ int mfl_fabric_barrier(uint32_t* const* signal_pads, int rank, int world, int ch
 int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
                   const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream);
 
+/* ---- K11: implicit-GEMM convolution forward on the same tcgen05 pipeline; the A operand is gathered by
+ * im2col-mode TMA (cuTensorMapEncodeIm2col), never materialised.  NHWC bf16: x[n,h,w,c], w[k,r,s,c],
+ * y[n,oh,ow,k]; c % 64 == 0, k % 8 == 0.  Stride-1 data gradients reuse it with flipped, transposed
+ * filters (metisfl_b200/ops/conv.py).  Replaces the framework convolutions under keras_model_ops.py:156. */
+int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, int r, int s,
+                          int stride, int pad, void* stream);
+
 /* ---- K5-K9: RNS-CKKS on the GPU (csrc/ckks/ckks_kernels.cu) ----------------------------------
  * Behavioural spec: encryption/palisade/ckks_scheme.cc:110-252 (Encrypt / ComputeWeightedAverage /
  * Decrypt) with the ciphertext layout of csrc/ckks/ckks_common.h: [ct][poly 0..1][limb][N] uint64 in

@@ -1,0 +1,104 @@
+"""Front-end of the implicit-GEMM convolution (K11) and an autograd-aware ``conv2d`` built on it.
+
+Forward and the stride-1 data gradient run on the tcgen05 kernel (the data gradient is the same
+convolution with spatially flipped, channel-transposed filters and padding ``R-1-p``); the weight
+gradient and stride-2 data gradients still go through ATen (cuDNN) - see DESIGN.md for the gap.
+Tensors are NHWC (``torch.channels_last``) bf16.  Reference counterpart: the framework convolutions
+under ``model.fit`` (``keras_model_ops.py:156``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from metisfl_b200.ops import _lib
+
+_BOUND = False
+
+
+def _bind():
+    global _BOUND
+    L = _lib.lib()
+    if not _BOUND:
+        vp, i = C.c_void_p, C.c_int
+        L.mfl_conv2d_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        _BOUND = True
+    return L
+
+
+def supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation=(1, 1), groups=1) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 4
+            and groups == 1 and tuple(dilation) == (1, 1) and stride[0] == stride[1] and padding[0] == padding[1]
+            and x.shape[1] % 64 == 0 and w.shape[0] % 8 == 0 and _lib.available())
+
+
+def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int) -> torch.Tensor:
+    """x: [N,C,H,W] channels_last bf16, w: [K,C,R,S] channels_last bf16 -> y: [N,K,OH,OW] channels_last."""
+    n, c, h, wd = x.shape
+    k, c2, r, s = w.shape
+    assert c == c2
+    x = x.contiguous(memory_format=torch.channels_last)
+    w = w.contiguous(memory_format=torch.channels_last)
+    oh, ow = (h + 2 * pad - r) // stride + 1, (wd + 2 * pad - s) // stride + 1
+    y = torch.empty((n, k, oh, ow), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    rc = _bind().mfl_conv2d_fprop_bf16(y.data_ptr(), x.data_ptr(), w.data_ptr(), n, h, wd, c, k, r, s, stride, pad,
+                                       _lib.stream_ptr())
+    _lib.check(rc, "mfl_conv2d_fprop_bf16")
+    return y
+
+
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, stride, pad):
+        ctx.save_for_backward(x, w)
+        ctx.stride, ctx.pad = stride, pad
+        return conv2d_fprop(x, w, stride, pad)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        stride, pad = ctx.stride, ctx.pad
+        gy = gy.contiguous(memory_format=torch.channels_last)
+        k, c, r, s = w.shape
+        gx = gw = None
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        if need_x and stride == 1 and k % 64 == 0 and c % 8 == 0 and r - 1 - pad >= 0:
+            # dX = conv(dY, flip(W)^T): filters [C, K, R, S] with both spatial axes reversed
+            wt = w.flip(2, 3).permute(1, 0, 2, 3).contiguous(memory_format=torch.channels_last)
+            gx = conv2d_fprop(gy, wt, 1, r - 1 - pad)
+            need_x = False
+        if need_x or need_w:
+            gx2, gw, _ = torch.ops.aten.convolution_backward(
+                gy, x, w, None, [stride, stride], [pad, pad], [1, 1], False, [0, 0], 1, [need_x, need_w, False])
+            if need_x:
+                gx = gx2
+        return gx, gw, None, None
+
+
+def conv2d(x: torch.Tensor, w: torch.Tensor, bias=None, stride=(1, 1), padding=(0, 0), dilation=(1, 1), groups=1):
+    """Drop-in for ``F.conv2d`` that uses the tcgen05 implicit-GEMM kernel when the operands allow it."""
+    stride = (stride, stride) if isinstance(stride, int) else tuple(stride)
+    padding = (padding, padding) if isinstance(padding, int) else tuple(padding)
+    if isinstance(padding, tuple) and supported(x, w, stride, padding, dilation if not isinstance(dilation, int)
+                                                else (dilation, dilation), groups):
+        y = _Conv2dFn.apply(x, w, stride[0], padding[0])
+        return y if bias is None else y + bias.view(1, -1, 1, 1)
+    return F.conv2d(x, w, bias, stride, padding, dilation, groups)
+
+
+class B200Conv2d(nn.Conv2d):
+    def forward(self, x):
+        if isinstance(self.padding, str) or self.padding_mode != "zeros":
+            return super().forward(x)
+        return conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
+
+
+def use_b200_conv(module: nn.Module) -> nn.Module:
+    """Re-class every ``nn.Conv2d`` so eligible layers run on the tcgen05 implicit-GEMM kernel."""
+    for m in module.modules():
+        if type(m) is nn.Conv2d:
+            m.__class__ = B200Conv2d
+    return module

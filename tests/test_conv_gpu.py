@@ -1,0 +1,64 @@
+"""Implicit-GEMM convolution (K11, im2col TMA + tcgen05) against an fp32 PyTorch reference, for every
+convolution shape of the CIFAR ResNet-18 that the kernel covers, forward and backward."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [  # (N, C, H, W, K, R, stride, pad)
+    (8, 64, 32, 32, 64, 3, 1, 1), (8, 64, 32, 32, 128, 3, 2, 1), (8, 64, 32, 32, 128, 1, 2, 0),
+    (8, 128, 16, 16, 128, 3, 1, 1), (4, 128, 16, 16, 256, 3, 2, 1), (4, 256, 8, 8, 256, 3, 1, 1),
+    (4, 256, 8, 8, 512, 1, 2, 0), (3, 512, 4, 4, 512, 3, 1, 1), (5, 64, 9, 7, 72, 3, 1, 1),
+]
+
+
+@pytest.mark.parametrize("n,c,h,w,k,r,stride,pad", SHAPES)
+def test_conv_fprop_matches_reference(n, c, h, w, k, r, stride, pad):
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(n * 1000 + c + k)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, r, r, generator=g) / (c * r * r) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last)
+    y = conv.conv2d_fprop(x, wt, stride, pad)
+    ref = F.conv2d(x.float(), wt.float(), None, stride, pad)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    torch.testing.assert_close(y.float(), ref, atol=3e-2, rtol=3e-2)
+
+
+@pytest.mark.parametrize("n,c,h,w,k,r,stride,pad", SHAPES[:6])
+def test_conv_autograd_matches_reference(n, c, h, w, k, r, stride, pad):
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, r, r, generator=g) / (c * r * r) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last)
+    x.requires_grad_(); wt.requires_grad_()
+    y = conv.conv2d(x, wt, None, stride, pad)
+    gy = torch.randn_like(y)
+    y.backward(gy)
+    xr, wr = x.detach().float().requires_grad_(), wt.detach().float().requires_grad_()
+    F.conv2d(xr, wr, None, stride, pad).backward(gy.float())
+    torch.testing.assert_close(x.grad.float(), xr.grad, atol=5e-2, rtol=5e-2)
+    torch.testing.assert_close(wt.grad.float(), wr.grad, atol=2e-1, rtol=5e-2)
+
+
+def test_resnet18_with_b200_conv_tracks_cudnn():
+    from metisfl_b200.models.zoo import ResNet18
+    from metisfl_b200.ops import conv
+    torch.manual_seed(0)
+    ref = ResNet18().cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    ours = ResNet18().cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    ours.load_state_dict(ref.state_dict())
+    conv.use_b200_conv(ours)
+    x = torch.randn(32, 3, 32, 32, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 10, (32,), device="cuda")
+    losses = []
+    for model in (ref, ours):
+        loss = F.cross_entropy(model(x).float(), y)
+        loss.backward()
+        losses.append(float(loss))
+    assert abs(losses[0] - losses[1]) < 5e-2, losses
+    gr = dict(ref.named_parameters())["layers.0.conv1.weight"].grad.float()
+    go = dict(ours.named_parameters())["layers.0.conv1.weight"].grad.float()
+    assert torch.nn.functional.cosine_similarity(gr.flatten(), go.flatten(), dim=0) > 0.98
