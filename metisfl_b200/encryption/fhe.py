@@ -134,3 +134,17 @@ class CKKS(object):
 
     def rescale(self, ciphertext: bytes) -> bytes:
         return _core.ckks_rescale(ciphertext)
+
+
+if __name__ == "__main__":  # python -m metisfl_b200.encryption.fhe --gen DIR
+    import argparse
+    ap = argparse.ArgumentParser(description="generate a CKKS context and key files")
+    ap.add_argument("--gen", required=True, metavar="DIR")
+    ap.add_argument("--batch_size", type=int, default=4096)
+    ap.add_argument("--scaling_factor_bits", type=int, default=52)
+    ap.add_argument("--seed", type=int, default=0)
+    a = ap.parse_args()
+    scheme = CKKS(a.batch_size, a.scaling_factor_bits)
+    scheme.gen_crypto_context_and_keys(a.gen, seed=a.seed)
+    for k, v in scheme.get_crypto_params_files().items():
+        print(k, v)

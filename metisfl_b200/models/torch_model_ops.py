@@ -206,7 +206,8 @@ class TorchModelOps(ModelOps):
     # -- training ---------------------------------------------------------------------------------
     def train_model(self, train_dataset: ModelDataset, learning_task_pb: metis_pb2.LearningTask,
                     hyperparameters_pb: metis_pb2.Hyperparameters, validation_dataset: ModelDataset = None,
-                    test_dataset: ModelDataset = None, verbose=False, cancel_event=None, *args, **kwargs):
+                    test_dataset: ModelDataset = None, verbose=False, cancel_event=None, callbacks=None, *args,
+                    **kwargs):
         if train_dataset is None:
             raise RuntimeError("Provided `dataset` for training is None.")
         self.construct_optimizer(hyperparameters_pb.optimizer)
@@ -226,12 +227,19 @@ class TorchModelOps(ModelOps):
         steps_done, epochs_done, epoch_ms = 0, 0, []
         t_task = time.perf_counter()
         cancelled = False
+        callbacks = list(callbacks or [])
+        for cb in callbacks:
+            cb.on_train_begin()
         while steps_done < total_steps and spe > 0 and not cancelled:
             t_epoch = time.perf_counter()
             running, n_run = None, 0
+            for cb in callbacks:
+                cb.on_epoch_begin(epochs_done)
             for x, y in batches:
-                if steps_done >= total_steps:
+                if steps_done >= total_steps or any(cb.stop_training for cb in callbacks):
                     break
+                for cb in callbacks:
+                    cb.on_train_batch_begin(steps_done)
                 if cancel_event is not None and cancel_event.is_set():
                     cancelled = True
                     break
@@ -244,15 +252,23 @@ class TorchModelOps(ModelOps):
                 running = loss.detach().float().clone() if running is None else running + loss.detach().float()
                 n_run += 1
                 steps_done += 1
+                for cb in callbacks:
+                    cb.on_train_batch_end(steps_done - 1)
+            for cb in callbacks:
+                cb.on_epoch_end(epochs_done)
             if self.device.type == "cuda":
                 torch.cuda.synchronize(self.device)
             epoch_ms.append((time.perf_counter() - t_epoch) * 1e3)
             epochs_done += 1
+            if any(cb.stop_training for cb in callbacks):
+                break
             if n_run:
                 train_stats.setdefault("loss", []).append(float(running) / n_run)
         if self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
         total_ms = (time.perf_counter() - t_task) * 1e3
+        for cb in callbacks:
+            cb.on_train_end()
         # end-of-task evaluation of the locally trained model (last epoch entry of each split)
         metrics = list(learning_task_pb.metrics.metric)
         for ds, stats in ((train_dataset, train_stats), (validation_dataset, valid_stats), (test_dataset, test_stats)):

@@ -91,3 +91,16 @@ class SSLConfigurator(object):
                 public_certificate_stream=stream)
         return proto_factory.MetisProtoMessages.construct_ssl_config_pb(
             enable_ssl=ssl_config_pb.enable_ssl, config_pb=config_pb)
+
+
+if __name__ == "__main__":  # python -m metisfl_b200.utils.ssl_configurator --out DIR [--host NAME ...]
+    import argparse
+    ap = argparse.ArgumentParser(description="write a self-signed server-cert.pem / server-key.pem pair")
+    ap.add_argument("--out", required=True)
+    ap.add_argument("--host", action="append", default=None)
+    ap.add_argument("--days", type=int, default=3650)
+    a = ap.parse_args()
+    os.makedirs(a.out, exist_ok=True)
+    SSLConfigurator._generate_self_signed(os.path.join(a.out, "server-cert.pem"), os.path.join(a.out, "server-key.pem"),
+                                          tuple(a.host or ["localhost"]), a.days)
+    print("wrote", a.out)

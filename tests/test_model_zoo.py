@@ -72,3 +72,30 @@ def test_family_trains_and_round_trips(name):
         assert a.name == b.name and a.plaintext_tensor.tensor_spec.value == b.plaintext_tensor.tensor_spec.value
     res = ops.evaluate_model(ds, batch_size=4)
     assert np.isfinite(res["loss"])
+
+
+def test_callbacks_step_counter_stops_exactly_and_profiler_records():
+    from metisfl_b200.models.callbacks import PerformanceProfiler, StepCounter
+    np.random.seed(0)
+    x, y = np.random.randn(40, 28, 28).astype("f4"), np.random.randint(0, 10, 40)
+    ds = ModelDatasetClassification(x=x, y=y, size=40)
+    ops = TorchModelOps(model=zoo.MnistFC(), device="cpu")
+    counter, prof = StepCounter(3), PerformanceProfiler("cpu")
+    done = ops.train_model(ds, _task(100), _hyper(4), callbacks=[counter, prof])
+    assert counter.steps_counter == 3 and done.execution_metadata.completed_batches == 3  # not total_steps + 1 (Q11)
+    assert len(prof.batches_wall_clock_time_sec) == 3 and len(prof.epochs_wall_clock_time_sec) == 1
+
+
+def test_fedprox_optimizer_matches_closed_form():
+    from metisfl_b200.optim import FedProx
+    torch.manual_seed(0)
+    w = torch.nn.Parameter(torch.randn(17))
+    opt = FedProx([w], learning_rate=0.1, proximal_term=0.5)
+    w0 = w.detach().clone()
+    ref = w0.clone()
+    for _ in range(3):
+        opt.zero_grad()
+        (w ** 2).sum().backward()
+        opt.step()
+        ref = ref - 0.1 * (2 * ref + 0.5 * (ref - w0))
+    torch.testing.assert_close(w.detach(), ref)
