@@ -149,6 +149,24 @@ int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda,
 int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, int r, int s,
                           int stride, int pad, void* stream);
 
+/* ---- K14: fused BatchNorm2d (+ residual add) (+ ReLU), NHWC bf16 activations viewed as [m, c] rows
+ * (m = N*H*W, c a power of two in [8, 2048]); fp32 affine / statistics (csrc/kernels/bn_relu.cu).
+ * forward : training != 0: batch statistics (saved to save_mean / save_invstd, running statistics and
+ *           num_batches_tracked updated in place), else running statistics;
+ *           y = relu?(bn(x) + residual?) - residual may be NULL.
+ * backward: g = relu ? dy * (y > 0) : dy; dx = BN backward of g; dres (may be NULL) = g;
+ *           dgamma / dbeta (may be NULL) are overwritten, or accumulated into when accumulate != 0.
+ * workspace: mfl_bn_workspace_bytes(m, c) bytes of device memory, contents irrelevant on entry.
+ * Replaces the framework normalisation / activation kernels under keras_model_ops.py:156. */
+size_t mfl_bn_workspace_bytes(int m, int c);
+int mfl_bn_fwd(void* y, const void* x, const void* residual, const float* gamma, const float* beta,
+               float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
+               float* save_invstd, float* workspace, size_t workspace_bytes, int m, int c, float eps,
+               float momentum, int training, int relu, void* stream);
+int mfl_bn_bwd(void* dx, void* dres, float* dgamma, float* dbeta, int accumulate, const void* dy, const void* y,
+               const void* x, const float* gamma, const float* save_mean, const float* save_invstd,
+               float* workspace, size_t workspace_bytes, int m, int c, int relu, void* stream);
+
 /* ---- K5-K9: RNS-CKKS on the GPU (csrc/ckks/ckks_kernels.cu) ----------------------------------
  * Behavioural spec: encryption/palisade/ckks_scheme.cc:110-252 (Encrypt / ComputeWeightedAverage /
  * Decrypt) with the ciphertext layout of csrc/ckks/ckks_common.h: [ct][poly 0..1][limb][N] uint64 in

@@ -1,11 +1,14 @@
 """ResNet-18 for 32x32 inputs (CIFAR-10 variant: 3x3 stem, no max-pool), 11 173 962 parameters
 plus BatchNorm running statistics.  The reference's closest model is a 1.6 M-parameter Keras CNN
 with BatchNorm (``examples/keras/models/cifar_cnn.py:21-53``); ResNet-18 is the north-star config
-#2 (BASELINE.json).  ``channels_last`` keeps convolutions on the NHWC tensor-core path.
+#2 (BASELINE.json).  ``channels_last`` keeps convolutions on the NHWC tensor-core path; every BatchNorm (+ residual add) (+ ReLU)
+group is one call of the fused kernel family K14 (``metisfl_b200/ops/bn.py``) on CUDA.
 """
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+
+from metisfl_b200.ops.bn import bn_act
 
 
 class BasicBlock(nn.Module):
@@ -22,9 +25,9 @@ class BasicBlock(nn.Module):
             self.shortcut = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
 
     def forward(self, x):
-        out = F.relu(self.bn1(self.conv1(x)), inplace=True)
-        out = self.bn2(self.conv2(out))
-        return F.relu(out + (x if self.shortcut is None else self.shortcut(x)), inplace=True)
+        out = bn_act(self.bn1, self.conv1(x))
+        skip = x if self.shortcut is None else bn_act(self.shortcut[1], self.shortcut[0](x), relu=False)
+        return bn_act(self.bn2, self.conv2(out), residual=skip)  # BN + residual add + ReLU in one pass (K14)
 
 
 class ResNet18(nn.Module):
@@ -41,7 +44,7 @@ class ResNet18(nn.Module):
         self.fc = nn.Linear(cin, num_classes)
 
     def forward(self, x):
-        x = F.relu(self.bn1(self.conv1(x)), inplace=True)
+        x = bn_act(self.bn1, self.conv1(x))
         x = self.layers(x)
         x = F.adaptive_avg_pool2d(x, 1).flatten(1)
         return self.fc(x)
