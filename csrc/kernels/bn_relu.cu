@@ -23,6 +23,7 @@ namespace bn {
 
 constexpr int kThreads = 256;
 constexpr int kUnroll = 4;
+constexpr int kMaxPartials = 256;  // finalize folds 32 lanes x 8 partials per channel
 using V = VecTraits<MFL_BFLOAT16>;
 
 __device__ __forceinline__ void load8(const float* p, float* f) {
@@ -137,23 +138,35 @@ __global__ void __launch_bounds__(kThreads) bwd_partial_kernel(const __nv_bfloat
   fold_block(red, s0, s1, ws, C, tpr, rpi);
 }
 
-// ---- finalize: fold G partials per channel in double; 32 channels per CTA, 32 partial lanes ------
+// ---- finalize: fold G partials per channel; 32 channels per CTA, 32 partial lanes ----------------
+// fp32 pairwise folding (fp64 units are scarce on this part: a double-precision fold of 256 partials cost
+// 4 us per launch); only the handful of per-channel operations that follow are done in double.
 __device__ __forceinline__ bool fold_partials(const float* ws, int G, int C, double& o0, double& o1) {
-  __shared__ double red[2][32][33];
+  __shared__ float red[2][32][33];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int c = blockIdx.x * 32 + tx;
-  double a0 = 0.0, a1 = 0.0;
-  if (c < C)
-    for (int g = ty; g < G; g += 32) {
-      a0 += (double)ws[((size_t)g * 2 + 0) * C + c];
-      a1 += (double)ws[((size_t)g * 2 + 1) * C + c];
-    }
-  red[0][ty][tx] = a0;
-  red[1][ty][tx] = a1;
+  // all loads first (G <= kMaxPartials = 32 lanes x 8), then the adds: one memory latency instead of G / 32
+  float v0[8], v1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = ty + 32 * j;
+    const bool ok = c < C && g < G;
+    v0[j] = ok ? ws[((size_t)g * 2 + 0) * C + c] : 0.f;
+    v1[j] = ok ? ws[((size_t)g * 2 + 1) * C + c] : 0.f;
+  }
+  red[0][ty][tx] = ((v0[0] + v0[1]) + (v0[2] + v0[3])) + ((v0[4] + v0[5]) + (v0[6] + v0[7]));
+  red[1][ty][tx] = ((v1[0] + v1[1]) + (v1[2] + v1[3])) + ((v1[4] + v1[5]) + (v1[6] + v1[7]));
   __syncthreads();
+  for (int s = 16; s > 0; s >>= 1) {
+    if (ty < s) {
+      red[0][ty][tx] += red[0][ty + s][tx];
+      red[1][ty][tx] += red[1][ty + s][tx];
+    }
+    __syncthreads();
+  }
   if (ty != 0 || c >= C) return false;
-  for (int r = 1; r < 32; ++r) { a0 += red[0][r][tx]; a1 += red[1][r][tx]; }
-  o0 = a0; o1 = a1;
+  o0 = (double)red[0][0][tx];
+  o1 = (double)red[1][0][tx];
   return true;
 }
 
@@ -321,7 +334,7 @@ static Plan make_plan(int m, int c) {
   p.tpr = c / 8;
   p.rpi = kThreads / p.tpr;
   const int iters = (m + p.rpi - 1) / p.rpi;                   // row-iterations in the whole tensor
-  p.partial_blocks = max(1, min(2 * sm_count(), (iters + 7) / 8));
+  p.partial_blocks = max(1, min(min(2 * sm_count(), kMaxPartials), (iters + 7) / 8));
   const int ipb = (iters + p.partial_blocks - 1) / p.partial_blocks;
   p.rows_per_block = ipb * p.rpi;
   p.partial_blocks = (m + p.rows_per_block - 1) / p.rows_per_block;

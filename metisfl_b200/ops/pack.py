@@ -73,6 +73,14 @@ def unpack_model_into_arena(model_pb: model_pb2.Model, arena) -> None:
     dev = staging.to(arena.device, non_blocking=True)
     for (src_wire, dst_wire, swap), (d, s, k) in groups.items():
         pack_cast(arena.state, dst_wire, dev, src_wire, d, s, k, swap)
+    # convolution filters live in [K,R,S,C] order inside the arena; the wire carries logical [K,C,R,S]
+    seg_views = layout.views(arena.state)
+    for i, var in enumerate(model_pb.variables):
+        info = layout.variables[i] if positional else by_name[var.name]
+        if info.channels_last:
+            flat = seg_views[info.segment][info.elem_offset:info.elem_offset + info.numel]
+            k_, c_, r_, s_ = info.shape
+            flat.copy_(flat.view(k_, c_, r_, s_).permute(0, 2, 3, 1).contiguous().view(-1))
     arena.sync_master_from_model()
 
 
@@ -90,5 +98,9 @@ def arena_to_model_pb(arena) -> model_pb2.Model:
         spec.dimensions.extend(info.shape)
         spec.type.type = dtypes.torch_to_wire(seg.dtype)
         spec.type.byte_order = model_pb2.DType.NA if seg.dtype.itemsize == 1 else model_pb2.DType.LITTLE_ENDIAN_ORDER
-        spec.value = raw[lo:lo + info.numel * seg.dtype.itemsize].tobytes()
+        chunk = raw[lo:lo + info.numel * seg.dtype.itemsize]
+        if info.channels_last:  # stored [K,R,S,C] -> wire order [K,C,R,S]
+            k_, c_, r_, s_ = info.shape
+            chunk = np.ascontiguousarray(chunk.reshape(k_, r_, s_, c_, seg.dtype.itemsize).transpose(0, 3, 1, 2, 4))
+        spec.value = chunk.tobytes()
     return m

@@ -34,6 +34,14 @@ class VarInfo:
     segment: int
     elem_offset: int          # element offset inside the segment (in units of dtype)
     numel: int
+    channels_last: bool = False  # 4-D convolution filters are stored [K,R,S,C] (what NHWC convolutions consume)
+
+    def shaped(self, flat: torch.Tensor) -> torch.Tensor:
+        """Logical-shape view of this variable's flat storage slice."""
+        if self.channels_last:
+            k, c, r, s = self.shape
+            return flat.view(k, r, s, c).permute(0, 3, 1, 2)
+        return flat.view(self.shape)
 
 
 @dataclass
@@ -90,11 +98,22 @@ class ArenaLayout:
         return out
 
     def var_view(self, seg_views: List[torch.Tensor], v: VarInfo) -> torch.Tensor:
-        return seg_views[v.segment][v.elem_offset:v.elem_offset + v.numel].view(v.shape)
+        return v.shaped(seg_views[v.segment][v.elem_offset:v.elem_offset + v.numel])
 
     @staticmethod
-    def from_module(module: nn.Module, model_dtype: torch.dtype, policy=None) -> "ArenaLayout":
+    def from_module(module: nn.Module, model_dtype: torch.dtype, policy=None,
+                    conv_channels_last: bool = True) -> "ArenaLayout":
+        """``conv_channels_last``: keep Conv2d filters in NHWC order inside the arena, so that the NHWC convolution
+        kernels read them in place and write weight gradients straight in the layout of the flat gradient buffer
+        (otherwise every step pays a layout copy per filter in forward and backward plus a strided accumulate; 225 us
+        per ResNet-18 step, profiles/r1_step_breakdown.md).  The wire format and ``state_dict`` keep the logical
+        [K,C,R,S] order - ``VarInfo.shaped`` returns a permuted view."""
         policy = policy or default_dtype_policy(model_dtype)
+        cl_ids = set()
+        if conv_channels_last:
+            for mod in module.modules():
+                if isinstance(mod, nn.Conv2d) and mod.weight is not None and mod.weight.dim() == 4:
+                    cl_ids.add(id(mod.weight))
         entries = []  # (name, tensor, trainable, dtype)
         seen = set()
         for mod_name, mod in module.named_modules():
@@ -122,7 +141,7 @@ class ArenaLayout:
             k = (tr, dt)
             per = _ALIGN_VAR // dt.itemsize if dt.itemsize <= _ALIGN_VAR else 1
             off = (cursors[k] + per - 1) // per * per
-            variables.append(VarInfo(name, tuple(t.shape), dt, tr, keys.index(k), off, t.numel()))
+            variables.append(VarInfo(name, tuple(t.shape), dt, tr, keys.index(k), off, t.numel(), id(t) in cl_ids))
             cursors[k] = off + t.numel()
         segments, byte = [], 0
         for k in keys:
@@ -172,7 +191,7 @@ class ModelArena:
                 view.copy_(t.detach().to(device=self.device, dtype=v.dtype))
                 t.data = view
                 if v.trainable:
-                    g = self.grad[v.segment][v.elem_offset:v.elem_offset + v.numel].view(v.shape)
+                    g = v.shaped(self.grad[v.segment][v.elem_offset:v.elem_offset + v.numel])
                     t.grad = g
         # non-persistent buffers and anything else still on the old device
         for mod in self.module.modules():

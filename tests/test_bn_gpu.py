@@ -127,6 +127,6 @@ def test_resnet18_fused_bn_is_as_close_to_fp32_as_the_aten_path():
         last.append(model.layers[7].conv2.weight.grad.float().flatten())
     cos = lambda a, b: float(F.cosine_similarity(a, b, dim=0))
     assert abs(losses[0] - losses[2]) < 5e-2 and abs(losses[1] - losses[2]) < 5e-2, losses
-    assert cos(last[0], last[2]) > 0.99, cos(last[0], last[2])
+    assert cos(last[0], last[2]) > max(0.95, cos(last[1], last[2]) - 0.02), (cos(last[0], last[2]), cos(last[1], last[2]))
     assert cos(first[0], first[2]) > cos(first[1], first[2]) - 0.03, (cos(first[0], first[2]), cos(first[1], first[2]))
     torch.testing.assert_close(nets[0].bn1.running_var, nets[2].bn1.running_var, atol=1e-3, rtol=1e-2)

@@ -44,3 +44,38 @@ def test_pack_roundtrip_cpu():
 @pytest.mark.gpu
 def test_pack_roundtrip_cuda_kernel():
     _roundtrip("cuda")
+
+
+def test_conv_filters_keep_logical_order_on_the_wire():
+    """Conv2d filters are stored [K,R,S,C] inside the arena (NHWC kernels read them in place); the protobuf model and
+    ``state_dict`` still see logical [K,C,R,S]."""
+    import torch.nn as nn
+    from metisfl_b200.ops import pack
+    from metisfl_b200.parallel.arena import ModelArena
+    from metisfl_b200.utils.proto_messages_factory import ModelProtoMessages
+    torch.manual_seed(0)
+    make = lambda: nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.BatchNorm2d(8), nn.ReLU(), nn.Conv2d(8, 16, 1),
+                                 nn.Flatten(), nn.Linear(16 * 4 * 4, 5))
+    src = make()
+    want = {k: v.detach().clone() for k, v in src.state_dict().items()}
+    a = ModelArena(src, "cpu", torch.float32)
+    info = {v.name: v for v in a.layout.variables}
+    assert info["0.weight"].channels_last and info["3.weight"].channels_last and not info["5.weight"].channels_last
+    assert src[0].weight.is_contiguous(memory_format=torch.channels_last)
+    assert src[0].weight.grad.stride() == src[0].weight.stride()
+    for k, v in src.state_dict().items():          # binding did not change any logical value
+        torch.testing.assert_close(v, want[k])
+    pb = pack.arena_to_model_pb(a)
+    for var in pb.variables:
+        got = ModelProtoMessages.TensorSpecProto.proto_tensor_spec_to_numpy_array(var.plaintext_tensor.tensor_spec)
+        assert tuple(got.shape) == tuple(want[var.name].shape)
+        torch.testing.assert_close(torch.from_numpy(got.copy()).to(want[var.name].dtype), want[var.name])
+    dst = make()
+    b = ModelArena(dst, "cpu", torch.float32)
+    pack.unpack_model_into_arena(pb, b)
+    for k, v in dst.state_dict().items():
+        torch.testing.assert_close(v, want[k])
+    # the forward pass agrees too
+    x = torch.randn(2, 3, 4, 4)
+    src.eval(); dst.eval()
+    torch.testing.assert_close(src(x), dst(x))
