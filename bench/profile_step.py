@@ -17,6 +17,7 @@ batch = int(os.environ.get("BATCH", "128"))
 conv = os.environ.get("B200_CONV", "0") == "1"
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
+torch.backends.cudnn.benchmark = os.environ.get("CUDNN_BENCHMARK", "1") == "1"
 model = ResNet18()
 if conv:
     from metisfl_b200.ops.conv import use_b200_conv

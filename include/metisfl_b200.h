@@ -157,15 +157,20 @@ int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, i
  * backward: g = relu ? dy * (y > 0) : dy; dx = BN backward of g; dres (may be NULL) = g;
  *           dgamma / dbeta (may be NULL) are overwritten, or accumulated into when accumulate != 0.
  * workspace: mfl_bn_workspace_bytes(m, c) bytes of device memory, contents irrelevant on entry.
+ * barrier  : NULL -> three launches per direction (partials, finalize, apply).  Otherwise MFL_BN_BARRIER_WORDS device
+ *            uint32 words (two-level arrival counters + generation) that were zero when first used (the kernels keep them consistent): the three phases then run as ONE
+ *            cooperative launch separated by grid barriers - a dependent launch costs more than a whole phase of the
+ *            small layers.  One barrier must not be shared by calls that can run concurrently.
  * Replaces the framework normalisation / activation kernels under keras_model_ops.py:156. */
+#define MFL_BN_BARRIER_WORDS (64 + 32 * 32)
 size_t mfl_bn_workspace_bytes(int m, int c);
 int mfl_bn_fwd(void* y, const void* x, const void* residual, const float* gamma, const float* beta,
                float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
-               float* save_invstd, float* workspace, size_t workspace_bytes, int m, int c, float eps,
-               float momentum, int training, int relu, void* stream);
+               float* save_invstd, float* workspace, size_t workspace_bytes, unsigned int* barrier, int m, int c,
+               float eps, float momentum, int training, int relu, void* stream);
 int mfl_bn_bwd(void* dx, void* dres, float* dgamma, float* dbeta, int accumulate, const void* dy, const void* y,
                const void* x, const float* gamma, const float* save_mean, const float* save_invstd,
-               float* workspace, size_t workspace_bytes, int m, int c, int relu, void* stream);
+               float* workspace, size_t workspace_bytes, unsigned int* barrier, int m, int c, int relu, void* stream);
 
 /* ---- K5-K9: RNS-CKKS on the GPU (csrc/ckks/ckks_kernels.cu) ----------------------------------
  * Behavioural spec: encryption/palisade/ckks_scheme.cc:110-252 (Encrypt / ComputeWeightedAverage /

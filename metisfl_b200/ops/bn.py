@@ -28,14 +28,31 @@ def _bind():
         vp, i, f, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
         L.mfl_bn_workspace_bytes.restype = sz
         L.mfl_bn_workspace_bytes.argtypes = [i, i]
-        L.mfl_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, i, i, f, f, i, i, vp]
-        L.mfl_bn_bwd.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, sz, i, i, i, vp]
+        L.mfl_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp, i, i, f, f, i, i, vp]
+        L.mfl_bn_bwd.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, sz, vp, i, i, i, vp]
         _BOUND = True
     return L
 
 
 def _ptr(t):
     return None if t is None else t.data_ptr()
+
+
+_BAR_WORDS = 64 + 32 * 32  # kBarWords in csrc/kernels/bn_relu.cu
+# One cooperative launch per direction (grid barriers between the phases) instead of three.  Measured on B200
+# (bench/bn_bench.py, CUDA-graph replays, fwd+bwd): 51.8 vs 45.4 us at 128x64x32x32, 24.8 vs 22.8 us at 128x512x4x4 -
+# the two grid barriers cost as much as the two launch boundaries they replace, so three launches stay the default.
+FUSED_FINALIZE = False
+
+
+def _tickets(bn: nn.Module, device) -> torch.Tensor:
+    """Grid-barrier state {count, generation} x {forward, backward}, owned by the module: a module never runs
+    concurrently with itself, which is the sharing rule of the barrier words (``include/metisfl_b200.h``)."""
+    t = bn.__dict__.get("_mfl_tickets")
+    if t is None or t.device != device:
+        t = torch.zeros(2 * _BAR_WORDS, dtype=torch.int32, device=device)  # forward barrier, backward barrier
+        bn.__dict__["_mfl_tickets"] = t
+    return t
 
 
 def supported(bn: nn.Module, x: torch.Tensor) -> bool:
@@ -51,7 +68,7 @@ class _BNActFn(torch.autograd.Function):
     """x, residual: NHWC bf16.  ``state`` carries the module's buffers (updated in place, never differentiated)."""
 
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, state, training, momentum, eps, relu):
+    def forward(ctx, x, residual, weight, bias, state, training, momentum, eps, relu, tickets):
         L = _bind()
         n, c, h, w = x.shape
         m = n * h * w
@@ -68,12 +85,13 @@ class _BNActFn(torch.autograd.Function):
             save_invstd = torch.empty(c, dtype=torch.float32, device=x.device)
         rc = L.mfl_bn_fwd(y.data_ptr(), x.data_ptr(), _ptr(residual), _ptr(weight), _ptr(bias), _ptr(rm), _ptr(rv),
                           _ptr(nbt) if training else None, _ptr(save_mean), _ptr(save_invstd), ws.data_ptr(), ws_bytes,
-                          m, c, float(eps), float(momentum or 0.0), int(training), int(relu), _lib.stream_ptr())
-        _lib.check(rc, "mfl_bn_fwd", 3 if training else 2)
+                          _ptr(tickets), m, c, float(eps), float(momentum or 0.0), int(training), int(relu),
+                          _lib.stream_ptr())
+        _lib.check(rc, "mfl_bn_fwd", 1 if (tickets is not None and training) else (3 if training else 2))
         if training:
             ctx.save_for_backward(x, y if relu else None, weight, save_mean, save_invstd)
             ctx.relu, ctx.has_res, ctx.has_bias = relu, residual is not None, bias is not None
-            ctx.bias_ref = bias
+            ctx.bias_ref, ctx.tickets = bias, tickets
         return y
 
     @staticmethod
@@ -104,12 +122,13 @@ class _BNActFn(torch.autograd.Function):
             pg = pb = None
             acc = 0
         rc = L.mfl_bn_bwd(dx.data_ptr(), _ptr(dres), pg, pb, acc, gy.data_ptr(), _ptr(y), x.data_ptr(), _ptr(weight),
-                          save_mean.data_ptr(), save_invstd.data_ptr(), ws.data_ptr(), ws_bytes, m, c, int(ctx.relu),
+                          save_mean.data_ptr(), save_invstd.data_ptr(), ws.data_ptr(), ws_bytes,
+                          None if ctx.tickets is None else ctx.tickets.data_ptr() + 4 * _BAR_WORDS, m, c, int(ctx.relu),
                           _lib.stream_ptr())
-        _lib.check(rc, "mfl_bn_bwd", 3)
+        _lib.check(rc, "mfl_bn_bwd", 1 if ctx.tickets is not None else 3)
         if dgamma is not None:
             dgamma, dbeta = dgamma.to(weight.dtype), (dbeta.to(bias.dtype) if bias is not None else None)
-        return dx, dres, dgamma, dbeta, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
 
 
 def bn_act(bn: nn.Module, x: torch.Tensor, residual: torch.Tensor = None, relu: bool = True) -> torch.Tensor:
@@ -117,7 +136,8 @@ def bn_act(bn: nn.Module, x: torch.Tensor, residual: torch.Tensor = None, relu: 
     if supported(bn, x) and (residual is None or (residual.dtype == x.dtype and residual.shape == x.shape)):
         use_batch_stats = bn.training or bn.running_mean is None
         state = (bn.running_mean, bn.running_var, bn.num_batches_tracked) if bn.track_running_stats else (None, None, None)
-        return _BNActFn.apply(x, residual, bn.weight, bn.bias, state, use_batch_stats, bn.momentum, bn.eps, relu)
+        return _BNActFn.apply(x, residual, bn.weight, bn.bias, state, use_batch_stats, bn.momentum, bn.eps, relu,
+                              _tickets(bn, x.device) if FUSED_FINALIZE else None)
     y = bn(x)
     if residual is not None:
         y = y + residual

@@ -6,6 +6,18 @@ import torch.nn.functional as F
 
 pytestmark = pytest.mark.gpu
 
+
+
+@pytest.fixture(params=["cooperative", "three_launches"], autouse=True)
+def finalize_mode(request):
+    """Both back-ends: one cooperative launch with grid barriers, and the three-launch sequence."""
+    from metisfl_b200.ops import bn as fbn
+    old = fbn.FUSED_FINALIZE
+    fbn.FUSED_FINALIZE = request.param == "cooperative"
+    yield
+    fbn.FUSED_FINALIZE = old
+
+
 SHAPES = [(128, 64, 32, 32), (32, 128, 16, 16), (7, 256, 5, 3), (16, 512, 4, 4), (3, 8, 9, 11), (2, 2048, 2, 2),
           (2, 64, 1, 1), (5, 32, 17, 13)]
 
