@@ -22,6 +22,9 @@ model = ResNet18()
 if conv:
     from metisfl_b200.ops.conv import use_b200_conv
     use_b200_conv(model)
+elif os.environ.get("OVERLAP_WGRAD", "1") == "1":
+    from metisfl_b200.ops.conv import use_overlapped_wgrad
+    use_overlapped_wgrad(model)
 arena = ModelArena(model, dev, torch.bfloat16)
 x = torch.randn(batch, 3, 32, 32, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
 y = torch.randint(0, 10, (batch,), device=dev)

@@ -134,6 +134,9 @@ class TorchModelOps(ModelOps):
         if loss_fn is None:
             loss_fn = module.loss_fn if _overrides(module, "loss_fn") else cross_entropy_loss
         self.loss_fn = loss_fn
+        if self.device.type == "cuda":
+            from metisfl_b200.ops import conv as _conv
+            _conv.use_overlapped_wgrad(module)  # weight gradients overlap the dgrad chain on a side stream
         if self.device.type == "cuda" and model_dtype == torch.bfloat16:
             from metisfl_b200.ops import gemm as _gemm
             _gemm.use_b200_linear(module)  # Linear layers on the tcgen05 GEMM (K10)

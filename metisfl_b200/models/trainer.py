@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from metisfl_b200.ops import conv as _conv_ops
 from metisfl_b200.ops.optim import OptimHyper, optimizer_step
 from metisfl_b200.parallel.arena import ModelArena
 
@@ -77,6 +78,8 @@ class LocalTrainer:
         out = self.module(x)
         loss = self.loss_fn(out, y)
         loss.backward()
+        if self.device.type == "cuda":
+            _conv_ops.join()  # weight gradients issued on the side stream (ops/conv.py)
         return loss.detach()
 
     def _capture(self, x, y):

@@ -102,3 +102,83 @@ def use_b200_conv(module: nn.Module) -> nn.Module:
         if type(m) is nn.Conv2d:
             m.__class__ = B200Conv2d
     return module
+
+
+# ---- weight gradients on a side stream -------------------------------------------------------------------------
+# In backward the data gradient of a convolution is on the critical path (the previous layer waits for it) while the
+# weight gradient is only needed by the optimizer at the very end.  Autograd would still run both back to back on
+# one stream; here the weight-gradient convolution is issued on a side stream and accumulates straight into the flat
+# gradient buffer, so it overlaps the dgrad -> BatchNorm-backward chain of the following layers.  Inside a CUDA
+# graph capture the fork / join become parallel branches of the graph.  ``join()`` must run before the gradients
+# are consumed (``LocalTrainer`` does it right after ``loss.backward()``).
+class _SideStream:
+    def __init__(self):
+        self.streams = {}
+        self.pending = []   # tensors the side stream still reads
+        self.dirty = set()
+
+    def stream(self, device) -> "torch.cuda.Stream":
+        s = self.streams.get(device)
+        if s is None:
+            s = self.streams[device] = torch.cuda.Stream(device=device)
+        return s
+
+
+_SIDE = _SideStream()
+OVERLAP_WGRAD = True
+
+
+def join():
+    """Make the current stream wait for every weight gradient issued on the side stream."""
+    for device in list(_SIDE.dirty):
+        torch.cuda.current_stream(device).wait_stream(_SIDE.streams[device])
+    _SIDE.dirty.clear()
+    _SIDE.pending.clear()
+
+
+class _OverlapConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, stride, padding, dilation, groups):
+        ctx.save_for_backward(x, w)
+        ctx.cfg = (list(stride), list(padding), list(dilation), groups)
+        return torch.ops.aten.convolution(x, w, None, stride, padding, dilation, False, [0, 0], groups)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        stride, padding, dilation, groups = ctx.cfg
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gw = None
+        direct = need_w and OVERLAP_WGRAD and w.grad is not None and w.grad.dtype == w.dtype
+        if direct:
+            main = torch.cuda.current_stream(x.device)
+            side = _SIDE.stream(x.device)
+            side.wait_stream(main)                       # gy (and x) are ready on the main stream
+            with torch.cuda.stream(side):
+                g = torch.ops.aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0], groups,
+                                                        [False, True, False])[1]
+                w.grad.add_(g)
+            _SIDE.pending.append((gy, x, g))             # keep the operands alive until join()
+            _SIDE.dirty.add(x.device)
+            need_w = False
+        gx = None
+        if need_x or need_w:
+            gx, gw, _ = torch.ops.aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0],
+                                                            groups, [need_x, need_w, False])
+        return gx, gw, None, None, None, None
+
+
+class OverlappedConv2d(nn.Conv2d):
+    def forward(self, x):
+        if (x.is_cuda and self.bias is None and self.padding_mode == "zeros" and not isinstance(self.padding, str)
+                and torch.is_grad_enabled()):
+            return _OverlapConvFn.apply(x, self.weight, self.stride, self.padding, self.dilation, self.groups)
+        return super().forward(x)
+
+
+def use_overlapped_wgrad(module: nn.Module) -> nn.Module:
+    """Re-class bias-free ``nn.Conv2d`` layers so their weight gradients run on the side stream."""
+    for m in module.modules():
+        if type(m) is nn.Conv2d and m.bias is None:
+            m.__class__ = OverlappedConv2d
+    return module

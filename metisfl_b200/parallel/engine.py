@@ -74,6 +74,7 @@ class EngineConfig:
     channels_last: bool = True
     use_cuda_graph: Optional[bool] = None
     fused_blocks: int = 296
+    overlap_wgrad: bool = True           # convolution weight gradients on a side stream (ops/conv.py), CUDA only
     use_b200_linear: bool = True         # nn.Linear forward/backward on the tcgen05 GEMM (K10) when bf16 on CUDA
     seed: int = 1234
 
@@ -94,6 +95,9 @@ class FederationEngine:
         module = model_factory()
         if cfg.channels_last and self.device.type == "cuda":
             module = module.to(memory_format=torch.channels_last)
+        if cfg.overlap_wgrad and self.device.type == "cuda":
+            from metisfl_b200.ops import conv as _conv
+            _conv.use_overlapped_wgrad(module)
         if cfg.use_b200_linear and self.device.type == "cuda" and cfg.model_dtype == torch.bfloat16:
             from metisfl_b200.ops import gemm as _gemm
             _gemm.use_b200_linear(module)
