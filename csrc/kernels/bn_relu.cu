@@ -46,6 +46,13 @@ __device__ __forceinline__ void load8_cg(const float* p, float* f) {  // written
   const float4 b = __ldcg(reinterpret_cast<const float4*>(p + 4));
   f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
 }
+// Programmatic dependent launch: the three kernels of one direction are launched back to back with the
+// programmatic-stream-serialization attribute; a dependent grid may start (and sit in pdl_wait) while its producer
+// is still running, which hides most of the ~3.8 us dependent-launch latency.  pdl_wait() returns once every
+// prerequisite grid has completed and its writes are visible, so the data flow is unchanged.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ uint4 ld_row(const __nv_bfloat16* p, bool ok) {
   return ok ? ld_stream(p) : make_uint4(0, 0, 0, 0);
 }
@@ -241,6 +248,7 @@ __global__ void __launch_bounds__(kThreads) stats_partial_kernel(const __nv_bflo
                                                                  float* __restrict__ ws, int M, int C,
                                                                  int rows_per_block) {
   __shared__ float red[kThreads * 16];
+  pdl_launch_dependents();
   const int tpr = C >> 3, rpi = kThreads / tpr;
   const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
   const int row0 = blockIdx.x * rows_per_block;
@@ -260,6 +268,7 @@ __global__ void __launch_bounds__(kThreads) bwd_partial_kernel(const __nv_bfloat
                                                                float* __restrict__ ws, int M, int C,
                                                                int rows_per_block) {
   __shared__ float red[kThreads * 16];
+  pdl_launch_dependents();
   const int tpr = C >> 3, rpi = kThreads / tpr;
   const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
   const int row0 = blockIdx.x * rows_per_block;
@@ -305,6 +314,8 @@ __device__ __forceinline__ bool fold_partials(const float* ws, int G, int C, flo
 __global__ void __launch_bounds__(1024) finalize_fwd_kernel(const float* __restrict__ ws, int G, int C, int M,
                                                             FwdFinal fin) {
   float s0, s1;
+  pdl_wait();
+  pdl_launch_dependents();
   if (blockIdx.x == 0 && threadIdx.x == 0 && threadIdx.y == 0 && fin.num_batches_tracked)
     *fin.num_batches_tracked += 1;
   if (!fold_partials(ws, G, C, s0, s1)) return;
@@ -314,6 +325,8 @@ __global__ void __launch_bounds__(1024) finalize_fwd_kernel(const float* __restr
 __global__ void __launch_bounds__(1024) finalize_bwd_kernel(const float* __restrict__ ws, int G, int C, int M,
                                                             BwdFinal fin) {
   float s0, s1;
+  pdl_wait();
+  pdl_launch_dependents();
   if (!fold_partials(ws, G, C, s0, s1)) return;
   finalize_bwd_channel(blockIdx.x * 32 + threadIdx.x, s0, s1, M, C, fin);
 }
@@ -337,6 +350,7 @@ __global__ void __launch_bounds__(kThreads) apply_fwd_kernel(const __nv_bfloat16
   const int tpr = C >> 3, rpi = kThreads / tpr;
   const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
   float sc[8], sh[8];
+  pdl_wait();
   load8(coef + tx * 8, sc);
   load8(coef + C + tx * 8, sh);
   rows_apply_fwd<RELU, RES>(x, res, y, C, (size_t)tx * 8, blockIdx.x * rpi + ty, M, gridDim.x * rpi, sc, sh);
@@ -356,6 +370,7 @@ __global__ void __launch_bounds__(kThreads) apply_bwd_kernel(const __nv_bfloat16
   float mu[8], is[8], a[8], b[8], cc[8];
   load8(mean + tx * 8, mu);
   load8(invstd + tx * 8, is);
+  pdl_wait();
   load8(coef + tx * 8, a);
   load8(coef + C + tx * 8, b);
   load8(coef + 2 * C + tx * 8, cc);
@@ -579,6 +594,22 @@ extern "C" size_t mfl_bn_workspace_bytes(int m, int c) {
 
 namespace {
 
+// Launch with the programmatic-stream-serialization attribute (see pdl_wait above).
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = getenv("MFL_BN_NO_PDL") ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 template <bool RELU, bool RES>
 int launch_coop_fwd(const __nv_bfloat16* x, const __nv_bfloat16* res, __nv_bfloat16* y, float* ws, int m, int c,
                     unsigned int* bar, bn::FwdFinal fin, cudaStream_t st) {
@@ -640,15 +671,17 @@ extern "C" int mfl_bn_fwd(void* y, const void* x, const void* residual, const fl
   }
   if (training) {
     bn::stats_partial_kernel<<<p.partial_blocks, bn::kThreads, 0, st>>>(xb, workspace, m, c, p.rows_per_block);
-    bn::finalize_fwd_kernel<<<(c + 31) / 32, dim3(32, 32), 0, st>>>(workspace, p.partial_blocks, c, m, fin);
+    MFL_CUDA(launch_pdl(bn::finalize_fwd_kernel, dim3((c + 31) / 32), dim3(32, 32), st, workspace, p.partial_blocks, c, m,
+                        fin));
   } else {
     bn::eval_coef_kernel<<<(c + 127) / 128, 128, 0, st>>>(c, gamma, beta, running_mean, running_var, coef, eps);
   }
-  const int g = p.apply_blocks;
-  if (relu && rb) bn::apply_fwd_kernel<true, true><<<g, bn::kThreads, 0, st>>>(xb, rb, yb, coef, m, c);
-  else if (relu) bn::apply_fwd_kernel<true, false><<<g, bn::kThreads, 0, st>>>(xb, rb, yb, coef, m, c);
-  else if (rb) bn::apply_fwd_kernel<false, true><<<g, bn::kThreads, 0, st>>>(xb, rb, yb, coef, m, c);
-  else bn::apply_fwd_kernel<false, false><<<g, bn::kThreads, 0, st>>>(xb, rb, yb, coef, m, c);
+  const dim3 g(p.apply_blocks), b(bn::kThreads);
+  const float* cf = coef;
+  if (relu && rb) MFL_CUDA(launch_pdl(bn::apply_fwd_kernel<true, true>, g, b, st, xb, rb, yb, cf, m, c));
+  else if (relu) MFL_CUDA(launch_pdl(bn::apply_fwd_kernel<true, false>, g, b, st, xb, rb, yb, cf, m, c));
+  else if (rb) MFL_CUDA(launch_pdl(bn::apply_fwd_kernel<false, true>, g, b, st, xb, rb, yb, cf, m, c));
+  else MFL_CUDA(launch_pdl(bn::apply_fwd_kernel<false, false>, g, b, st, xb, rb, yb, cf, m, c));
   MFL_CUDA(cudaGetLastError());
   return 0;
 }
@@ -685,16 +718,18 @@ extern "C" int mfl_bn_bwd(void* dx, void* dres, float* dgamma, float* dbeta, int
   else
     bn::bwd_partial_kernel<false><<<p.partial_blocks, bn::kThreads, 0, st>>>(xb, db, yb, save_mean, save_invstd,
                                                                               workspace, m, c, p.rows_per_block);
-  bn::finalize_bwd_kernel<<<(c + 31) / 32, dim3(32, 32), 0, st>>>(workspace, p.partial_blocks, c, m, fin);
-  const int g = p.apply_blocks;
+  MFL_CUDA(launch_pdl(bn::finalize_bwd_kernel, dim3((c + 31) / 32), dim3(32, 32), st, workspace, p.partial_blocks, c, m,
+                      fin));
+  const dim3 g(p.apply_blocks), b(bn::kThreads);
+  const float* cf = coef;
   if (relu && drb)
-    bn::apply_bwd_kernel<true, true><<<g, bn::kThreads, 0, st>>>(xb, db, yb, dxb, drb, save_mean, save_invstd, coef, m, c);
+    MFL_CUDA(launch_pdl(bn::apply_bwd_kernel<true, true>, g, b, st, xb, db, yb, dxb, drb, save_mean, save_invstd, cf, m, c));
   else if (relu)
-    bn::apply_bwd_kernel<true, false><<<g, bn::kThreads, 0, st>>>(xb, db, yb, dxb, drb, save_mean, save_invstd, coef, m, c);
+    MFL_CUDA(launch_pdl(bn::apply_bwd_kernel<true, false>, g, b, st, xb, db, yb, dxb, drb, save_mean, save_invstd, cf, m, c));
   else if (drb)
-    bn::apply_bwd_kernel<false, true><<<g, bn::kThreads, 0, st>>>(xb, db, yb, dxb, drb, save_mean, save_invstd, coef, m, c);
+    MFL_CUDA(launch_pdl(bn::apply_bwd_kernel<false, true>, g, b, st, xb, db, yb, dxb, drb, save_mean, save_invstd, cf, m, c));
   else
-    bn::apply_bwd_kernel<false, false><<<g, bn::kThreads, 0, st>>>(xb, db, yb, dxb, drb, save_mean, save_invstd, coef, m, c);
+    MFL_CUDA(launch_pdl(bn::apply_bwd_kernel<false, false>, g, b, st, xb, db, yb, dxb, drb, save_mean, save_invstd, cf, m, c));
   MFL_CUDA(cudaGetLastError());
   return 0;
 }

@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from metisfl_b200.ops import _lib
 from metisfl_b200.ops import conv as _conv_ops
 from metisfl_b200.ops.optim import OptimHyper, optimizer_step
 from metisfl_b200.parallel.arena import ModelArena
@@ -39,6 +40,7 @@ class LocalTrainer:
         self._graph_key = None
         self._static_x = self._static_y = self._static_loss = None
         self.launches_per_step = 0
+        self.graph_launches = 0
         self._alloc_state()
 
     # -- optimizer state -----------------------------------------------------------------------
@@ -99,8 +101,10 @@ class LocalTrainer:
             if g is not None:
                 g.zero_()
         self._graph = torch.cuda.CUDAGraph()
+        launches0 = _lib.LAUNCHES
         with torch.cuda.graph(self._graph):
             self._static_loss = self._fwd_bwd(self._static_x, self._static_y)
+        self.graph_launches = _lib.LAUNCHES - launches0  # library kernels (K10 / K14 ...) every replay launches
         # undo what warm-up and capture did to BatchNorm statistics etc.
         arena.state.copy_(saved)
         for g in arena.grad:
@@ -125,6 +129,7 @@ class LocalTrainer:
             if y.data_ptr() != self._static_y.data_ptr():
                 self._static_y.copy_(y, non_blocking=True)
             self._graph.replay()
+            _lib.LAUNCHES += self.graph_launches
             return self._static_loss
         return self._fwd_bwd(x, y)
 
