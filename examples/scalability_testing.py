@@ -39,12 +39,16 @@ if __name__ == "__main__":
     ap.add_argument("--width", type=int, default=100)
     ap.add_argument("--depth", type=int, default=10)
     ap.add_argument("--launcher", default="inprocess")
+    ap.add_argument("--echo", action="store_true",
+                    help="learners that only sleep and echo the model (the reference's learner_notrain_noeval backend)")
+    ap.add_argument("--echo_sleep_secs", type=float, default=0.5)
     a = ap.parse_args()
     env = EnvGen(os.path.join(here, "config", "template.yaml")).generate_localhost(a.rounds, a.learners)
     env.local_model_config.optimizer_config.optimizer_pb_kwargs["learning_rate"] = 0.0  # nothing trains
     env.evaluation_metric = "loss"
     session = DriverSession(env, Regressor(width=a.width, depth=a.depth), recipe, None, recipe, launcher=a.launcher,
-                            banner=False)
+                            banner=False, neural_engine="echo" if a.echo else "pytorch",
+                            echo_sleep_secs=a.echo_sleep_secs)
     stats = session.run(request_every_secs=1)
     md = [m for m in stats["federation_runtime_metadata"]["metadata"] if "completed_at" in m]
     agg = [m.get("model_aggregation_total_duration_ms", 0.0) for m in md]

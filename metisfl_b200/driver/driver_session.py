@@ -29,6 +29,7 @@ import torch
 from google.protobuf.json_format import MessageToDict
 
 from metisfl_b200.models.torch_model_ops import TorchModelOps, save_torch_model
+from metisfl_b200.proto import metis_pb2
 from metisfl_b200.utils import fedenv_parser, proto_messages_factory
 from metisfl_b200.utils.grpc_controller_client import GRPCControllerClient
 from metisfl_b200.utils.grpc_learner_client import GRPCLearnerClient
@@ -44,7 +45,9 @@ class DriverSessionBase(object):
 
     def __init__(self, fed_env, model, train_dataset_recipe_fn, validation_dataset_recipe_fn=None,
                  test_dataset_recipe_fn=None, working_dir="/tmp/metis/", launcher=None, model_dtype=None,
-                 banner=True):
+                 banner=True, neural_engine="pytorch", echo_sleep_secs=3.0):
+        # neural_engine="echo": learners that sleep ``echo_sleep_secs`` and echo the model back (controller load test)
+        self.neural_engine, self.echo_sleep_secs = neural_engine, echo_sleep_secs
         if banner:
             MetisASCIIArt.print()
         self.federation_environment = fed_env if isinstance(fed_env, fedenv_parser.FederationEnvironment) \
@@ -202,7 +205,8 @@ class DriverSessionBase(object):
             validation_dataset=learner.dataset_configs.validation_dataset_path,
             test_dataset=learner.dataset_configs.test_dataset_path,
             train_dataset_recipe=recipes[0], validation_dataset_recipe=recipes[1] or "",
-            test_dataset_recipe=recipes[2] or "", neural_engine="pytorch", device=device)
+            test_dataset_recipe=recipes[2] or "", neural_engine=self.neural_engine, device=device) + (
+                " --echo_sleep_secs={}".format(self.echo_sleep_secs) if self.neural_engine == "echo" else "")
 
     # -- launchers --------------------------------------------------------------------------------
     def _popen(self, name, cmd, extra_env=None):
@@ -237,12 +241,19 @@ class DriverSessionBase(object):
             from metisfl_b200.learner.learner import Learner
             from metisfl_b200.learner.learner_servicer import LearnerServicer
             dev = device or ("cuda:{}".format(learner.cuda_devices[0]) if learner.cuda_devices else None)
-            lrn = Learner(self._server_entity_pb(learner), self._server_entity_pb(self.federation_environment.controller),
-                          self._learners_he_scheme_config_pb, "pytorch", self._save_model_dir,
-                          learner.dataset_configs.train_dataset_path, recipes[0],
-                          learner.dataset_configs.validation_dataset_path, recipes[1] or "",
-                          learner.dataset_configs.test_dataset_path, recipes[2] or "", device=dev,
-                          learner_credentials_fp=os.path.join(self.working_dir, "learner_credentials"))
+            if self.neural_engine == "echo":
+                from metisfl_b200.learner.echo_learner import EchoLearner
+                lrn = EchoLearner(self._server_entity_pb(learner),
+                                  self._server_entity_pb(self.federation_environment.controller),
+                                  metis_pb2.HESchemeConfig(), sleep_secs=self.echo_sleep_secs,
+                                  learner_credentials_fp=os.path.join(self.working_dir, "learner_credentials"))
+            else:
+                lrn = Learner(self._server_entity_pb(learner), self._server_entity_pb(self.federation_environment.controller),
+                              self._learners_he_scheme_config_pb, "pytorch", self._save_model_dir,
+                              learner.dataset_configs.train_dataset_path, recipes[0],
+                              learner.dataset_configs.validation_dataset_path, recipes[1] or "",
+                              learner.dataset_configs.test_dataset_path, recipes[2] or "", device=dev,
+                              learner_credentials_fp=os.path.join(self.working_dir, "learner_credentials"))
             svc = LearnerServicer(lrn, servicer_workers=5)
             svc.init_servicer()
             t = threading.Thread(target=svc.wait_servicer, daemon=True)

@@ -12,6 +12,20 @@ def _from_hex(cls, hex_str):
 
 
 def init_learner(a, block=True):
+    if (a.neural_engine or "").lower() == "echo":  # load-test backend: sleeps and echoes the model (no training)
+        from metisfl_b200.learner.echo_learner import EchoLearner
+        learner = EchoLearner(
+            learner_server_entity=_from_hex(metis_pb2.ServerEntity,
+                                            a.learner_server_entity_protobuff_serialized_hexadecimal),
+            controller_server_entity=_from_hex(metis_pb2.ServerEntity,
+                                               a.controller_server_entity_protobuff_serialized_hexadecimal),
+            he_scheme_config_pb=metis_pb2.HESchemeConfig(), sleep_secs=a.echo_sleep_secs,
+            learner_credentials_fp=a.credentials_dir)
+        servicer = LearnerServicer(learner=learner, servicer_workers=5)
+        servicer.init_servicer()
+        if block:
+            servicer.wait_servicer()
+        return servicer
     learner = Learner(
         learner_server_entity=_from_hex(metis_pb2.ServerEntity, a.learner_server_entity_protobuff_serialized_hexadecimal),
         controller_server_entity=_from_hex(metis_pb2.ServerEntity,
@@ -45,6 +59,7 @@ def main():
     ap.add_argument("--device", type=str, default=None)
     ap.add_argument("--logical_learners", type=int, default=1)
     ap.add_argument("--credentials_dir", type=str, default="/tmp/metis/learner/")
+    ap.add_argument("--echo_sleep_secs", type=float, default=3.0, help="task duration of the echo backend")
     init_learner(ap.parse_args())
 
 

@@ -177,3 +177,20 @@ def test_engine_world_size_2_gloo(tmp_path):
                         "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
                        capture_output=True, text=True, timeout=300)
     assert "GLOO_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_echo_learners_drive_the_controller_without_training(tmp_path):
+    """The reference's fake backend (``test/learner_notrain_noeval.py``): learners sleep and echo the model, so the
+    rounds measure only the controller path; the community model stays equal to the initial one under FedAvg."""
+    torch.manual_seed(0)
+    model = FashionMnistMLP()
+    want = {k: v.clone() for k, v in model.state_dict().items()}
+    d = _env()
+    d["FederationEnvironment"]["TerminationSignals"]["FederationRounds"] = 3
+    s = DriverSession(FederationEnvironment(d), model, _recipe(16, 1), None, None, working_dir=str(tmp_path / "w"),
+                      launcher="inprocess", banner=False, neural_engine="echo", echo_sleep_secs=0.2)
+    stats = s.run(request_every_secs=0.3)
+    md = stats["federation_runtime_metadata"]["metadata"]
+    assert len(md) >= 3 and all(len(m["completed_by_learner_id"]) == 2 for m in md[:3])
+    tasks = stats["learners_models_results"]["learner_task"]
+    assert len(tasks) == 2
