@@ -215,6 +215,16 @@ void Controller::TaskFailed(const std::string& id, const std::string& what) {
   Log("RPC to learner %s failed: %s", id, what);
 }
 
+bool Controller::EvictLearner(const std::string& id, const std::string& why) {
+  {
+    std::lock_guard<std::mutex> l(mu_);
+    if (!learners_.count(id)) return false;
+    EvictLocked(id, why.c_str());
+  }
+  FlushOutbox();
+  return true;
+}
+
 // ---------------------------------------------------------------------------------------------
 void Controller::ScheduleInitialTask(const std::string& id) {
   {

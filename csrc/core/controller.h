@@ -142,6 +142,8 @@ class Controller {
   StatusOr LearnerCompletedTask(const std::string& id, const std::string& token, std::string model_bytes, TaskMeta meta);
   void EvaluationCompleted(const std::string& id, uint32_t eval_index, std::string evaluations_bytes);
   void TaskFailed(const std::string& id, const std::string& what);
+  // Failure detector hook (heartbeat): drop a learner that stopped answering; returns false if it was unknown.
+  bool EvictLearner(const std::string& id, const std::string& why);
 
   std::vector<LearnerRecord> GetLearners();
   ModelBytes CommunityModel();  // serialized FederatedModel

@@ -346,6 +346,7 @@ PYBIND11_MODULE(_core, m) {
         c.EvaluationCompleted(id, idx, std::move(s));
       })
       .def("task_failed", &Controller::TaskFailed, py::call_guard<py::gil_scoped_release>())
+      .def("evict_learner", &Controller::EvictLearner, py::call_guard<py::gil_scoped_release>())
       .def("get_learners", [](Controller& c) {
         std::vector<LearnerRecord> recs;
         { py::gil_scoped_release rel; recs = c.GetLearners(); }
@@ -356,6 +357,7 @@ PYBIND11_MODULE(_core, m) {
           d["auth_token"] = r.auth_token; d["server_entity"] = py::bytes(r.server_entity);
           d["dataset_spec"] = py::bytes(r.dataset_spec); d["num_training_examples"] = r.n_train;
           d["num_local_updates"] = r.num_local_updates;
+          d["public_certificate"] = py::bytes(r.endpoint.public_certificate);
           l.append(d);
         }
         return l;

@@ -117,6 +117,11 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             os.makedirs(self._snapshot_dir, exist_ok=True)
             self._resume_from_snapshot()
         self._evaluation_metrics = metis_pb2.EvaluationMetrics()
+        # failure detector: poll every learner's health RPC, evict after N consecutive misses
+        self._heartbeat_secs = float(os.environ.get("METISFL_HEARTBEAT_SECS", "0") or 0)
+        self._heartbeat_misses = max(1, int(os.environ.get("METISFL_HEARTBEAT_MISSES", "3")))
+        self._missed = {}
+        self._heartbeat_thread = None
 
     # -- server lifecycle -----------------------------------------------------------------------
     def start(self, max_workers: int = 16):
@@ -127,8 +132,42 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         if self._snapshot_dir:
             self._snapshot_thread = threading.Thread(target=self._snapshot_loop, daemon=True)
             self._snapshot_thread.start()
+        if self._heartbeat_secs > 0:
+            self._heartbeat_thread = threading.Thread(target=self._heartbeat_loop, daemon=True)
+            self._heartbeat_thread.start()
         MetisLogger.info("Controller listening on %s:%s", self.params_pb.server_entity.hostname,
                          self.params_pb.server_entity.port)
+
+    # -- heartbeat --------------------------------------------------------------------------------------
+    def heartbeat_once(self, timeout=2.0):
+        """One sweep of the failure detector; returns the ids evicted by it."""
+        evicted = []
+        for rec in self.core.get_learners():
+            lid = rec["id"]
+            try:
+                stub = self._stub_for(lid, rec["hostname"], rec["port"], rec.get("public_certificate", b""))
+                stub.GetServicesHealthStatus(service_common_pb2.GetServicesHealthStatusRequest(), timeout=timeout)
+                self._missed[lid] = 0
+            except Exception as e:
+                self._missed[lid] = self._missed.get(lid, 0) + 1
+                MetisLogger.warning("heartbeat miss %d/%d for %s: %s", self._missed[lid], self._heartbeat_misses, lid,
+                                    getattr(e, "code", lambda: e)())
+                if self._missed[lid] >= self._heartbeat_misses:
+                    if self.core.evict_learner(lid, "evicted: heartbeat lost"):
+                        evicted.append(lid)
+                    self._missed.pop(lid, None)
+                    with self._channels_lock:
+                        ch = self._channels.pop(lid, None)
+                    if ch:
+                        ch[0].close()
+        return evicted
+
+    def _heartbeat_loop(self):
+        while not self._shutdown_event.wait(self._heartbeat_secs):
+            try:
+                self.heartbeat_once()
+            except Exception as e:
+                MetisLogger.warning("heartbeat sweep failed: %r", e)
 
     # -- snapshots ------------------------------------------------------------------------------------
     def _resume_from_snapshot(self):

@@ -78,3 +78,60 @@ def test_tls_federation(tmp_path):
     stats = s.run(request_every_secs=0.5)
     assert len(stats["federation_runtime_metadata"]["metadata"]) >= 3
     assert stats["community_model_results"]["community_evaluation"]
+
+
+def test_heartbeat_evicts_a_learner_that_stopped_answering(tmp_path, monkeypatch):
+    """Failure detector: after N missed health probes the learner is evicted and the
+    synchronous barrier shrinks, so the round completes with the survivors."""
+    import socket
+    import time
+
+    import torch
+    import yaml
+
+    from metisfl_b200.driver.driver_session import DriverSession
+    from metisfl_b200.models.zoo import FashionMnistMLP
+    from metisfl_b200.utils.fedenv_parser import FederationEnvironment
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(root, "examples", "config", "fashionmnist_2learners_sync_fedavg.yaml")) as f:
+        d = yaml.safe_load(f)
+    fe = d["FederationEnvironment"]
+    socks = [socket.socket() for _ in range(3)]
+    for s in socks:
+        s.bind(("127.0.0.1", 0))
+    ports = [s.getsockname()[1] for s in socks]
+    for s in socks:
+        s.close()
+    fe["Controller"]["GRPCServicer"]["Port"] = ports[0]
+    for l, p in zip(fe["Learners"], ports[1:]):
+        l["GRPCServicer"]["Port"] = p
+    fe["TerminationSignals"]["FederationRounds"] = 1000
+    monkeypatch.setenv("METISFL_HEARTBEAT_MISSES", "2")
+    torch.manual_seed(0)
+    sess = DriverSession(FederationEnvironment(d), FashionMnistMLP(), lambda: None, None, None,
+                         working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False, neural_engine="echo",
+                         echo_sleep_secs=0.1)
+    sess.initialize_federation()
+    try:
+        controller = dict(sess._inprocess)["controller"]
+        service = controller._wrapper._servicer
+        deadline = time.time() + 20
+        while len(service.core.get_learners()) < 2 and time.time() < deadline:
+            time.sleep(0.1)
+        assert len(service.core.get_learners()) == 2
+        assert service.heartbeat_once() == []          # everybody answers
+        victim = dict(sess._inprocess)["learner1"]
+        victim._LearnerServicer__grpc_server.server.stop(0).wait()   # the process "dies": its port stops answering
+        lost = []
+        for _ in range(4):
+            lost += service.heartbeat_once(timeout=0.5)
+            if lost:
+                break
+        assert len(lost) == 1 and len(service.core.get_learners()) == 1
+        it0 = service.core.global_iteration()
+        deadline = time.time() + 20
+        while service.core.global_iteration() < it0 + 2 and time.time() < deadline:
+            time.sleep(0.1)
+        assert service.core.global_iteration() >= it0 + 2   # rounds keep completing with the survivor
+    finally:
+        sess.shutdown_federation()
