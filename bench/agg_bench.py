@@ -4,6 +4,8 @@
 Per model size (ResNet-18 = 11.2 M, GPT-2-medium = 355 M parameters, bf16) and world size:
   * ours : ONE launch of mfl_fused_aggregate per rank (weighted reduce-scatter + all-gather over NVLink
            peer loads/stores, in-kernel barriers);
+  * nvls : the same launch with the reduction done inside the NVSwitch (multimem.ld_reduce on pre-scaled slots)
+           and the result multicast-stored to every GPU (multimem.st);
   * nccl : per rank `buf *= w` then `dist.all_reduce(SUM)` on the same flat bf16 buffer.
 Timed with CUDA events over `--iters` launches after warm-up, max over ranks; a buffer larger than
 L2 is written between iterations when `--flush` is given.  Reports params/s, per-rank NVLink bytes
@@ -55,8 +57,8 @@ def main():
     for n in [int(s) for s in args.sizes.split(",")]:
         n = (n + 7) // 8 * 8
         nbytes = n * 2
-        slots = fab.alloc(nbytes * k)
-        comm = fab.alloc(nbytes)
+        slots = fab.alloc(nbytes * k, multicast=True)
+        comm = fab.alloc(nbytes, multicast=True)
         pads = fab.signal_pads(296)
         slots.local.view(torch.bfloat16)[:n * k].copy_(torch.randn(n * k, device=dev).to(torch.bfloat16))
         L = world * k
@@ -67,6 +69,12 @@ def main():
 
         def ours():
             agg.fused_aggregate(srcs, w, comm.ptrs, pads.ptrs, rank, world, seg, n_blocks=296)
+
+        have_mc = bool(world > 1 and slots.mc_ptr and comm.mc_ptr and k <= 8)
+
+        def nvls():  # slots are taken as already scaled by w (what K2's publish_scale produces)
+            agg.fused_aggregate(srcs, w, comm.ptrs, pads.ptrs, rank, world, seg, n_blocks=296,
+                                mc_src_ptrs=[slots.mc_ptr + j * nbytes for j in range(k)], mc_out_ptr=comm.mc_ptr)
 
         flat = slots.local.view(torch.bfloat16)[:n].clone()
 
@@ -104,6 +112,13 @@ def main():
             ref = sum(slots.local.view(torch.bfloat16)[j * n:(j + 1) * n][:4096].float() for j in range(k)) / L
             got = comm.local.view(torch.bfloat16)[:4096].float()
             assert torch.allclose(got, ref, atol=2e-2, rtol=2e-2)
+        t_nvls, nvls_err = None, None
+        if have_mc:
+            ours(); torch.cuda.synchronize(); dist.barrier()
+            want = comm.local.view(torch.bfloat16)[:n].float().clone() * L   # unweighted sum = L x the average
+            t_nvls = timeit(nvls)
+            torch.cuda.synchronize(); dist.barrier()
+            nvls_err = float((comm.local.view(torch.bfloat16)[:n].float() - want).abs().max())
         t_nccl = timeit(nccl)
         # bytes that must cross NVLink per rank: read (L - k) remote shards of n/world, write (world-1) shards
         shard = nbytes / world
@@ -114,6 +129,11 @@ def main():
             "params": n, "learners": L, "world": world, "ours_ms": t_ours, "nccl_fedavg_ms": t_nccl,
             "speedup_vs_nccl": t_nccl / t_ours, "ours_params_per_s": L * n / (t_ours * 1e-3),
             "roofline_ms": roof_ms, "fraction_of_roofline": roof_ms / t_ours,
+            "nvls_ms": t_nvls, "nvls_max_abs_err_vs_p2p": nvls_err,
+            # per direction: the switch pulls (world-1)/world of each of my k slots, I push my 1/world shard once
+            "nvls_link_bytes_per_rank": ((world - 1) * k + 1) * shard if have_mc else None,
+            "nvls_fraction_of_link_roofline": (((world - 1) * k + 1) * shard / (NVLINK_GBS * 1e9) * 1e3 / t_nvls)
+            if t_nvls else None,
             "roofline_kind": "NVLink 770 GB/s measured peer copy" if world > 1 else f"HBM copy {hbm} GB/s of measured",
         })
         del slots, comm

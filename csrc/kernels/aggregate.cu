@@ -187,7 +187,95 @@ struct FusedArgs {
   mfl_segment seg[MFL_MAX_SEGMENTS];
   int n_seg, rank, world;
   float* install_f32;
+  // NVLS mode (n_mc > 0): mc_src[j] / mc_out are MULTICAST addresses of symmetric buffers.  A multimem.ld_reduce on
+  // mc_src[j] + x returns the sum over all GPUs of the value at offset x of slot j, added inside the NVSwitch; a
+  // multimem.st on mc_out + x lands in every GPU's community buffer.  Per GPU and per byte of model that is one
+  // pull of 1/world and one push of 1/world over NVLink instead of (world-1)/world each way with peer loads/stores.
+  // The switch only adds, so the slots must hold pre-scaled models (K2 publishes w_l * theta_l).
+  const void* mc_src[MFL_MAX_MC_SRC];
+  void* mc_out;
+  int n_mc;
 };
+
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_f16(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_f32(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(void* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// NVLS variant of fused_segment_fast: my shard of the segment, reduced by the switch, multicast back.
+template <int DT>
+__device__ __forceinline__ void fused_segment_nvls(const FusedArgs& fa, const mfl_segment& sg) {
+  constexpr int kVecPerUnit = (DT == MFL_FLOAT32) ? 2 : 1;  // a unit is 8 elements
+  const size_t units = sg.numel / kUnit;
+  const size_t upr = (units + fa.world - 1) / fa.world;
+  const size_t begin = min(units, upr * fa.rank), end = min(units, begin + upr);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  char* out = reinterpret_cast<char*>(fa.mc_out) + sg.offset_bytes;
+  auto ld = [](const char* p) {
+    return DT == MFL_FLOAT32 ? multimem_ld_reduce_f32(p)
+                             : (DT == MFL_BFLOAT16 ? multimem_ld_reduce_bf16(p) : multimem_ld_reduce_f16(p));
+  };
+  // 16-byte vectors [vbegin, vend) of my shard; kNvlsBatch switch reductions in flight per thread
+  constexpr int kNvlsBatch = 8;
+  const size_t vbegin = begin * kVecPerUnit, vend = end * kVecPerUnit;
+  const size_t first = vbegin + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (fa.n_mc == 1) {
+    const char* src = reinterpret_cast<const char*>(fa.mc_src[0]) + sg.offset_bytes;
+    for (size_t v = first; v < vend; v += stride * kNvlsBatch) {
+      uint4 r[kNvlsBatch];
+#pragma unroll
+      for (int b = 0; b < kNvlsBatch; ++b) {
+        const size_t idx = v + b * stride;
+        if (idx < vend) r[b] = ld(src + idx * sizeof(uint4));
+      }
+#pragma unroll
+      for (int b = 0; b < kNvlsBatch; ++b) {
+        const size_t idx = v + b * stride;
+        if (idx < vend) multimem_st(out + idx * sizeof(uint4), r[b]);
+      }
+    }
+  } else {  // several learners per GPU: one switch reduction per local slot index, folded in fp32 here
+    constexpr int N = VecTraits<DT>::N;
+    for (size_t v = first; v < vend; v += stride) {
+      float acc[N], f[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) acc[i] = 0.f;
+      for (int jj = 0; jj < fa.n_mc; ++jj) {
+        VecTraits<DT>::unpack(ld(reinterpret_cast<const char*>(fa.mc_src[jj]) + sg.offset_bytes + v * sizeof(uint4)), f);
+#pragma unroll
+        for (int i = 0; i < N; ++i) acc[i] += f[i];
+      }
+      multimem_st(out + v * sizeof(uint4), VecTraits<DT>::pack(acc));
+    }
+  }
+  // tail elements (numel % 8) go through the peer-pointer path on the last rank
+  if (fa.rank == fa.world - 1 && blockIdx.x == 0 && threadIdx.x < sg.numel % kUnit) {
+    const size_t i = units * kUnit + threadIdx.x;
+    float acc = 0.f;
+    for (int l = 0; l < fa.agg.n; ++l)
+      acc += load_as_float(reinterpret_cast<const char*>(fa.agg.src[l]) + sg.offset_bytes, DT, i);
+    for (int t = 0; t < fa.world; ++t)
+      store_from_float(reinterpret_cast<char*>(fa.out[t]) + sg.offset_bytes, DT, i, acc);
+  }
+}
 
 template <int DT>
 __device__ __forceinline__ void fused_segment_fast(const FusedArgs& fa, const mfl_segment& sg) {
@@ -258,6 +346,12 @@ __global__ void __launch_bounds__(512, 2) fused_aggregate_kernel(const __grid_co
   // Phase 1: reduce my shard of every segment and scatter it to all ranks.
   for (int s = 0; s < fa.n_seg; ++s) {
     const mfl_segment& sg = fa.seg[s];
+    if (fa.n_mc > 0 && !sg.exact && (sg.dtype == MFL_BFLOAT16 || sg.dtype == MFL_FLOAT32 || sg.dtype == MFL_FLOAT16)) {
+      if (sg.dtype == MFL_BFLOAT16) fused_segment_nvls<MFL_BFLOAT16>(fa, sg);
+      else if (sg.dtype == MFL_FLOAT32) fused_segment_nvls<MFL_FLOAT32>(fa, sg);
+      else fused_segment_nvls<MFL_FLOAT16>(fa, sg);
+      continue;
+    }
     if (!sg.exact && sg.dtype == MFL_BFLOAT16) fused_segment_fast<MFL_BFLOAT16>(fa, sg);
     else if (!sg.exact && sg.dtype == MFL_FLOAT32) fused_segment_fast<MFL_FLOAT32>(fa, sg);
     else if (!sg.exact && sg.dtype == MFL_FLOAT16) fused_segment_fast<MFL_FLOAT16>(fa, sg);
@@ -377,10 +471,10 @@ static int fill_fused(FusedArgs& fa, uint32_t* const* pads, int rank, int world)
   return 0;
 }
 
-extern "C" int mfl_fused_aggregate(const void* const* src_slots, const double* weights, int n_src,
-                                   void* const* out_bufs, uint32_t* const* signal_pads, int rank, int world,
-                                   const mfl_segment* segments, int n_segments, float* install_f32,
-                                   int n_blocks, void* stream) {
+static int fused_aggregate_impl(const void* const* src_slots, const double* weights, int n_src,
+                                void* const* out_bufs, uint32_t* const* signal_pads, int rank, int world,
+                                const mfl_segment* segments, int n_segments, float* install_f32, int n_blocks,
+                                void* stream, const void* const* mc_src, int n_mc, void* mc_out) {
   MFL_ARG(n_src >= 1 && n_src <= MFL_MAX_SRC, "fused_aggregate: n_src=%d outside [1,%d]", n_src, MFL_MAX_SRC);
   MFL_ARG(n_segments >= 1 && n_segments <= MFL_MAX_SEGMENTS, "fused_aggregate: n_segments=%d", n_segments);
   MFL_ARG(n_blocks >= 1 && n_blocks <= 2 * sm_count(), "fused_aggregate: n_blocks=%d must be in [1, 2 x #SMs] "
@@ -405,8 +499,34 @@ extern "C" int mfl_fused_aggregate(const void* const* src_slots, const double* w
             "fused_aggregate: segment %d misaligned or bad dtype", s);
   }
   local.install_f32 = install_f32;
+  MFL_ARG(n_mc >= 0 && n_mc <= MFL_MAX_MC_SRC, "fused_aggregate: n_mc=%d outside [0,%d]", n_mc, MFL_MAX_MC_SRC);
+  MFL_ARG(n_mc == 0 || (mc_out && world > 1), "fused_aggregate: NVLS mode needs a multicast output and world > 1");
+  local.n_mc = n_mc;
+  local.mc_out = mc_out;
+  for (int j = 0; j < n_mc; ++j) {
+    local.mc_src[j] = mc_src[j];
+    MFL_ARG(mc_src[j] && aligned16(mc_src[j]), "fused_aggregate: multicast source %d null or misaligned", j);
+  }
   fused_aggregate_kernel<<<n_blocks, 512, 0, (cudaStream_t)stream>>>(local);
   return check(cudaGetLastError(), "fused_aggregate_kernel launch");
+}
+
+extern "C" int mfl_fused_aggregate(const void* const* src_slots, const double* weights, int n_src,
+                                   void* const* out_bufs, uint32_t* const* signal_pads, int rank, int world,
+                                   const mfl_segment* segments, int n_segments, float* install_f32,
+                                   int n_blocks, void* stream) {
+  return fused_aggregate_impl(src_slots, weights, n_src, out_bufs, signal_pads, rank, world, segments, n_segments,
+                              install_f32, n_blocks, stream, nullptr, 0, nullptr);
+}
+
+extern "C" int mfl_fused_aggregate_nvls(const void* const* src_slots, const double* weights, int n_src,
+                                        void* const* out_bufs, uint32_t* const* signal_pads, int rank, int world,
+                                        const mfl_segment* segments, int n_segments, float* install_f32,
+                                        int n_blocks, void* stream, const void* const* mc_src_slots, int n_mc,
+                                        void* mc_out) {
+  MFL_ARG(n_mc >= 1, "fused_aggregate_nvls: need at least one multicast source");
+  return fused_aggregate_impl(src_slots, weights, n_src, out_bufs, signal_pads, rank, world, segments, n_segments,
+                              install_f32, n_blocks, stream, mc_src_slots, n_mc, mc_out);
 }
 
 extern "C" int mfl_fabric_barrier(uint32_t* const* signal_pads, int rank, int world, int channel, void* stream) {

@@ -43,7 +43,7 @@ err = [0.0]
 
 
 def secure_round():
-    eng.train_learner(0, batches)
+    eng.train_learner(0, batches, publish_scale=1.0)  # the slot feeds the encoder: keep it unscaled
     x = eng.slot_views[0][0]
     g.encrypt_device(x, seed=1000 + rank, out=ct_slot.local.view(torch.int64)[:words])
     g.fused_weighted_sum(ct_slot.ptrs, w, words, ct_out.ptrs, eng.pads.ptrs, rank, world, n_blocks=148)

@@ -66,6 +66,21 @@ int mfl_fused_aggregate(const void* const* src_slots, const double* weights, int
                         const mfl_segment* segments, int n_segments,
                         float* install_f32, /* optional local fp32 copy of segment 0 */
                         int n_blocks, void* stream);
+
+/* NVLS variant: the same launch contract and arguments as mfl_fused_aggregate, plus MULTICAST addresses of the
+ * symmetric slot / community buffers (cuMulticast* objects bound on every GPU; torch.distributed._symmetric_memory
+ * provides them).  Floating-point segments are reduced INSIDE the NVSwitch (multimem.ld_reduce on mc_src_slots[j],
+ * j = local slot index, n_mc = learners per GPU <= MFL_MAX_MC_SRC) and multicast-stored to every GPU
+ * (multimem.st on mc_out): per GPU 1/world of the model crosses NVLink each way instead of (world-1)/world.
+ * The switch only adds, so every learner of the federation must participate and the slots must already hold
+ * w_l * theta_l (mfl_optimizer_step's publish_scale); `weights` is used only by integer ("exact") segments and
+ * the < 8-element tails, which keep the peer-pointer path.  No reference counterpart (controller.cc:428-518
+ * sums on the CPU). */
+#define MFL_MAX_MC_SRC 8
+int mfl_fused_aggregate_nvls(const void* const* src_slots, const double* weights, int n_src, void* const* out_bufs,
+                             uint32_t* const* signal_pads, int rank, int world, const mfl_segment* segments,
+                             int n_segments, float* install_f32, int n_blocks, void* stream,
+                             const void* const* mc_src_slots, int n_mc, void* mc_out);
 size_t mfl_signal_pad_bytes(int n_blocks);
 
 /* ---- K2: fused optimizer step + publish (keras_model_ops.py:245-283, fed_prox.py:50-60) ---

@@ -51,6 +51,8 @@ def lib():
         L.mfl_rolling_update.argtypes = [vp, i, vp, vp, d, vp, d, d, sz, vp]
         L.mfl_fused_aggregate.argtypes = [C.POINTER(vp), C.POINTER(d), i, C.POINTER(vp), C.POINTER(vp),
                                           i, i, C.POINTER(Segment), i, vp, i, vp]
+        L.mfl_fused_aggregate_nvls.argtypes = [C.POINTER(vp), C.POINTER(d), i, C.POINTER(vp), C.POINTER(vp),
+                                               i, i, C.POINTER(Segment), i, vp, i, vp, C.POINTER(vp), i, vp]
         L.mfl_signal_pad_bytes.restype = sz
         L.mfl_signal_pad_bytes.argtypes = [i]
         L.mfl_optimizer_step.argtypes = [vp, vp, i, vp, i, vp, vp, vp, vp, i, sz, C.POINTER(OptimCfg), i, vp]

@@ -131,10 +131,13 @@ class Quantifier:
 
 def fused_aggregate(src_slot_ptrs: Sequence[int], weights: Sequence[float], out_ptrs: Sequence[int],
                     signal_pad_ptrs: Sequence[int], rank: int, world: int, segments, install_f32=None,
-                    n_blocks: Optional[int] = None, stream=None):
+                    n_blocks: Optional[int] = None, stream=None, mc_src_ptrs: Optional[Sequence[int]] = None,
+                    mc_out_ptr: int = 0):
     """Launch the fused reduce-scatter + all-gather kernel (every rank must make the same call).
 
-    ``segments`` is a list of ``(offset_bytes, numel, torch_dtype_or_wire, exact)``.
+    ``segments`` is a list of ``(offset_bytes, numel, torch_dtype_or_wire, exact)``.  With ``mc_src_ptrs`` (multicast
+    addresses of the local slot indices) and ``mc_out_ptr`` the floating-point segments are reduced inside the
+    NVSwitch and multicast back (NVLS); the slots must then hold pre-scaled models and all learners participate.
     """
     L = _lib.lib()
     segs = (_lib.Segment * len(segments))()
@@ -144,6 +147,14 @@ def fused_aggregate(src_slot_ptrs: Sequence[int], weights: Sequence[float], out_
         s.exact = int(bool(exact))
     if n_blocks is None:
         n_blocks = default_fused_blocks()
+    if mc_src_ptrs:
+        rc = L.mfl_fused_aggregate_nvls(_lib.voidp_array(src_slot_ptrs), _lib.double_array(weights),
+                                        len(src_slot_ptrs), _lib.voidp_array(out_ptrs),
+                                        _lib.voidp_array(signal_pad_ptrs), rank, world, segs, len(segments),
+                                        _lib.ptr(install_f32), int(n_blocks), _lib.stream_ptr(stream),
+                                        _lib.voidp_array(mc_src_ptrs), len(mc_src_ptrs), int(mc_out_ptr))
+        _lib.check(rc, "mfl_fused_aggregate_nvls")
+        return
     rc = L.mfl_fused_aggregate(_lib.voidp_array(src_slot_ptrs), _lib.double_array(weights), len(src_slot_ptrs),
                                _lib.voidp_array(out_ptrs), _lib.voidp_array(signal_pad_ptrs), rank, world,
                                segs, len(segments), _lib.ptr(install_f32), int(n_blocks), _lib.stream_ptr(stream))

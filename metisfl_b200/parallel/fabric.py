@@ -31,10 +31,11 @@ class _CudaMem:
 class SymmetricBuffer:
     """One buffer per rank, all mapped into this process. ``ptrs[r]`` is rank r's base address here."""
 
-    def __init__(self, local: torch.Tensor, ptrs: List[int], owner=None):
+    def __init__(self, local: torch.Tensor, ptrs: List[int], owner=None, mc_ptr: int = 0):
         self.local = local
         self.ptrs = ptrs
         self._owner = owner
+        self.mc_ptr = mc_ptr  # multicast (NVLS) address of the same buffers, 0 when unavailable
 
     @property
     def nbytes(self) -> int:
@@ -53,6 +54,7 @@ class Fabric:
         self.device = torch.device(device)
         self.peer_mapped = self.device.type == "cuda"
         self._allocs = []
+        self._symm_handles = []
         self._opened = []
         if self.peer_mapped and self.world > 1:
             torch.cuda.set_device(self.device)
@@ -73,9 +75,17 @@ class Fabric:
             dist.barrier(group=self.group)
 
     # -- allocation --------------------------------------------------------------------------
-    def alloc(self, nbytes: int) -> SymmetricBuffer:
-        """Collective: every rank must call with the same size, in the same order."""
+    def alloc(self, nbytes: int, multicast: bool = False) -> SymmetricBuffer:
+        """Collective: every rank must call with the same size, in the same order.
+
+        ``multicast=True`` asks for a buffer that also has an NVLS multicast address (``mc_ptr``): the allocation and
+        the cuMulticast binding are done by ``torch.distributed._symmetric_memory`` (plumbing only - the kernels that
+        use the addresses are ours).  Falls back to the cudaIpc allocation (``mc_ptr == 0``) when unsupported."""
         nbytes = (int(nbytes) + 255) // 256 * 256
+        if multicast and self.peer_mapped and self.world > 1:
+            buf = self._alloc_multicast(nbytes)
+            if buf is not None:
+                return buf
         if not self.peer_mapped:
             t = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
             return SymmetricBuffer(t, [t.data_ptr()] * 1 if self.world == 1 else [0] * self.world)
@@ -103,6 +113,24 @@ class Fabric:
         local = torch.as_tensor(_CudaMem(p.value, nbytes), device=self.device)
         self.host_barrier()
         return SymmetricBuffer(local, ptrs, owner=self)
+
+    def _alloc_multicast(self, nbytes: int) -> Optional[SymmetricBuffer]:
+        ok, t, hdl = 1, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm
+            t = symm.empty(nbytes, dtype=torch.uint8, device=self.device)
+            hdl = symm.rendezvous(t, self.group if self.group is not None else dist.group.WORLD)
+            if not hdl.multicast_ptr or len(hdl.buffer_ptrs) != self.world:
+                ok = 0
+        except Exception:  # older driver / no fabric manager / API moved
+            ok = 0
+        flags = self.all_gather_object(ok)
+        if not all(flags):
+            return None
+        t.zero_()
+        self._symm_handles.append((t, hdl))
+        self.host_barrier()
+        return SymmetricBuffer(t, [int(p) for p in hdl.buffer_ptrs], owner=hdl, mc_ptr=int(hdl.multicast_ptr))
 
     def signal_pads(self, n_blocks: int = 296) -> SymmetricBuffer:
         if self._pads is None:

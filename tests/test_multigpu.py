@@ -23,7 +23,7 @@ from metisfl_b200.models.zoo import ResNet18
 from metisfl_b200.ops import aggregation as agg
 k = {k}
 ex = [100 * (i + 1) for i in range(world * k)]
-eng = FederationEngine(ResNet18, EngineConfig(learners_per_gpu=k, use_cuda_graph=False), device=f"cuda:{{lr}}",
+eng = FederationEngine(ResNet18, EngineConfig(learners_per_gpu=k, use_cuda_graph=False, nvls=True), device=f"cuda:{{lr}}",
                        examples_per_learner=ex)
 g = torch.Generator().manual_seed(100 + rank)
 for j in range(k):
@@ -57,6 +57,33 @@ for si, s in enumerate(eng.layout.segments):
         ok &= bool(torch.allclose(got.float(), ref.float(), atol=2e-2, rtol=2e-2))
 if eng.direct_install:
     ok &= bool(torch.allclose(eng.arena.master[0].cpu(), eng.community_views[0].cpu().float()))
+# NVLS path: the same aggregation with the reduction done inside the NVSwitch (slots pre-scaled by w_l)
+nvls_ok = True
+if eng.nvls:
+    for j in range(k):
+        wl = eng._static_weight(eng.learner_id(j))
+        for si, s in enumerate(eng.layout.segments):
+            if not s.exact:
+                eng.slot_views[j][si].mul_(wl)
+        eng._slot_scale[j] = wl
+    torch.cuda.synchronize(); dist.barrier()
+    for it in range(2):
+        eng.aggregate_sync()
+    torch.cuda.synchronize(); dist.barrier()
+    for si, s in enumerate(eng.layout.segments):
+        srcs = []
+        for i in range(world * k):
+            r, j = divmod(i, k)
+            buf = allslots[r][j * nb:(j + 1) * nb]
+            srcs.append(buf[s.byte_offset:s.byte_offset + s.nbytes].view(s.dtype).cpu())
+        ref = agg.weighted_sum(srcs, w, exact=s.exact)
+        got = eng.community_views[si].cpu()
+        if s.exact:
+            nvls_ok &= bool(torch.equal(got, ref))
+        else:
+            nvls_ok &= bool(torch.allclose(got.float(), ref.float(), atol=3e-2, rtol=3e-2))
+    ok &= nvls_ok
+    eng._slot_scale = [1.0] * k
 t = torch.tensor([1.0 if ok else 0.0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
 # one real round as well: train + publish + fused aggregation
 data = [[(torch.randn(32, 3, 32, 32), torch.randint(0, 10, (32,))) for _ in range(2)] for _ in range(k)]
@@ -66,7 +93,8 @@ gathered = [torch.empty_like(flat) for _ in range(world)]
 dist.all_gather(gathered, flat)
 same = all(torch.equal(gathered[0], x) for x in gathered)
 if rank == 0:
-    print("MULTIGPU_OK" if (t.item() == 1.0 and same) else f"MULTIGPU_BAD agg={{t.item()}} same={{same}}", out["loss"])
+    print("MULTIGPU_OK" if (t.item() == 1.0 and same) else f"MULTIGPU_BAD agg={{t.item()}} same={{same}}", out["loss"],
+          "nvls" if eng.nvls else "p2p-only")
 eng.close()
 dist.destroy_process_group()
 """
