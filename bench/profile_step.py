@@ -17,6 +17,8 @@ batch = int(os.environ.get("BATCH", "128"))
 conv = os.environ.get("B200_CONV", "0") == "1"
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
+import metisfl_b200.models.zoo.resnet as _rn  # noqa: E402
+_rn.PARALLEL_SHORTCUT = os.environ.get("PARALLEL_SHORTCUT", "1") == "1"
 torch.backends.cudnn.benchmark = os.environ.get("CUDNN_BENCHMARK", "1") == "1"
 model = ResNet18()
 if conv:

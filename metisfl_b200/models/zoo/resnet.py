@@ -11,6 +11,17 @@ import torch.nn.functional as F
 from metisfl_b200.ops.bn import bn_act
 
 
+PARALLEL_SHORTCUT = True  # downsample branch (1x1 conv + BN) on a second stream, concurrent with conv1 / bn1
+_SHORTCUT_STREAMS = {}
+
+
+def _shortcut_stream(device):
+    s = _SHORTCUT_STREAMS.get(device)
+    if s is None:
+        s = _SHORTCUT_STREAMS[device] = torch.cuda.Stream(device=device)
+    return s
+
+
 class BasicBlock(nn.Module):
     expansion = 1
 
@@ -25,6 +36,20 @@ class BasicBlock(nn.Module):
             self.shortcut = nn.Sequential(nn.Conv2d(cin, cout, 1, stride, bias=False), nn.BatchNorm2d(cout))
 
     def forward(self, x):
+        if self.shortcut is not None and x.is_cuda and PARALLEL_SHORTCUT:
+            # the two branches are independent and each is a chain of short kernels: run them side by side (inside
+            # a CUDA graph capture this becomes a fork / join; autograd replays the same streams in backward)
+            main = torch.cuda.current_stream(x.device)
+            side = _shortcut_stream(x.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                skip = bn_act(self.shortcut[1], self.shortcut[0](x), relu=False)
+            x.record_stream(side)
+            out = bn_act(self.bn1, self.conv1(x))
+            out = self.conv2(out)
+            main.wait_stream(side)
+            skip.record_stream(main)
+            return bn_act(self.bn2, out, residual=skip)
         out = bn_act(self.bn1, self.conv1(x))
         skip = x if self.shortcut is None else bn_act(self.shortcut[1], self.shortcut[0](x), relu=False)
         return bn_act(self.bn2, self.conv2(out), residual=skip)  # BN + residual add + ReLU in one pass (K14)
