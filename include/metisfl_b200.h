@@ -164,6 +164,16 @@ int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda,
 int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, int r, int s,
                           int stride, int pad, void* stream);
 
+/* ---- K15: weight-stationary 3x3 / stride-1 / pad-1 convolution on tcgen05 (csrc/kernels/conv3x3_halo.cu): all
+ * filter taps of a CTA's 64 output channels stay in shared memory, one zero-padded halo tile per output tile is
+ * loaded by tiled TMA and read nine times through shifted shared-memory descriptors.  NHWC bf16: x[n,h,w,c],
+ * w[k,3,3,c], y[n,h,w,k]; c in {64, 128}, k % 64 == 0, even w <= 126 (mfl_conv3x3_supported).  Data gradients
+ * use it with the filters transposed and flipped.  stats: NULL, or [2][k] fp32 to which the per-channel sum and
+ * sum of squares of the outputs are added.  Replaces the framework convolutions (keras_model_ops.py:156). */
+int mfl_conv3x3_supported(int n, int h, int wd, int c, int k);
+int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* stats, int n, int h, int wd, int c, int k,
+                     void* stream);
+
 /* ---- K14: fused BatchNorm2d (+ residual add) (+ ReLU), NHWC bf16 activations viewed as [m, c] rows
  * (m = N*H*W, c a power of two in [8, 2048]); fp32 affine / statistics (csrc/kernels/bn_relu.cu).
  * forward : training != 0: batch statistics (saved to save_mean / save_invstd, running statistics and

@@ -25,6 +25,8 @@ def _bind():
     if not _BOUND:
         vp, i = C.c_void_p, C.c_int
         L.mfl_conv2d_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        L.mfl_conv3x3_supported.argtypes = [i, i, i, i, i]
+        L.mfl_conv3x3_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
         _BOUND = True
     return L
 
@@ -47,6 +49,29 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int) -> tor
     rc = _bind().mfl_conv2d_fprop_bf16(y.data_ptr(), x.data_ptr(), w.data_ptr(), n, h, wd, c, k, r, s, stride, pad,
                                        _lib.stream_ptr())
     _lib.check(rc, "mfl_conv2d_fprop_bf16")
+    return y
+
+
+def conv3x3_supported(x: torch.Tensor, w: torch.Tensor) -> bool:
+    """Shapes the weight-stationary 3x3 kernel (K15) takes: stride 1, padding 1, C in {64, 128}, K % 64 == 0."""
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 4
+            and tuple(w.shape[2:]) == (3, 3) and _lib.available()):
+        return False
+    n, c, h, wd = x.shape
+    return bool(_bind().mfl_conv3x3_supported(n, h, wd, c, w.shape[0]))
+
+
+def conv3x3(x: torch.Tensor, w: torch.Tensor, stats: torch.Tensor = None) -> torch.Tensor:
+    """K15: y = conv2d(x, w, stride 1, padding 1); x [N,C,H,W] and w [K,C,3,3] channels_last bf16.
+    ``stats`` ([2, K] fp32) receives += the per-channel sum and sum of squares of y."""
+    n, c, h, wd = x.shape
+    k = w.shape[0]
+    x = x.contiguous(memory_format=torch.channels_last)
+    w = w.contiguous(memory_format=torch.channels_last)
+    y = torch.empty((n, k, h, wd), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    rc = _bind().mfl_conv3x3_bf16(y.data_ptr(), x.data_ptr(), w.data_ptr(), None if stats is None else stats.data_ptr(),
+                                  n, h, wd, c, k, _lib.stream_ptr())
+    _lib.check(rc, "mfl_conv3x3_bf16")
     return y
 
 

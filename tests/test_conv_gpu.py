@@ -93,3 +93,25 @@ def test_overlapped_wgrad_matches_autograd_eager_and_in_a_graph():
         torch.cuda.synchronize()
         for (n, p), (_, q) in zip(ref.named_parameters(), ours.named_parameters()):
             torch.testing.assert_close(q.grad, p.grad, atol=2e-3, rtol=1e-2, msg=f"{n} graph={use_graph}")
+
+
+HALO_SHAPES = [(4, 64, 32, 32, 64), (2, 128, 16, 16, 128), (3, 64, 8, 8, 128), (2, 64, 5, 6, 64), (5, 128, 4, 4, 64),
+               (2, 64, 33, 30, 64)]
+
+
+@pytest.mark.parametrize("n,c,h,w,k", HALO_SHAPES)
+def test_weight_stationary_conv3x3_matches_reference(n, c, h, w, k):
+    """K15: halo tile + nine shifted shared-memory descriptors, against an fp32 convolution of the same operands."""
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(n * 131 + c + k + h)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, 3, 3, generator=g) / (c * 9) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last)
+    assert conv.conv3x3_supported(x, wt)
+    stats = torch.zeros(2, k, device="cuda")
+    y = conv.conv3x3(x, wt, stats)
+    ref = F.conv2d(x.float(), wt.float(), None, 1, 1)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    torch.testing.assert_close(y.float(), ref, atol=3e-2, rtol=3e-2)
+    torch.testing.assert_close(stats[0], y.float().sum(dim=(0, 2, 3)), atol=0.5, rtol=2e-2)
+    torch.testing.assert_close(stats[1], (y.float() ** 2).sum(dim=(0, 2, 3)), atol=0.5, rtol=2e-2)
