@@ -34,9 +34,11 @@ for (c, h, k, r, st, p) in [(64, 32, 64, 3, 1, 1), (64, 32, 128, 3, 2, 1), (128,
     x = torch.randn(n, c, h, h, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     w = torch.randn(k, c, r, r, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     t_ours = timeit(lambda: conv.conv2d_fprop(x, w, st, p))
+    t_halo = timeit(lambda: conv.conv3x3(x, w)) if (r == 3 and st == 1 and p == 1 and conv.conv3x3_supported(x, w)) else None
     t_cudnn = timeit(lambda: F.conv2d(x, w, None, st, p))
     oh = (h + 2 * p - r) // st + 1
     fl = 2.0 * n * oh * oh * k * c * r * r
     rows.append({"C": c, "HW": h, "K": k, "R": r, "stride": st, "ours_us": t_ours * 1e3, "cudnn_us": t_cudnn * 1e3,
+                 "k15_us": t_halo * 1e3 if t_halo else None, "k15_tflops": fl / t_halo / 1e9 if t_halo else None,
                  "ours_tflops": fl / t_ours / 1e9, "cudnn_tflops": fl / t_cudnn / 1e9})
 print(json.dumps({"bench": "conv_bench", "batch": 128, "results": rows}))

@@ -12,6 +12,6 @@ n, c, hw, k, r, stride, pad = [int(v) for v in (sys.argv[1:8] if len(sys.argv) >
 x = torch.randn(n, c, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
 w = torch.randn(k, c, r, r, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
 for _ in range(4):
-    y = conv.conv2d_fprop(x, w, stride, pad)
+    y = conv.conv3x3(x, w) if os.environ.get("K15") == "1" else conv.conv2d_fprop(x, w, stride, pad)
 torch.cuda.synchronize()
 print("profile_conv ok", tuple(y.shape))

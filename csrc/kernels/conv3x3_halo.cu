@@ -36,7 +36,7 @@ using namespace mfl::gemm;
 constexpr int kThreads = 256;
 constexpr int kBN = 64;                          // output channels per CTA
 constexpr int kBTileBytes = kBN * kBlockK * 2;   // one tap x one 64-channel block of filters: 8 KB
-constexpr int kAStages = 2;
+constexpr int kMaxAStages = 6;               // halo ring depth is chosen at launch from the shared memory left over
 constexpr int kMaxCBlocks = 2;                   // C <= 128: 18 filter tiles = 144 KB stay resident
 constexpr int kTmemCols = 2 * kBN;
 
@@ -48,6 +48,7 @@ struct Params {
   int halo_bytes;        // shared-memory bytes reserved per halo stage (multiple of 1024)
   int box_bytes;         // bytes one halo TMA delivers: (TH + 2) * Wp * 128
   int tiles_per_img, num_m_tiles, n_tiles;
+  int a_stages;          // depth of the halo ring (2..kMaxAStages)
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2,
@@ -63,11 +64,12 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int cblocks = p.C / kBlockK;
-  uint8_t* halo = smem;                                             // kAStages x halo_bytes
+  const int kAStages = p.a_stages;
+  uint8_t* halo = smem;                                             // a_stages x halo_bytes
   uint8_t* filt = smem + (size_t)kAStages * p.halo_bytes;           // 9 * cblocks tiles of 8 KB, 1024-aligned
   uint64_t* a_full = reinterpret_cast<uint64_t*>(filt + (size_t)9 * cblocks * kBTileBytes);
-  uint64_t* a_empty = a_full + kAStages;
-  uint64_t* w_bar = a_empty + kAStages;
+  uint64_t* a_empty = a_full + kMaxAStages;
+  uint64_t* w_bar = a_empty + kMaxAStages;
   uint64_t* tmem_full = w_bar + 1;    // [2]
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
@@ -116,35 +118,38 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         }
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer =====
-      const uint32_t idesc = make_idesc<kBN>();
-      mbar_wait(w_bar, 0);
-      uint32_t it = 0, t = 0;
-      for (int mt = m_first; mt < p.num_m_tiles; mt += m_step, ++t) {
-        const uint32_t buf = t & 1, use = t >> 1;
-        mbar_wait(tmem_empty + buf, (use & 1) ^ 1);
+  } else if (warp == 1) {  // ===== MMA issuer: the whole warp runs the loop, one elected lane issues =====
+    const uint32_t idesc = make_idesc<kBN>();
+    mbar_wait(w_bar, 0);
+    uint32_t it = 0, t = 0;
+    for (int mt = m_first; mt < p.num_m_tiles; mt += m_step, ++t) {
+      const uint32_t buf = t & 1, use = t >> 1;
+      mbar_wait(tmem_empty + buf, (use & 1) ^ 1);
+      tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * kBN;
+      for (int cb = 0; cb < cblocks; ++cb, ++it) {
+        const int s = it % kAStages;
+        mbar_wait(a_full + s, (it / kAStages) & 1);
         tcgen05_fence_after();
-        const uint32_t tmem_d = tmem_base + buf * kBN;
-        for (int cb = 0; cb < cblocks; ++cb, ++it) {
-          const int s = it % kAStages;
-          mbar_wait(a_full + s, (it / kAStages) & 1);
-          tcgen05_fence_after();
-          const uint32_t a_base = smem_u32(halo + (size_t)s * p.halo_bytes);
-          const uint32_t b_base = smem_u32(filt + (size_t)cb * 9 * kBTileBytes);
-#pragma unroll 1
-          for (int tap = 0; tap < 9; ++tap) {
-            const int r = tap / 3, sx = tap - 3 * r;
-            const uint64_t adesc = make_sw128_desc(a_base + (uint32_t)((r * p.Wp + sx) * 128));
-            const uint64_t bdesc = make_sw128_desc(b_base + (uint32_t)(tap * kBTileBytes));
+        const uint64_t a0 = make_sw128_desc(smem_u32(halo + (size_t)s * p.halo_bytes));
+        const uint64_t b0 = make_sw128_desc(smem_u32(filt + (size_t)cb * 9 * kBTileBytes));
+        const uint64_t row = (uint64_t)((p.Wp * 128) >> 4);  // one halo row of pixels, in descriptor units of 16 B
+        const uint64_t px = 8;                                // one pixel (128 B)
+        if (elect_one()) {
+          if (cb == 0) umma_f16_c<false>(tmem_d, a0, b0, idesc);
+          else umma_f16_c<true>(tmem_d, a0, b0, idesc);
 #pragma unroll
-            for (int k = 0; k < kBlockK / kUmmaK; ++k)
-              umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (uint32_t)((cb | tap | k) != 0));
+          for (int q = 1; q < 36; ++q) {  // q = tap * 4 + k: 9 taps x 4 K-steps of 16 channels, straight-line
+            const int tap = q >> 2, k = q & 3, r = tap / 3, sx = tap - 3 * r;
+            umma_f16_c<true>(tmem_d, a0 + (uint64_t)r * row + (uint64_t)sx * px + (uint64_t)(k * 2),
+                             b0 + (uint64_t)(tap * (kBTileBytes >> 4) + k * 2), idesc);
           }
           umma_commit(a_empty + s);
         }
-        umma_commit(tmem_full + buf);
+        __syncwarp();
       }
+      if (elect_one()) umma_commit(tmem_full + buf);
+      __syncwarp();
     }
   } else if (warp >= 4) {  // ===== epilogue =====
     const int wq = warp & 3;
@@ -254,8 +259,10 @@ extern "C" int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* st
   p.num_m_tiles = n * p.tiles_per_img;
   p.n_tiles = k / kBN;
   const int cblocks = c / 64;
-  const size_t smem = 1024 + (size_t)kAStages * p.halo_bytes + (size_t)9 * cblocks * kBTileBytes + 256;
-  MFL_ARG(smem <= 227 * 1024, "conv3x3: tile needs %zu bytes of shared memory", smem);
+  const size_t fixed = 1024 + (size_t)9 * cblocks * kBTileBytes + 256;
+  p.a_stages = (int)std::min<size_t>(kMaxAStages, (227 * 1024 - fixed) / p.halo_bytes);
+  MFL_ARG(p.a_stages >= 2, "conv3x3: not enough shared memory for two halo stages (%d bytes each)", p.halo_bytes);
+  const size_t smem = fixed + (size_t)p.a_stages * p.halo_bytes;
 
   CUtensorMap tx, tw;
   {  // activations: 4-D {C, W, H, N}, box {64, W + 2, TH + 2, 1}; out-of-bounds elements read as zero = the padding

@@ -133,31 +133,37 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         }
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer =====
-      const uint32_t idesc = make_idesc<BN>();
-      uint32_t it = 0, t = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-        const uint32_t buf = t & 1, use = t >> 1;
-        mbar_wait(tmem_empty_bar + buf, (use & 1) ^ 1);  // epilogue has drained this accumulator
+  } else if (warp == 1) {  // ===== MMA issuer =====
+    // The whole warp runs the loop (so the descriptor arithmetic is warp-uniform and stays in uniform registers:
+    // with a lane-0-only loop every tcgen05.mma cost an ELECT + two R2UR moves and the issue interval was ~140
+    // cycles, capping the tensor pipe at 88 % for N = 256 and far lower for narrow tiles); one elected lane issues.
+    const uint32_t idesc = make_idesc<BN>();
+    uint32_t it = 0, t = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+      const uint32_t buf = t & 1, use = t >> 1;
+      mbar_wait(tmem_empty_bar + buf, (use & 1) ^ 1);  // epilogue has drained this accumulator
+      tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * BN;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int s = it % kStages;
+        const uint32_t phase = (it / kStages) & 1;
+        mbar_wait(full_bar + s, phase);
         tcgen05_fence_after();
-        const uint32_t tmem_d = tmem_base + buf * BN;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int s = it % kStages;
-          const uint32_t phase = (it / kStages) & 1;
-          mbar_wait(full_bar + s, phase);
-          tcgen05_fence_after();
-          const uint32_t a_addr = smem_u32(smem + (size_t)s * C::kStageBytes);
-          const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + kABytes);
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * C::kStageBytes);
+        const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + kABytes);
+        if (elect_one()) {
+          // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
+          if (kb == 0) umma_f16_c<false>(tmem_d, adesc, bdesc, idesc);
+          else umma_f16_c<true>(tmem_d, adesc, bdesc, idesc);
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
-            umma_f16(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
-          }
+          for (int k = 1; k < kBlockK / kUmmaK; ++k)
+            umma_f16_c<true>(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc);
           umma_commit(empty_bar + s);  // frees the smem slot once these MMAs have read it
         }
-        umma_commit(tmem_full_bar + buf);  // accumulator complete
+        __syncwarp();
       }
+      if (elect_one()) umma_commit(tmem_full_bar + buf);  // accumulator complete
+      __syncwarp();
     }
   } else if (warp >= 4) {  // ===== epilogue: TMEM -> registers -> global =====
     const int wq = warp & 3;  // TMEM lane quarter this warp may access
