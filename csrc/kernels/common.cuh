@@ -26,6 +26,12 @@ int check(cudaError_t e, const char* what);
     }                                                    \
   } while (0)
 
+// Bind the current device's primary context to the calling thread (legal during stream capture, unlike cudaFree(0)).
+inline void bind_context() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaSetDevice(dev);
+}
+
 constexpr int kSMs = 148;
 
 inline int sm_count() {

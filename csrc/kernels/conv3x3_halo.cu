@@ -244,6 +244,7 @@ extern "C" int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* st
   MFL_ARG(y && x && w, "conv3x3: null operand");
   MFL_ARG(mfl_conv3x3_supported(n, h, wd, c, k), "conv3x3: unsupported shape n=%d h=%d w=%d c=%d k=%d (need c in {64,128}, "
           "k %% 64 == 0, even w <= 126)", n, h, wd, c, k);
+  bind_context();  // the driver-API tensor-map calls need the primary context bound to this thread
   EncodeTiledFn fn = encode_fn();
   MFL_ARG(fn != nullptr, "conv3x3: cuTensorMapEncodeTiled is not available from this driver");
   Params p;

@@ -55,6 +55,9 @@ struct Epilogue {
   int32_t tma_store;  // C goes through swizzled smem slabs + cp.async.bulk.tensor stores (needs 16 B row pitch)
   // implicit-GEMM convolution (K11): A rows are output pixels, A columns are (r, s, c) - loaded with im2col TMA
   int32_t conv, out_h, out_w, stride, pad, filt_s, c_blocks;
+  // operand majors: 0 = K-major (reduction index contiguous), 1 = MN-major (tensor map is [reduction rows, M or N
+  // contiguous]; the tile arrives as 64 x 64 boxes, 8 KB apart, and the instruction descriptor transposes it)
+  int32_t a_mn, b_mn;
 };
 
 template <int ACT> __device__ __forceinline__ float apply_act(float x) {
@@ -126,10 +129,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             const int rs = kb / ep.c_blocks, cb = kb % ep.c_blocks;
             tma_load_im2col_4d(a_dst, &tmap_a, full_bar + s, cb * kBlockK, ow * ep.stride - ep.pad,
                                oh * ep.stride - ep.pad, img, (uint16_t)(rs % ep.filt_s), (uint16_t)(rs / ep.filt_s));
+          } else if (ep.a_mn) {
+#pragma unroll
+            for (int j = 0; j < kBlockM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmap_a, full_bar + s, m0 + 64 * j, kb * kBlockK);
           } else {
             tma_load_2d(a_dst, &tmap_a, full_bar + s, kb * kBlockK, m0);
           }
-          tma_load_2d(a_dst + kABytes, &tmap_b, full_bar + s, kb * kBlockK, n0);
+          if (ep.b_mn) {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(a_dst + kABytes + j * 8192, &tmap_b, full_bar + s, n0 + 64 * j, kb * kBlockK);
+          } else {
+            tma_load_2d(a_dst + kABytes, &tmap_b, full_bar + s, kb * kBlockK, n0);
+          }
         }
       }
     }
@@ -137,7 +149,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     // The whole warp runs the loop (so the descriptor arithmetic is warp-uniform and stays in uniform registers:
     // with a lane-0-only loop every tcgen05.mma cost an ELECT + two R2UR moves and the issue interval was ~140
     // cycles, capping the tensor pipe at 88 % for N = 256 and far lower for narrow tiles); one elected lane issues.
-    const uint32_t idesc = make_idesc<BN>();
+    const uint32_t idesc = make_idesc<BN>() | (ep.a_mn ? (1u << 15) : 0u) | (ep.b_mn ? (1u << 16) : 0u);
+    // descriptor units are 16 B: a K step of 16 elements is +32 B inside the swizzle row for a K-major operand and
+    // two 1024-byte atoms (16 reduction rows of 128 B) for an MN-major one, whose 64-wide blocks lie 8 KB apart
+    const uint64_t a_kstep = ep.a_mn ? 128 : 2, b_kstep = ep.b_mn ? 128 : 2;
+    const uint32_t a_lbo = ep.a_mn ? 512 : 1, b_lbo = ep.b_mn ? 512 : 1;
     uint32_t it = 0, t = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
       const uint32_t buf = t & 1, use = t >> 1;
@@ -150,14 +166,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         mbar_wait(full_bar + s, phase);
         tcgen05_fence_after();
         const uint32_t a_addr = smem_u32(smem + (size_t)s * C::kStageBytes);
-        const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + kABytes);
+        const uint64_t adesc = make_sw128_desc(a_addr, a_lbo), bdesc = make_sw128_desc(a_addr + kABytes, b_lbo);
         if (elect_one()) {
           // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
           if (kb == 0) umma_f16_c<false>(tmem_d, adesc, bdesc, idesc);
           else umma_f16_c<true>(tmem_d, adesc, bdesc, idesc);
 #pragma unroll
           for (int k = 1; k < kBlockK / kUmmaK; ++k)
-            umma_f16_c<true>(tmem_d, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc);
+            umma_f16_c<true>(tmem_d, adesc + (uint64_t)k * a_kstep, bdesc + (uint64_t)k * b_kstep, idesc);
           umma_commit(empty_bar + s);  // frees the smem slot once these MMAs have read it
         }
         __syncwarp();
@@ -280,6 +296,7 @@ static EncodeTiledFn encode_fn() {
 }
 
 static int make_map(CUtensorMap* map, const void* base, int rows, int k, int64_t ld, int box_rows, bool fp32 = false) {
+  bind_context();  // driver-API call below: this thread (e.g. an autograd worker) may not have the context bound
   EncodeTiledFn fn = encode_fn();
   MFL_ARG(fn != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
   const int esz = fp32 ? 4 : 2;
@@ -345,8 +362,47 @@ static EncodeIm2colFn encode_im2col_fn() {
 }
 }}  // namespace mfl::gemm
 
+namespace mfl { namespace gemm {
+// [reduction rows, mn contiguous] matrix -> 64 x 64 boxes (one 128-byte swizzle row per reduction index)
+static int make_map_mn(CUtensorMap* map, const void* base, int mn, int kred, int64_t ld) {
+  bind_context();
+  EncodeTiledFn fn = encode_fn();
+  MFL_ARG(fn != nullptr, "gemm: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {(cuuint64_t)mn, (cuuint64_t)kred};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64, 64};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MFL_ARG(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled (MN-major) failed with CUresult %d (mn=%d k=%d ld=%lld)", (int)r, mn,
+          kred, (long long)ld);
+  return 0;
+}
+}}  // namespace mfl::gemm
+
+static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b,
+                          int64_t ldb, int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act,
+                          void* stream);
+
 extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
                              const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream) {
+  return gemm_bf16_impl(c, c_dtype, ldc, a, lda, 0, b, ldb, 0, bias, bias_dtype, m, n, k, act, stream);
+}
+
+// C[m,n] = act(op(A) . op(B)^T + bias): a_mn = 0: A is [m, k] row-major; a_mn = 1: A is given as [k, m] row-major
+// (its transpose: the m index contiguous).  Same for B with n.  This is what the backward GEMMs of a Linear layer
+// need (dX = dY . W reads W [n_red, k_out] as an MN-major B; dW = dY^T . X reads both operands MN-major), so no
+// transposed copies are ever made.
+extern "C" int mfl_gemm_bf16_ex(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b,
+                                int64_t ldb, int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act,
+                                void* stream) {
+  return gemm_bf16_impl(c, c_dtype, ldc, a, lda, a_mn, b, ldb, b_mn, bias, bias_dtype, m, n, k, act, stream);
+}
+
+static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b,
+                          int64_t ldb, int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act,
+                          void* stream) {
   using namespace mfl::gemm;
   MFL_ARG(a && b && c && m > 0 && n > 0 && k > 0, "gemm: null operand or empty shape");
   MFL_ARG(c_dtype == MFL_BFLOAT16 || c_dtype == MFL_FLOAT32, "gemm: output must be BFLOAT16 or FLOAT32");
@@ -356,8 +412,8 @@ extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, i
   MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
   CUtensorMap ta, tb, tc;
   const int bn = n > 128 ? 256 : (n > 64 ? 128 : 64);
-  if (int rc = make_map(&ta, a, m, k, lda, kBlockM)) return rc;
-  if (int rc = make_map(&tb, b, n, k, ldb, bn)) return rc;
+  if (int rc = a_mn ? make_map_mn(&ta, a, m, k, lda) : make_map(&ta, a, m, k, lda, kBlockM)) return rc;
+  if (int rc = b_mn ? make_map_mn(&tb, b, n, k, ldb) : make_map(&tb, b, n, k, ldb, bn)) return rc;
   const bool c32 = c_dtype == MFL_FLOAT32;
   const bool tma_store = ((uintptr_t)c & 15) == 0 && (ldc * (c32 ? 4 : 2)) % 16 == 0;
   if (tma_store) {
@@ -365,7 +421,7 @@ extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, i
   } else {
     tc = ta;  // unused by the kernel
   }
-  Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store, 0, 0, 0, 0, 0, 0, 0};
+  Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store, 0, 0, 0, 0, 0, 0, 0, a_mn ? 1 : 0, b_mn ? 1 : 0};
   return launch_gemm(ta, tb, tc, ep, bn, act, c32, (cudaStream_t)stream);
 }
 

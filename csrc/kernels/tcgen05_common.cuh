@@ -48,10 +48,12 @@ __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.f
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // K-major, 128-byte swizzled operand tile starting at `smem_addr` (1024-byte aligned ring slot)
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+// For an MN-major operand (the non-reduction dimension contiguous: 64 elements = one 128-byte swizzle row, eight
+// consecutive reduction indices = one 1024-byte atom) pass lbo16 = distance between 64-element blocks >> 4.
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr, uint32_t lbo16 = 1) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);        // start address
-  d |= (uint64_t)1 << 16;                            // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(lbo16 & 0x3FFF) << 16;             // leading byte offset (unused for swizzled K-major)
   d |= (uint64_t)(1024 >> 4) << 32;                  // stride byte offset: 8 rows x 128 B
   d |= (uint64_t)1 << 46;                            // descriptor version (Blackwell)
   d |= (uint64_t)2 << 61;                            // layout type SWIZZLE_128B

@@ -156,6 +156,12 @@ int mfl_fabric_barrier(uint32_t* const* signal_pads, int rank, int world, int ch
  * Replaces the framework matmul under the learners' Linear layers (keras_model_ops.py:156). */
 int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
                   const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream);
+/* Same kernel with per-operand majors: a_mn = 0 -> A is [m, k] row-major (reduction index contiguous); a_mn = 1 -> A is
+ * passed as its transpose, [k, m] row-major (lda = its row pitch).  Likewise b_mn for B ([n, k] or [k, n]).  The backward
+ * GEMMs of a Linear layer (dX = dY . W, dW = dY^T . X) therefore need no transposed copies: the TMA loads 64 x 64 boxes
+ * and the instruction descriptor transposes in the tensor core. */
+int mfl_gemm_bf16_ex(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb,
+                     int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream);
 
 /* ---- K11: implicit-GEMM convolution forward on the same tcgen05 pipeline; the A operand is gathered by
  * im2col-mode TMA (cuTensorMapEncodeIm2col), never materialised.  NHWC bf16: x[n,h,w,c], w[k,r,s,c],

@@ -9,6 +9,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from metisfl_b200.ops.gemm import linear
+
 
 class Block(nn.Module):
     def __init__(self, d, heads):
@@ -30,9 +32,14 @@ class Block(nn.Module):
 
 
 class GPT2(nn.Module):
-    def __init__(self, vocab=50257, ctx=1024, d=1024, layers=24, heads=16):
+    def __init__(self, vocab=50257, ctx=1024, d=1024, layers=24, heads=16, pad_vocab_to=64):
         super().__init__()
-        self.wte = nn.Embedding(vocab, d)
+        # the embedding table / tied LM head is padded to a multiple of 64 rows (50257 -> 50304): an odd leading
+        # dimension forces unaligned legacy GEMM kernels for the head (8.7 of 42 ms per step, profiles/README.md);
+        # the extra rows are never indexed and only add 47 * d unused parameters
+        self.vocab = vocab
+        self.vocab_padded = (vocab + pad_vocab_to - 1) // pad_vocab_to * pad_vocab_to if pad_vocab_to else vocab
+        self.wte = nn.Embedding(self.vocab_padded, d)
         self.wpe = nn.Embedding(ctx, d)
         self.blocks = nn.ModuleList([Block(d, heads) for _ in range(layers)])
         self.ln_f = nn.LayerNorm(d)
@@ -53,7 +60,7 @@ class GPT2(nn.Module):
         x = self.wte(idx) + self.wpe(torch.arange(T, device=idx.device))
         for b in self.blocks:
             x = b(x)
-        return F.linear(self.ln_f(x), self.wte.weight)  # tied LM head
+        return linear(self.ln_f(x), self.wte.weight)  # tied LM head (tcgen05 GEMM on CUDA bf16, F.linear elsewhere)
 
 
 def gpt2_medium(**kw):

@@ -2,8 +2,8 @@
 ``linear`` built on it.
 
 ``y = act(x @ W^T + b)`` runs as ONE kernel (bias and activation fused in the TMEM epilogue).  The
-backward pass reuses the same K-major kernel: ``dX = dY @ W`` is fed ``W^T`` made contiguous, and
-``dW = dY^T @ X`` is fed the two transposes - a stop-gap until MN-major operand descriptors land.
+backward pass runs on the same kernel with MN-major operand descriptors (``gemm_ex``): ``dX = dY @ W`` reads ``W``
+and ``dW = dY^T @ X`` reads ``dY`` and ``X`` exactly as they are stored - no transposed copies.
 Reference counterpart: the framework matmuls under ``model.fit`` (``keras_model_ops.py:156``).
 """
 from __future__ import annotations
@@ -27,6 +27,7 @@ def _bind():
     if not _BOUND:
         vp, i, i64 = C.c_void_p, C.c_int, C.c_int64
         L.mfl_gemm_bf16.argtypes = [vp, i, i64, vp, i64, vp, i64, vp, i, i, i, i, i, vp]
+        L.mfl_gemm_bf16_ex.argtypes = [vp, i, i64, vp, i64, i, vp, i64, i, vp, i, i, i, i, i, vp]
         _BOUND = True
     return L
 
@@ -58,6 +59,35 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = Non
     return out
 
 
+def _ok2d(t: torch.Tensor) -> bool:
+    return t.dim() == 2 and t.stride(1) == 1 and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
+
+
+def gemm_ex(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = False,
+            out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """General-major product on the tcgen05 kernel, no transposed copies.
+
+    ``a_mn=False``: ``a`` is ``[M, K]``; ``a_mn=True``: ``a`` is ``[K, M]`` (the transpose of the logical operand).
+    ``b_mn=False``: ``b`` is ``[N, K]``; ``b_mn=True``: ``b`` is ``[K, N]``.  Returns ``[M, N]``.
+    """
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    if not _ok2d(a):
+        a = a.contiguous()
+    if not _ok2d(b):
+        b = b.contiguous()
+    m, k = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    n, k2 = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert k == k2, (a.shape, b.shape, a_mn, b_mn)
+    out = torch.empty(m, n, dtype=out_dtype, device=a.device)
+    rc = _bind().mfl_gemm_bf16_ex(out.data_ptr(), _lib.wire(out), out.stride(0), a.data_ptr(), a.stride(0), int(a_mn),
+                                  b.data_ptr(), b.stride(0), int(b_mn), None, 0, m, n, k, 0, _lib.stream_ptr())
+    _lib.check(rc, "mfl_gemm_bf16_ex")
+    return out
+
+
+MN_MAJOR_BACKWARD = True  # dX / dW straight from the stored layouts (no .t().contiguous() copies)
+
+
 class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias):
@@ -78,18 +108,22 @@ class _LinearFn(torch.autograd.Function):
         gx = gw = gb = None
         n, k = w.shape
         if ctx.needs_input_grad[0]:
-            if n % 8 == 0:
+            if MN_MAJOR_BACKWARD and n % 8 == 0 and k % 8 == 0:
+                gx = gemm_ex(g2, w, False, True).view(ctx.x_shape)          # dY [M,N] . W [N,K]: W read MN-major
+            elif n % 8 == 0:
                 gx = gemm_nt(g2, w.t().contiguous()).view(ctx.x_shape)      # [M,N] x [K,N]^T
             else:
                 gx = (g2 @ w).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
             m = g2.shape[0]
-            if m % 8 == 0:
+            if MN_MAJOR_BACKWARD and n % 8 == 0 and k % 8 == 0:
+                gw = gemm_ex(g2, x2, True, True)                            # dY^T . X: both read MN-major
+            elif m % 8 == 0:
                 gw = gemm_nt(g2.t().contiguous(), x2.t().contiguous())      # [N,M] x [K,M]^T
             else:
                 gw = g2.t() @ x2
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = g2.float().sum(0).to(ctx.bias_dtype)
+            gb = g2.sum(0, dtype=torch.float32).to(ctx.bias_dtype)  # fp32 accumulation without an fp32 copy of dY
         return gx, gw, gb
 
 

@@ -77,3 +77,30 @@ def test_mlp_trains_with_b200_linear():
         F.cross_entropy(model(x).float(), y).backward()
     for (n1, p1), (_, p2) in zip(ref.named_parameters(), ours.named_parameters()):
         torch.testing.assert_close(p2.grad.float(), p1.grad.float(), atol=2e-2, rtol=1e-1), n1
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 128, 64), (384, 320, 192), (4096, 1024, 1024), (200, 72, 136), (1024, 3072, 1024)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+def test_mn_major_operands_match_reference(m, n, k, a_mn, b_mn):
+    """General-major GEMM: operands handed over as their transposes, transposed inside the tensor core."""
+    from metisfl_b200.ops import gemm
+    g = torch.Generator().manual_seed(m + n + k)
+    a = torch.randn(m, k, generator=g).to(torch.bfloat16).cuda()
+    b = torch.randn(n, k, generator=g).to(torch.bfloat16).cuda()
+    ref = a.float() @ b.float().t()
+    out = gemm.gemm_ex(a.t().contiguous() if a_mn else a, b.t().contiguous() if b_mn else b, a_mn, b_mn)
+    torch.testing.assert_close(out.float(), ref, atol=k ** 0.5 * 3e-2, rtol=2e-2)
+
+
+def test_linear_backward_without_transposed_copies_matches_autograd():
+    from metisfl_b200.ops import gemm
+    torch.manual_seed(0)
+    x = torch.randn(6, 64, 256, device="cuda").to(torch.bfloat16).requires_grad_()
+    w = (torch.randn(512, 256, device="cuda") / 16).to(torch.bfloat16).requires_grad_()
+    b = torch.randn(512, device="cuda").to(torch.bfloat16).requires_grad_()
+    gy = torch.randn(6, 64, 512, device="cuda").to(torch.bfloat16)
+    gemm.linear(x, w, b).backward(gy)
+    xr, wr, br = (t.detach().float().requires_grad_() for t in (x, w, b))
+    torch.nn.functional.linear(xr, wr, br).backward(gy.float())
+    torch.testing.assert_close(x.grad.float(), xr.grad, atol=0.3, rtol=3e-2)
+    torch.testing.assert_close(w.grad.float(), wr.grad, atol=0.6, rtol=3e-2)
