@@ -180,6 +180,15 @@ int mfl_conv3x3_supported(int n, int h, int wd, int c, int k);
 int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* stats, int n, int h, int wd, int c, int k,
                      void* stream);
 
+/* ---- K16: fused softmax cross-entropy for a language-model head (csrc/kernels/cross_entropy.cu): per-row loss and
+ * d(loss)/d(logits) in one pass pair over bf16 logits, no fp32 copy.  logits [rows, vocab] bf16 with row pitch ld,
+ * targets [rows] int64 (rows with target == ignore_index contribute nothing), dlogits [rows, vocab] bf16 with pitch
+ * ldd receives (softmax - onehot) * scale, row_loss [rows] fp32 receives logsumexp - logit[target].
+ * Replaces the framework loss under keras_model_ops.py:156. */
+int mfl_lm_cross_entropy(void* dlogits, int64_t ldd, float* row_loss, const void* logits, int64_t ld,
+                         const long long* targets, int rows, int vocab, float scale, long long ignore_index,
+                         void* stream);
+
 /* ---- K14: fused BatchNorm2d (+ residual add) (+ ReLU), NHWC bf16 activations viewed as [m, c] rows
  * (m = N*H*W, c a power of two in [8, 2048]); fp32 affine / statistics (csrc/kernels/bn_relu.cu).
  * forward : training != 0: batch statistics (saved to save_mean / save_invstd, running statistics and

@@ -72,5 +72,13 @@ def gpt2_small(**kw):
 
 
 def lm_loss(logits, tokens):
-    """Next-token cross entropy; ``tokens`` are the inputs themselves."""
+    """Next-token cross entropy; ``tokens`` are the inputs themselves.  On CUDA bf16 logits the fused kernel K16
+    (``ops/loss.py``) computes loss and logit gradients without an fp32 copy of the [B*T, V] logits: the last
+    position of every sequence gets the ignore label instead of slicing the logits."""
+    if logits.is_cuda and logits.dtype == torch.bfloat16:
+        from metisfl_b200.ops.loss import lm_cross_entropy
+        b, t = tokens.shape
+        targets = torch.full((b, t), -100, dtype=torch.int64, device=tokens.device)
+        targets[:, :-1] = tokens[:, 1:]
+        return lm_cross_entropy(logits, targets, n_valid=b * (t - 1))
     return F.cross_entropy(logits[:, :-1].reshape(-1, logits.size(-1)).float(), tokens[:, 1:].reshape(-1))

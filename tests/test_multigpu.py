@@ -23,8 +23,13 @@ from metisfl_b200.models.zoo import ResNet18
 from metisfl_b200.ops import aggregation as agg
 k = {k}
 ex = [100 * (i + 1) for i in range(world * k)]
-eng = FederationEngine(ResNet18, EngineConfig(learners_per_gpu=k, use_cuda_graph=False, nvls=True), device=f"cuda:{{lr}}",
-                       examples_per_learner=ex)
+import torch.distributed._symmetric_memory as _symm
+try:  # NVLS needs multicast objects (NVSwitch + fabric manager); the peer-pointer path is tested either way
+    have_mc = bool(_symm._SymmetricMemory.has_multicast_support(_symm.DeviceType.CUDA, lr))
+except Exception:
+    have_mc = False
+eng = FederationEngine(ResNet18, EngineConfig(learners_per_gpu=k, use_cuda_graph=False, nvls=True if have_mc else False),
+                       device=f"cuda:{{lr}}", examples_per_learner=ex)
 g = torch.Generator().manual_seed(100 + rank)
 for j in range(k):
     for si, s in enumerate(eng.layout.segments):
