@@ -189,6 +189,11 @@ int mfl_lm_cross_entropy(void* dlogits, int64_t ldd, float* row_loss, const void
                          const long long* targets, int rows, int vocab, float scale, long long ignore_index,
                          void* stream);
 
+/* ---- K17: fp32 column sums of a bf16 [rows, cols] matrix (bias gradient of a Linear layer), csrc/kernels/colsum.cu.
+ * partial is [mfl_colsum_slices(rows), cols] fp32 and is overwritten; the caller adds the slices. */
+int mfl_colsum_slices(int rows);
+int mfl_colsum_bf16(float* partial, const void* x, int64_t ld, int rows, int cols, void* stream);
+
 /* ---- K14: fused BatchNorm2d (+ residual add) (+ ReLU), NHWC bf16 activations viewed as [m, c] rows
  * (m = N*H*W, c a power of two in [8, 2048]); fp32 affine / statistics (csrc/kernels/bn_relu.cu).
  * forward : training != 0: batch statistics (saved to save_mean / save_invstd, running statistics and

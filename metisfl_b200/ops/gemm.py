@@ -28,6 +28,8 @@ def _bind():
         vp, i, i64 = C.c_void_p, C.c_int, C.c_int64
         L.mfl_gemm_bf16.argtypes = [vp, i, i64, vp, i64, vp, i64, vp, i, i, i, i, i, vp]
         L.mfl_gemm_bf16_ex.argtypes = [vp, i, i64, vp, i64, i, vp, i64, i, vp, i, i, i, i, i, vp]
+        L.mfl_colsum_slices.argtypes = [i]
+        L.mfl_colsum_bf16.argtypes = [vp, vp, i64, i, i, vp]
         _BOUND = True
     return L
 
@@ -85,6 +87,18 @@ def gemm_ex(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = F
     return out
 
 
+def colsum(x: torch.Tensor) -> torch.Tensor:
+    """fp32 column sums of a bf16 ``[rows, cols]`` matrix (K17): the bias gradient, without an fp32 copy of ``x``."""
+    rows, cols = x.shape
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and cols % 8 == 0 and _ok2d(x) and _lib.available()):
+        return x.sum(0, dtype=torch.float32)
+    L = _bind()
+    partial = torch.empty(L.mfl_colsum_slices(rows), cols, dtype=torch.float32, device=x.device)
+    _lib.check(L.mfl_colsum_bf16(partial.data_ptr(), x.data_ptr(), x.stride(0), rows, cols, _lib.stream_ptr()),
+               "mfl_colsum_bf16")
+    return partial.sum(0) if partial.shape[0] > 1 else partial[0]
+
+
 MN_MAJOR_BACKWARD = True  # dX / dW straight from the stored layouts (no .t().contiguous() copies)
 
 
@@ -123,7 +137,7 @@ class _LinearFn(torch.autograd.Function):
             else:
                 gw = g2.t() @ x2
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = g2.sum(0, dtype=torch.float32).to(ctx.bias_dtype)  # fp32 accumulation without an fp32 copy of dY
+            gb = colsum(g2).to(ctx.bias_dtype)  # K17: fp32 accumulation straight from the bf16 dY
         return gx, gw, gb
 
 

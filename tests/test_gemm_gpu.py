@@ -104,3 +104,13 @@ def test_linear_backward_without_transposed_copies_matches_autograd():
     torch.nn.functional.linear(xr, wr, br).backward(gy.float())
     torch.testing.assert_close(x.grad.float(), xr.grad, atol=0.3, rtol=3e-2)
     torch.testing.assert_close(w.grad.float(), wr.grad, atol=0.6, rtol=3e-2)
+
+
+@pytest.mark.parametrize("rows,cols", [(4096, 1024), (4096, 3072), (100, 72), (7, 8), (5000, 4096)])
+def test_colsum_matches_reference(rows, cols):
+    from metisfl_b200.ops import gemm
+    x = torch.randn(rows, cols, device="cuda").to(torch.bfloat16)
+    got = gemm.colsum(x)
+    ref = x.float().sum(0)
+    assert got.dtype == torch.float32
+    torch.testing.assert_close(got, ref, atol=1e-2 * rows ** 0.5, rtol=1e-3)
