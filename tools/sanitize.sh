@@ -1,6 +1,6 @@
 #!/usr/bin/env bash
 # Sanitizer targets (the reference has none).
-#   tools/sanitize.sh memcheck|racecheck|synccheck|initcheck   - compute-sanitizer over the kernel tests
+#   tools/sanitize.sh memcheck|racecheck|synccheck|initcheck [core|train] - compute-sanitizer over the kernel tests
 #                                                                 (ONE tool per gpurun call, see B200_PROFILING.md)
 #   tools/sanitize.sh tsan                                      - ThreadSanitizer build of the host controller core (OpenMP off:
 #                                                                 libgomp is not instrumented and only yields false positives)
@@ -10,6 +10,11 @@ cd "$(dirname "$0")/.."
 case "${1:-memcheck}" in
   memcheck|racecheck|synccheck|initcheck)
     python build.py kernels
+    if [ "${2:-core}" = "train" ]; then  # the training-side kernels: K14 BatchNorm, K15 conv, K16 loss, K17 / MN-major GEMM
+      exec compute-sanitizer --tool "$1" --error-exitcode 1 \
+        python -m pytest tests/test_bn_gpu.py tests/test_loss_gpu.py tests/test_gemm_gpu.py tests/test_conv_gpu.py -x -q -m gpu \
+          -k "(three_launches and (shape2 or shape4 or eval or affine)) or lm_cross_entropy or colsum or (mn_major and 200) or (weight_stationary and 5-6)"
+    fi
     exec compute-sanitizer --tool "$1" --error-exitcode 1 \
       python -m pytest tests/test_kernels_gpu.py -x -q -m gpu -k "weighted_sum_fast or quantifier or optimizer_step or rolling"
     ;;
