@@ -194,6 +194,19 @@ int mfl_lm_cross_entropy(void* dlogits, int64_t ldd, float* row_loss, const void
 int mfl_colsum_slices(int rows);
 int mfl_colsum_bf16(float* partial, const void* x, int64_t ld, int rows, int cols, void* stream);
 
+/* ---- K18: fused residual-add + LayerNorm (csrc/kernels/layernorm.cu), bf16 activations [rows, d], d in
+ * {256, 512, 768, 1024}; gamma / beta are bf16 (param_bf16 != 0) or fp32, may be NULL.
+ * forward : r = a + b (b may be NULL: then r_out may be NULL and r = a), h = LN(r); mean / rstd [rows] fp32 are saved.
+ * backward: dr_out = (dr_in ? dr_in : 0) + LN'(dh); partial [mfl_ln_partial_rows(rows)][2][d] fp32 receives per-CTA
+ *           dgamma / dbeta rows (the caller sums over the first axis).
+ * Replaces the framework normalisation layers under keras_model_ops.py:156. */
+int mfl_ln_supported(int d);
+int mfl_ln_partial_rows(int rows);
+int mfl_add_ln_fwd(void* r_out, void* h_out, float* mean, float* rstd, const void* a, const void* b, const void* gamma,
+                   const void* beta, int param_bf16, int rows, int d, float eps, void* stream);
+int mfl_add_ln_bwd(void* dr_out, float* partial, const void* dh, const void* dr_in, const void* r, const void* gamma,
+                   int param_bf16, const float* mean, const float* rstd, int rows, int d, void* stream);
+
 /* ---- K14: fused BatchNorm2d (+ residual add) (+ ReLU), NHWC bf16 activations viewed as [m, c] rows
  * (m = N*H*W, c a power of two in [8, 2048]); fp32 affine / statistics (csrc/kernels/bn_relu.cu).
  * forward : training != 0: batch statistics (saved to save_mean / save_invstd, running statistics and

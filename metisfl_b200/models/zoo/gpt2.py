@@ -10,6 +10,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from metisfl_b200.ops.gemm import linear
+from metisfl_b200.ops.layernorm import add_layer_norm, layer_norm
 
 
 class _SplitQKV(torch.autograd.Function):
@@ -42,12 +43,19 @@ class Block(nn.Module):
         self.out = nn.Linear(4 * d, d)
         self.heads = heads
 
-    def forward(self, x):
-        B, T, D = x.shape
-        q, k, v = _SplitQKV.apply(self.qkv(self.ln1(x)).view(B, T, 3, self.heads, D // self.heads))
+    def attn_branch(self, h):
+        """proj(attention(qkv(h))) for an already normalised ``h``."""
+        B, T, D = h.shape
+        q, k, v = _SplitQKV.apply(self.qkv(h).view(B, T, 3, self.heads, D // self.heads))
         a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
-        x = x + self.proj(a.transpose(1, 2).reshape(B, T, D))
-        return x + self.out(F.gelu(self.fc(self.ln2(x)), approximate="tanh"))
+        return self.proj(a.transpose(1, 2).reshape(B, T, D))
+
+    def mlp_branch(self, h):
+        return self.out(F.gelu(self.fc(h), approximate="tanh"))
+
+    def forward(self, x):
+        x = x + self.attn_branch(self.ln1(x))
+        return x + self.mlp_branch(self.ln2(x))
 
 
 class GPT2(nn.Module):
@@ -76,10 +84,15 @@ class GPT2(nn.Module):
 
     def forward(self, idx):
         B, T = idx.shape
-        x = self.wte(idx) + self.wpe(torch.arange(T, device=idx.device))
-        for b in self.blocks:
-            x = b(x)
-        return linear(self.ln_f(x), self.wte.weight)  # tied LM head (tcgen05 GEMM on CUDA bf16, F.linear elsewhere)
+        r = self.wte(idx) + self.wpe(torch.arange(T, device=idx.device))
+        # Pre-LN blocks with every "residual add + next LayerNorm" pair fused (K18, ops/layernorm.py): r is the
+        # residual stream, h its normalised view for the next branch.  Off the GPU the two ops run separately.
+        h = layer_norm(r, self.blocks[0].ln1)
+        n = len(self.blocks)
+        for i, blk in enumerate(self.blocks):
+            r, h = add_layer_norm(r, blk.attn_branch(h), blk.ln2)
+            r, h = add_layer_norm(r, blk.mlp_branch(h), self.blocks[i + 1].ln1 if i + 1 < n else self.ln_f)
+        return linear(h, self.wte.weight)  # tied LM head (tcgen05 GEMM on CUDA bf16, F.linear elsewhere)
 
 
 def gpt2_medium(**kw):
