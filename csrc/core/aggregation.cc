@@ -54,6 +54,16 @@ void CheckCompatible(const VariableView& a, const VariableView& b) {
   if (a.t.dtype != b.t.dtype) throw std::runtime_error("tensors have different data types");
 }
 
+// A learner-supplied plaintext variable must match the reference metadata and carry as many bytes as it declares;
+// everything downstream indexes value.data() by the reference length, so this is checked before any loop runs.
+void CheckPayload(const VariableView& ref, const VariableView& x) {
+  CheckCompatible(ref, x);
+  const size_t esz = wire::DTypeSize(ref.t.dtype);
+  if (esz == 0) throw std::runtime_error("unsupported tensor data type");
+  if (x.t.value.size() < (size_t)ref.t.length * esz)
+    throw std::runtime_error("tensor payload shorter than its declared length");
+}
+
 }  // namespace
 
 void WeightedSumBytes(int dtype, size_t numel, const std::vector<const char*>& srcs,
@@ -139,15 +149,31 @@ void RollingAverageBase::Fold(const std::string* old_model, double w_old, const 
       scaled_[v].assign((size_t)nv[v].t.length * wire::DTypeSize(nv[v].t.dtype), '\0');
   }
   if (nv.size() != scaled_.size()) throw std::runtime_error("model shape changed between contributions");
+  if (old_model && ov.size() != scaled_.size()) throw std::runtime_error("previous model has a different shape");
+  // validate everything before S is touched: a malformed contribution must leave the rolling state intact
+  for (size_t v = 0; v < nv.size(); ++v) {
+    if (nv[v].ciphertext) continue;
+    CheckPayload(meta_[v], nv[v]);
+    if (old_model) CheckPayload(meta_[v], ov[v]);
+    if (scaled_[v].size() < (size_t)meta_[v].t.length * wire::DTypeSize(meta_[v].t.dtype))
+      throw std::runtime_error("rolling state does not match the model metadata");
+  }
+  std::string err;
 #pragma omp parallel for schedule(dynamic)
   for (long v = 0; v < (long)nv.size(); ++v) {
     if (nv[v].ciphertext) continue;
-    const int dt = nv[v].t.dtype;
-    const size_t n = nv[v].t.length;
-    if (old_model && v < (long)ov.size())  // S -= T(w_old * x_old)
-      WeightedSumBytes(dt, n, {ov[v].t.value.data()}, {-w_old}, scaled_[v].data(), true);
-    WeightedSumBytes(dt, n, {nv[v].t.value.data()}, {w_new}, scaled_[v].data(), true);  // S += T(w_new * x_new)
+    try {
+      const int dt = meta_[v].t.dtype;
+      const size_t n = meta_[v].t.length;
+      if (old_model)  // S -= T(w_old * x_old)
+        WeightedSumBytes(dt, n, {ov[v].t.value.data()}, {-w_old}, scaled_[v].data(), true);
+      WeightedSumBytes(dt, n, {nv[v].t.value.data()}, {w_new}, scaled_[v].data(), true);  // S += T(w_new * x_new)
+    } catch (const std::exception& e) {
+#pragma omp critical
+      err = e.what();
+    }
   }
+  if (!err.empty()) throw std::runtime_error(err);
 }
 
 Aggregated RollingAverageBase::Community() const {
@@ -187,9 +213,9 @@ Aggregated FedRec::Aggregate(const std::vector<LearnerModels>& block) {
       z_ += lm.WeightOf(0);
       ++contributors_;
     } else {
-      // swap the learner's previous contribution for its newest one
-      z_ += lm.WeightOf(1) - lm.WeightOf(0);
+      // swap the learner's previous contribution for its newest one (z moves only once the fold went through)
       Fold(lm.lineage[0].get(), lm.WeightOf(0), *lm.lineage[1], lm.WeightOf(1));
+      z_ += lm.WeightOf(1) - lm.WeightOf(0);
     }
   }
   return Community();
@@ -219,18 +245,30 @@ Aggregated FedAsync::Aggregate(const std::vector<LearnerModels>& block) {
     auto cv = ParseOrThrow(*community_);
     auto xv = ParseOrThrow(*x);
     if (cv.size() != xv.size()) throw std::runtime_error("FedAsync: model shape mismatch");
+    for (size_t v = 0; v < cv.size(); ++v) {
+      if (cv[v].ciphertext || xv[v].ciphertext) throw std::runtime_error("FedAsync aggregates plaintext variables only");
+      CheckPayload(cv[v], cv[v]);
+      CheckPayload(cv[v], xv[v]);
+    }
     std::vector<std::string> values(cv.size());
+    std::string err;
 #pragma omp parallel for schedule(dynamic)
     for (long v = 0; v < (long)cv.size(); ++v) {
-      const int dt = cv[v].t.dtype;
-      const size_t n = cv[v].t.length;
-      values[v].resize(n * wire::DTypeSize(dt));
-      if (dt <= 7) {  // integer bookkeeping variables: adopt the newest value
-        std::memcpy(values[v].data(), xv[v].t.value.data(), values[v].size());
-      } else {
-        WeightedSumBytes(dt, n, {cv[v].t.value.data(), xv[v].t.value.data()}, {1.0 - at, at}, values[v].data(), false);
+      try {
+        const int dt = cv[v].t.dtype;
+        const size_t n = cv[v].t.length;
+        values[v].resize(n * wire::DTypeSize(dt));
+        if (dt <= 7) {  // integer bookkeeping variables: adopt the newest value
+          std::memcpy(values[v].data(), xv[v].t.value.data(), values[v].size());
+        } else {
+          WeightedSumBytes(dt, n, {cv[v].t.value.data(), xv[v].t.value.data()}, {1.0 - at, at}, values[v].data(), false);
+        }
+      } catch (const std::exception& e) {
+#pragma omp critical
+        err = e.what();
       }
     }
+    if (!err.empty()) throw std::runtime_error(err);
     auto next = std::make_shared<std::string>();
     for (size_t v = 0; v < cv.size(); ++v) {
       std::string_view sv(values[v]);

@@ -100,6 +100,8 @@ StatusOr Controller::ReplaceCommunityModel(std::string bytes) {
     std::lock_guard<std::mutex> l(mu_);
     community_model_ = std::make_shared<std::string>(model);
     community_ = std::make_shared<std::string>(std::move(bytes));
+    community_ref_.reset();  // fabric learners install these bytes once; references start with the first aggregation
+    community_model_ref_.reset();
     if (auto* fa = dynamic_cast<FedAsync*>(aggregator_.get())) fa->SetCommunity(community_model_);
     community_lineage_.push_back(community_);
     while (community_lineage_.size() > std::max<uint32_t>(1, params_.community_lineage_length)) community_lineage_.pop_front();
@@ -151,6 +153,7 @@ void Controller::EvictLocked(const std::string& id, const char* why) {
   learners_.erase(id);
   local_tasks_.erase(id);
   store_->EraseModels({id});
+  device_w_.erase(id);
   Log("learner %s %s", id, why);
   // a shrinking federation may complete a synchronous barrier
   if (params_.protocol != Protocol::kAsynchronous && !learners_.empty() && !stop_) {
@@ -184,6 +187,15 @@ StatusOr Controller::LearnerCompletedTask(const std::string& id, const std::stri
     auto it = learners_.find(id);
     if (it == learners_.end() || it->second.auth_token != token)
       return {Status::kUnauthenticated, "Learner does not exist or incorrect credentials."};
+    // store first: a failing insert (Redis down, malformed bytes) must leave the round bookkeeping untouched so the
+    // learner can retry, and must reach the learner as a status instead of unwinding through the RPC thread
+    auto t0 = std::chrono::steady_clock::now();
+    try {
+      store_->InsertModel(id, std::make_shared<std::string>(std::move(model_bytes)));
+    } catch (const std::exception& e) {
+      return {Status::kInternal, std::string("model store insert failed: ") + e.what()};
+    }
+    const double insert_ms = ElapsedMs(t0);
     it->second.task_in_flight = false;
     // the task's own iteration stamps the metadata slot (falls back to the current round)
     uint32_t iter = meta.global_iteration ? meta.global_iteration : global_iteration_;
@@ -192,9 +204,7 @@ StatusOr Controller::LearnerCompletedTask(const std::string& id, const std::stri
       md.completed.push_back(id);
       md.train_received_at[id] = NowSeconds();
     }
-    auto t0 = std::chrono::steady_clock::now();
-    store_->InsertModel(id, std::make_shared<std::string>(std::move(model_bytes)));
-    if (!metadata_.empty()) metadata_.back().insertion_ms[id] = ElapsedMs(t0);
+    if (!metadata_.empty()) metadata_.back().insertion_ms[id] = insert_ms;
     if (!meta.global_iteration) meta.global_iteration = global_iteration_;
     local_tasks_[id].push_front(std::move(meta));
   }
@@ -269,8 +279,9 @@ void Controller::SendRunTasksLocked(const std::vector<std::string>& ids) {
   if (!items.empty() && dispatcher_) {
     auto d = dispatcher_;
     auto fm = community_;
+    auto ref = community_ref_;
     std::lock_guard<std::mutex> l(outbox_mu_);
-    outbox_.push_back([d, items, fm] { d->SendRunTasks(items, fm); });
+    outbox_.push_back([d, items, fm, ref] { d->SendRunTasks(items, fm, ref); });
   }
 }
 
@@ -296,9 +307,10 @@ void Controller::SendEvaluationTasksLocked(const std::vector<std::string>& ids, 
   if (!eps.empty() && dispatcher_) {
     auto d = dispatcher_;
     auto model = community_model_;
+    auto ref = community_model_ref_;
     const uint32_t bs = params_.batch_size;
     std::lock_guard<std::mutex> l(outbox_mu_);
-    outbox_.push_back([d, eps, model, bs, eval_index, it] { d->SendEvaluationTasks(eps, model, bs, eval_index, it); });
+    outbox_.push_back([d, eps, model, ref, bs, eval_index, it] { d->SendEvaluationTasks(eps, model, ref, bs, eval_index, it); });
   }
 }
 
@@ -324,13 +336,30 @@ void Controller::AfterBarrier(const std::vector<std::string>& to_schedule, const
   try {
     model = ComputeCommunityModel(selected, completing, md, &contributors);
   } catch (const std::exception& e) {
-    Log("aggregation failed: %s", e.what());
-    return;
+    // One bad upload must not stall the federation: the scheduler's barrier set is already consumed and no task is
+    // in flight, so nothing would ever call back in.  Keep the previous community model, close the round and
+    // re-issue tasks from it; the offending learner's next upload supersedes the bad contribution.
+    Log("aggregation failed (%s); round %s keeps the previous community model", e.what(),
+        std::to_string(global_iteration_));
+    aggregator_->Reset();
+    store_->ResetState();
+    ++aggregation_failures_;
+    pending_ref_.clear();
+    model.reset();
   }
   if (model && !model->empty()) {
-    RecordModelSize(*model, md);
+    if (md.quantifiers.empty()) RecordModelSize(*model, md);  // the device path already counted on the GPU (K4)
     community_model_ = model;
     community_ = std::make_shared<std::string>(wire::BuildFederatedModel(contributors, global_iteration_, *model));
+    if (!pending_ref_.empty()) {
+      community_model_ref_ = std::make_shared<std::string>(std::move(pending_ref_));
+      community_ref_ = std::make_shared<std::string>(
+          wire::BuildFederatedModel(contributors, global_iteration_, *community_model_ref_));
+    } else {
+      community_model_ref_.reset();
+      community_ref_.reset();
+    }
+    pending_ref_.clear();
     if (auto* fa = dynamic_cast<FedAsync*>(aggregator_.get())) fa->SetCommunity(community_model_);
     community_lineage_.push_back(community_);
     while (community_lineage_.size() > std::max<uint32_t>(1, params_.community_lineage_length)) community_lineage_.pop_front();
@@ -403,16 +432,111 @@ ModelBytes Controller::ComputeCommunityModel(const std::vector<std::string>& sel
       block.push_back(std::move(lm));
     }
     md.block_size.push_back((double)block.size());
-    result = aggregator_->Aggregate(block);
+    const bool first_block = b == 0, last_block = b + stride >= parts.size();
+    if (!AggregateBlockOnDevice(req, models, weights, first_block, last_block, md, &result)) {
+      result = aggregator_->Aggregate(block);
+      md.block_duration_ms.push_back(ElapsedMs(t_block));
+    }
     md.block_memory_kb.push_back((double)MaxRssKb());
-    md.block_duration_ms.push_back(ElapsedMs(t_block));
     store_->ResetState();
   }
   aggregator_->Reset();
   md.aggregation_completed_at = NowSeconds();
   md.aggregation_total_ms = ElapsedMs(t_start);
+  if (md.device_timed) {  // report what the GPUs measured, not the RPC round trip around it
+    md.aggregation_total_ms = 0;
+    for (double v : md.block_duration_ms) md.aggregation_total_ms += v;
+  }
   *contributors = result.num_contributors;
   return std::make_shared<std::string>(std::move(result.model));
+}
+
+static bool DeviceSlotOf(const std::string& model, wire::DeviceSlot* slot) {
+  std::vector<wire::VariableView> vars;
+  if (!wire::ParseModel(model, vars) || vars.empty() || !vars[0].t.slot.present) return false;
+  *slot = vars[0].t.slot;
+  return true;
+}
+
+bool Controller::AggregateBlockOnDevice(const std::vector<std::pair<std::string, int>>& req,
+                                        const std::map<std::string, std::vector<ModelBytes>>& models,
+                                        const std::map<std::string, double>& weights, bool first_block,
+                                        bool last_block, RuntimeMetadata& md, Aggregated* result) {
+  if (!dispatcher_ || params_.rule == "PWA") return false;
+  DeviceAggregateRequest dr;
+  dr.rule = params_.rule;
+  dr.global_iteration = global_iteration_;
+  dr.first_block = first_block;
+  dr.last_block = last_block;
+  bool any_device = false;
+  double z = device_z_;
+  std::map<std::string, double> new_w;
+  uint32_t new_contributors = 0;
+  for (auto& [id, n] : req) {
+    auto f = models.find(id);
+    if (f == models.end() || f->second.empty()) continue;
+    const auto& lineage = f->second;
+    DeviceSource src;
+    src.learner_id = id;
+    auto w = weights.find(id);
+    src.weight = w == weights.end() ? 0.0 : w->second;
+    wire::DeviceSlot slot;
+    if (DeviceSlotOf(*lineage.back(), &slot)) {
+      any_device = true;
+      src.rank = slot.device_rank; src.slot = slot.slot; src.version = slot.version;
+    } else {
+      src.staged_model = lineage.back();
+    }
+    if (params_.rule == "FedRec") {
+      // recency swap (federated_recency.cc:27-94): z += w_new - w_old when the learner contributed before
+      auto prev = device_w_.find(id);
+      wire::DeviceSlot old;
+      if (prev != device_w_.end() && lineage.size() >= 2 && DeviceSlotOf(*lineage[lineage.size() - 2], &old)) {
+        src.has_previous = true;
+        src.previous_slot = old.slot;
+        src.previous_weight = prev->second;
+        z += src.weight - prev->second;
+      } else if (prev != device_w_.end()) {
+        return false;  // the previous contribution is not addressable on the device: host path owns this learner
+      } else {
+        z += src.weight;
+        ++new_contributors;
+      }
+      new_w[id] = src.weight;
+    } else if (params_.rule == "FedAsync") {
+      auto lr = learners_.find(id);
+      const double staleness = lr == learners_.end() ? 0.0
+                                                     : (double)global_iteration_ - (double)lr->second.task_issued_iteration;
+      dr.mix = std::min(1.0, std::max(0.0, params_.fedasync_alpha * FedAsync::Staleness(params_.staleness_fn, staleness,
+                                                                                        params_.staleness_a,
+                                                                                        params_.staleness_b)));
+    }
+    dr.sources.push_back(std::move(src));
+  }
+  if (!any_device || dr.sources.empty()) return false;
+  dr.z = z;
+  DeviceAggregateResult out;
+  if (!dispatcher_->AggregateOnDevice(dr, &out)) return false;
+  if (!out.error.empty()) throw std::runtime_error("device aggregation failed: " + out.error);
+  if (out.model_ref.empty()) throw std::runtime_error("device aggregation returned no community model reference");
+  md.device_timed = true;
+  md.block_duration_ms.push_back(out.device_ms);
+  if (last_block) {
+    if (!out.quantifiers.empty()) md.quantifiers = out.quantifiers;
+    pending_ref_ = out.model_ref;
+  }
+  if (params_.rule == "FedRec") {
+    device_z_ = z;
+    device_contributors_ += new_contributors;
+    for (auto& kv : new_w) device_w_[kv.first] = kv.second;
+    result->num_contributors = device_contributors_;
+  } else if (params_.rule == "FedAsync") {
+    result->num_contributors = ++device_contributors_;
+  } else {
+    result->num_contributors = (first_block ? 0 : result->num_contributors) + (uint32_t)dr.sources.size();
+  }
+  result->model = out.model_bytes.empty() ? out.model_ref : std::move(out.model_bytes);
+  return true;
 }
 
 template <typename T> static uint32_t CountZeros(const char* p, size_t n) {
@@ -490,6 +614,11 @@ std::vector<LearnerRecord> Controller::GetLearners() {
 ModelBytes Controller::CommunityModel() {
   std::lock_guard<std::mutex> l(mu_);
   return community_;
+}
+
+uint32_t Controller::AggregationFailures() {
+  std::lock_guard<std::mutex> l(mu_);
+  return aggregation_failures_;
 }
 
 uint32_t Controller::GlobalIteration() {

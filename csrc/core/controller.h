@@ -79,15 +79,59 @@ struct TaskItem {
   float percent_validation = 0.f;
 };
 
+struct TensorQuant { uint32_t non_zeros = 0, zeros = 0, bytes = 0; };
+
+// ---- device-resident federation ----------------------------------------------------------
+// A learner that hosts a rank of the on-box NVLink fabric does not upload its model: MarkTaskCompleted carries a
+// Model whose TensorSpecs have no value bytes but a device_slot{rank, slot, offset, version}.  When the models of
+// an aggregation block are such references, the controller does not run its CPU loop; it names the slots, the
+// scaling factors it computed and the rule in a DeviceAggregateRequest and the dispatcher makes the GPU processes
+// run the aggregation kernel (K1 for FedAvg / FedStride, K3 for FedRec / FedAsync).  Learners outside the fabric
+// still upload bytes; their models travel inside the request and are unpacked into a staging slot (K12).
+struct DeviceSource {
+  std::string learner_id;
+  uint32_t rank = 0, slot = 0;
+  uint64_t version = 0;
+  double weight = 0.0;
+  bool has_previous = false;  // FedRec: the contribution this one replaces is still in the learner's slot ring
+  uint32_t previous_slot = 0;
+  double previous_weight = 0.0;
+  ModelBytes staged_model;  // non-null for an off-box learner (serialized metisfl.Model with bytes)
+};
+
+struct DeviceAggregateRequest {
+  std::string rule;
+  uint32_t global_iteration = 0;
+  std::vector<DeviceSource> sources;
+  double mix = 0.0;  // FedAsync: alpha * s(staleness) of the single source
+  double z = 0.0;    // FedRec: normaliser after this fold
+  bool first_block = true, last_block = true;  // FedStride streams blocks into one running result
+  bool quantify = true;
+};
+
+struct DeviceAggregateResult {
+  std::string model_ref;    // serialized Model, control-only (device_slot references to the community buffer)
+  std::string model_bytes;  // serialized Model with values, when the service layer asked a rank for them
+  double device_ms = 0.0;   // CUDA-event duration, max over the ranks that ran the kernel
+  std::vector<TensorQuant> quantifiers;  // K4 counts of the new community model
+  std::string error;
+};
+
 // Outbound RPC fan-out, implemented by the Python service layer.
 class Dispatcher {
  public:
   virtual ~Dispatcher() = default;
-  // federated_model = serialized metisfl.FederatedModel shared by all items
-  virtual void SendRunTasks(const std::vector<TaskItem>& items, const ModelBytes& federated_model) = 0;
+  // federated_model = serialized metisfl.FederatedModel shared by all items; federated_model_ref (may be null) is
+  // its control-only twin for learners that sit on the fabric
+  virtual void SendRunTasks(const std::vector<TaskItem>& items, const ModelBytes& federated_model,
+                            const ModelBytes& federated_model_ref) = 0;
   // model = serialized metisfl.Model; eval_index addresses the community evaluation lineage entry
   virtual void SendEvaluationTasks(const std::vector<LearnerEndpoint>& learners, const ModelBytes& model,
-                                   uint32_t batch_size, uint32_t eval_index, uint32_t global_iteration) = 0;
+                                   const ModelBytes& model_ref, uint32_t batch_size, uint32_t eval_index,
+                                   uint32_t global_iteration) = 0;
+  // Blocking; returns false when there is no device fabric behind this dispatcher (host aggregation is used then).
+  // Called with the controller lock held: the implementation must not call back into the controller.
+  virtual bool AggregateOnDevice(const DeviceAggregateRequest&, DeviceAggregateResult*) { return false; }
 };
 
 struct TaskMeta {  // the fields of metisfl.TaskExecutionMetadata the controller interprets
@@ -98,8 +142,6 @@ struct TaskMeta {  // the fields of metisfl.TaskExecutionMetadata the controller
   std::string serialized;  // the whole TaskExecutionMetadata, echoed by GetLocalTaskLineage
 };
 
-struct TensorQuant { uint32_t non_zeros = 0, zeros = 0, bytes = 0; };
-
 struct RuntimeMetadata {
   uint32_t global_iteration = 0;
   double started_at = 0, completed_at = 0;  // unix seconds
@@ -109,6 +151,7 @@ struct RuntimeMetadata {
   double aggregation_started_at = 0, aggregation_completed_at = 0, aggregation_total_ms = 0;
   std::vector<double> block_size, block_memory_kb, block_duration_ms;
   std::vector<TensorQuant> quantifiers;
+  bool device_timed = false;  // block durations are CUDA-event times reported by the GPU processes
 };
 
 struct CommunityEvaluation {
@@ -148,6 +191,7 @@ class Controller {
   std::vector<LearnerRecord> GetLearners();
   ModelBytes CommunityModel();  // serialized FederatedModel
   uint32_t GlobalIteration();
+  uint32_t AggregationFailures();
   std::vector<RuntimeMetadata> GetRuntimeMetadataLineage(int num_backtracks);
   std::vector<CommunityEvaluation> GetCommunityEvaluationLineage(int num_backtracks);
   std::map<std::string, std::vector<std::string>> GetLocalTaskLineage(const std::vector<std::string>& ids, int num_backtracks);
@@ -164,6 +208,11 @@ class Controller {
   ModelBytes ComputeCommunityModel(const std::vector<std::string>& selected, const std::string& completing,
                                    RuntimeMetadata& md, uint32_t* contributors);
   void RecordModelSize(const std::string& model, RuntimeMetadata& md);
+  // Device path of one aggregation block; returns false when the block has to run on the host.
+  bool AggregateBlockOnDevice(const std::vector<std::pair<std::string, int>>& req,
+                              const std::map<std::string, std::vector<ModelBytes>>& models,
+                              const std::map<std::string, double>& weights, bool first_block, bool last_block,
+                              RuntimeMetadata& md, Aggregated* result);
   void UpdateTaskTemplates(const std::vector<std::string>& ids);
   void SendRunTasksLocked(const std::vector<std::string>& ids);
   void SendEvaluationTasksLocked(const std::vector<std::string>& ids, uint32_t eval_index);
@@ -187,8 +236,16 @@ class Controller {
   std::vector<std::string> pending_initial_;
   ModelBytes community_;           // serialized FederatedModel
   ModelBytes community_model_;     // serialized Model inside it
+  ModelBytes community_ref_;       // control-only FederatedModel (device_slot references), null on the host path
+  ModelBytes community_model_ref_; // control-only Model inside it
+  std::string pending_ref_;        // model_ref of the aggregation in progress
+  // rolling state of FedRec on the device path (the sums live in HBM, the scalars here)
+  double device_z_ = 0.0;
+  uint32_t device_contributors_ = 0;
+  std::map<std::string, double> device_w_;
   std::deque<ModelBytes> community_lineage_;
   uint32_t global_iteration_ = 0;
+  uint32_t aggregation_failures_ = 0;
   std::vector<RuntimeMetadata> metadata_;
   std::vector<CommunityEvaluation> evaluations_;
   ThreadPool pool_;

@@ -64,37 +64,84 @@ py::tuple DoAggregate(AggregationFunction& f, const py::list& block) {
 
 class PyDispatcher : public Dispatcher {
  public:
-  PyDispatcher(py::object run, py::object eval) : run_(std::move(run)), eval_(std::move(eval)) {}
+  PyDispatcher(py::object run, py::object eval, py::object agg)
+      : run_(std::move(run)), eval_(std::move(eval)), agg_(std::move(agg)) {}
   ~PyDispatcher() override {
     py::gil_scoped_acquire g;
     run_ = py::object();
     eval_ = py::object();
+    agg_ = py::object();
   }
-  void SendRunTasks(const std::vector<TaskItem>& items, const ModelBytes& fm) override {
+  // request -> dict; the callback answers None (no fabric: aggregate on the host) or a dict with model_ref,
+  // model_bytes, device_ms, quantifiers [(non_zeros, zeros, bytes)], error
+  bool AggregateOnDevice(const DeviceAggregateRequest& r, DeviceAggregateResult* out) override {
+    py::gil_scoped_acquire g;
+    if (agg_.is_none()) return false;
+    try {
+      py::dict d;
+      d["rule"] = r.rule; d["global_iteration"] = r.global_iteration; d["mix"] = r.mix; d["z"] = r.z;
+      d["first_block"] = r.first_block; d["last_block"] = r.last_block; d["quantify"] = r.quantify;
+      py::list srcs;
+      for (auto& s : r.sources) {
+        py::dict sd;
+        sd["learner_id"] = s.learner_id; sd["device_rank"] = s.rank; sd["slot"] = s.slot; sd["version"] = s.version;
+        sd["weight"] = s.weight; sd["has_previous"] = s.has_previous; sd["previous_slot"] = s.previous_slot;
+        sd["previous_weight"] = s.previous_weight;
+        if (s.staged_model) sd["staged_model"] = py::bytes(*s.staged_model);
+        else sd["staged_model"] = py::none();
+        srcs.append(sd);
+      }
+      d["sources"] = srcs;
+      py::object res = agg_(d);
+      if (res.is_none()) return false;
+      py::dict rd = py::cast<py::dict>(res);
+      if (rd.contains("error") && !rd["error"].is_none()) out->error = py::cast<std::string>(rd["error"]);
+      if (rd.contains("model_ref")) out->model_ref = std::string(py::cast<py::bytes>(rd["model_ref"]));
+      if (rd.contains("model_bytes") && !rd["model_bytes"].is_none())
+        out->model_bytes = std::string(py::cast<py::bytes>(rd["model_bytes"]));
+      if (rd.contains("device_ms")) out->device_ms = py::cast<double>(rd["device_ms"]);
+      if (rd.contains("quantifiers"))
+        for (auto q : py::cast<py::list>(rd["quantifiers"])) {
+          py::tuple t = py::cast<py::tuple>(q);
+          out->quantifiers.push_back({py::cast<uint32_t>(t[0]), py::cast<uint32_t>(t[1]), py::cast<uint32_t>(t[2])});
+        }
+      return true;
+    } catch (py::error_already_set& e) {
+      out->error = e.what();
+      return true;
+    } catch (const std::exception& e) {
+      out->error = e.what();
+      return true;
+    }
+  }
+  void SendRunTasks(const std::vector<TaskItem>& items, const ModelBytes& fm, const ModelBytes& ref) override {
     py::gil_scoped_acquire g;
     try {
       py::list l;
       for (auto& it : items)
         l.append(py::make_tuple(it.learner.id, it.learner.hostname, it.learner.port, py::bytes(it.learner.public_certificate),
                                 it.global_iteration, it.num_local_updates, it.percent_validation));
-      run_(l, py::bytes(*fm));
+      if (ref) run_(l, py::bytes(*fm), py::bytes(*ref));  // the control-only twin only exists on the device path
+      else run_(l, py::bytes(*fm));
     } catch (py::error_already_set& e) {
       e.discard_as_unraisable("metisfl_b200 dispatcher (run tasks)");
     }
   }
-  void SendEvaluationTasks(const std::vector<LearnerEndpoint>& learners, const ModelBytes& model, uint32_t batch_size,
-                           uint32_t eval_index, uint32_t global_iteration) override {
+  void SendEvaluationTasks(const std::vector<LearnerEndpoint>& learners, const ModelBytes& model,
+                           const ModelBytes& ref, uint32_t batch_size, uint32_t eval_index,
+                           uint32_t global_iteration) override {
     py::gil_scoped_acquire g;
     try {
       py::list l;
       for (auto& ep : learners) l.append(py::make_tuple(ep.id, ep.hostname, ep.port, py::bytes(ep.public_certificate)));
-      eval_(l, py::bytes(*model), batch_size, eval_index, global_iteration);
+      if (ref) eval_(l, py::bytes(*model), batch_size, eval_index, global_iteration, py::bytes(*ref));
+      else eval_(l, py::bytes(*model), batch_size, eval_index, global_iteration);
     } catch (py::error_already_set& e) {
       e.discard_as_unraisable("metisfl_b200 dispatcher (evaluation tasks)");
     }
   }
  private:
-  py::object run_, eval_;
+  py::object run_, eval_, agg_;
 };
 
 py::dict MetaToDict(const RuntimeMetadata& m) {
@@ -114,6 +161,7 @@ py::dict MetaToDict(const RuntimeMetadata& m) {
   py::list q;
   for (auto& t : m.quantifiers) q.append(py::make_tuple(t.non_zeros, t.zeros, t.bytes));
   d["model_tensor_quantifiers"] = q;
+  d["device_timed"] = m.device_timed;
   return d;
 }
 
@@ -300,12 +348,13 @@ PYBIND11_MODULE(_core, m) {
       .def_readwrite("evaluate_community_model", &ControllerParams::evaluate_community_model);
 
   py::class_<Controller>(m, "Controller")
-      .def(py::init([](const ControllerParams& p, py::object run_cb, py::object eval_cb) {
+      .def(py::init([](const ControllerParams& p, py::object run_cb, py::object eval_cb, py::object agg_cb) {
              std::shared_ptr<Dispatcher> d;
-             if (!run_cb.is_none()) d = std::make_shared<PyDispatcher>(run_cb, eval_cb);
+             if (!run_cb.is_none()) d = std::make_shared<PyDispatcher>(run_cb, eval_cb, agg_cb);
              return new Controller(p, d);
            }),
-           py::arg("params"), py::arg("send_run_tasks") = py::none(), py::arg("send_evaluation_tasks") = py::none())
+           py::arg("params"), py::arg("send_run_tasks") = py::none(), py::arg("send_evaluation_tasks") = py::none(),
+           py::arg("aggregate_on_device") = py::none())
       .def("replace_community_model", [](Controller& c, const py::bytes& b) {
         std::string s(b);
         py::gil_scoped_release rel;
@@ -369,6 +418,7 @@ PYBIND11_MODULE(_core, m) {
         return py::bytes(*m);
       })
       .def("global_iteration", &Controller::GlobalIteration, py::call_guard<py::gil_scoped_release>())
+      .def("aggregation_failures", &Controller::AggregationFailures, py::call_guard<py::gil_scoped_release>())
       .def("get_runtime_metadata_lineage", [](Controller& c, int n) {
         std::vector<RuntimeMetadata> v;
         { py::gil_scoped_release rel; v = c.GetRuntimeMetadataLineage(n); }

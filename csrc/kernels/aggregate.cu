@@ -118,10 +118,11 @@ __global__ void __launch_bounds__(512) weighted_sum_kernel(const __grid_constant
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t u = (size_t)blockIdx.x * blockDim.x + threadIdx.x; u < units; u += stride) {
     float acc[kUnit];
+    // the accumulator and dst are rewritten below, so they are read with plain loads (PEER = true), never .nc
     if (acc_f32 && accumulate) {
-      Unit<MFL_FLOAT32>::load<false>(acc_f32, u, acc);
+      Unit<MFL_FLOAT32>::load<true>(acc_f32, u, acc);
     } else if (!acc_f32 && accumulate) {
-      Unit<DST>::template load<false>(dst, u, acc);
+      Unit<DST>::template load<true>(dst, u, acc);
     } else {
 #pragma unroll
       for (int i = 0; i < kUnit; ++i) acc[i] = 0.f;
@@ -362,20 +363,35 @@ __global__ void __launch_bounds__(512, 2) fused_aggregate_kernel(const __grid_co
   // Phase 2: all shards have landed everywhere.
   peer_barrier(fa.pads, fa.rank, fa.world, slot1, /*have_prior_writes=*/true);
   // Phase 3 (optional): install the new community parameters as this rank's fp32 master copy.
+  // The flag barriers pair block b here with block b of every peer and with nothing else, so block b may only read
+  // what block b of some rank wrote in phase 1.  The loop therefore walks the shards rank by rank with the writer's
+  // own index mapping (shard begin + block * blockDim + thread + k * grid stride) instead of striding over the whole
+  // segment, whose units belong to blocks this one never synchronised with.
   if (fa.install_f32) {
     const mfl_segment& sg = fa.seg[0];
     const char* c = reinterpret_cast<const char*>(fa.out[fa.rank]) + sg.offset_bytes;
     const size_t units = sg.numel / kUnit;
+    const size_t upr = (units + fa.world - 1) / fa.world;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t u = (size_t)blockIdx.x * blockDim.x + threadIdx.x; u < units; u += stride) {
-      float f[kUnit];
-      if (sg.dtype == MFL_BFLOAT16) VecTraits<MFL_BFLOAT16>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + u), f);
-      else if (sg.dtype == MFL_FLOAT16) VecTraits<MFL_FLOAT16>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + u), f);
-      else {
-        VecTraits<MFL_FLOAT32>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + 2 * u), f);
-        VecTraits<MFL_FLOAT32>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + 2 * u + 1), f + 4);
+    const size_t lane = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool vec_mapped = fa.n_mc > 0 && sg.dtype == MFL_FLOAT32;  // the NVLS writer strides 16-byte vectors
+    for (int r = 0; r < fa.world; ++r) {
+      const size_t begin = min(units, upr * r), end = min(units, begin + upr);
+      if (vec_mapped) {
+        for (size_t v = 2 * begin + lane; v < 2 * end; v += stride)
+          st_stream(reinterpret_cast<uint4*>(fa.install_f32) + v, ld_peer(reinterpret_cast<const uint4*>(c) + v));
+        continue;
       }
-      Unit<MFL_FLOAT32>::store(fa.install_f32, u, f);
+      for (size_t u = begin + lane; u < end; u += stride) {
+        float f[kUnit];
+        if (sg.dtype == MFL_BFLOAT16) VecTraits<MFL_BFLOAT16>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + u), f);
+        else if (sg.dtype == MFL_FLOAT16) VecTraits<MFL_FLOAT16>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + u), f);
+        else {
+          VecTraits<MFL_FLOAT32>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + 2 * u), f);
+          VecTraits<MFL_FLOAT32>::unpack(ld_peer(reinterpret_cast<const uint4*>(c) + 2 * u + 1), f + 4);
+        }
+        Unit<MFL_FLOAT32>::store(fa.install_f32, u, f);
+      }
     }
     if (blockIdx.x == 0 && threadIdx.x < sg.numel % kUnit) {
       const size_t i = units * kUnit + threadIdx.x;
@@ -409,6 +425,8 @@ static int launch_ws(int dst_dtype, const AggArgs& a, void* dst, float* acc, int
 }  // namespace mfl
 
 using namespace mfl;
+
+MFL_SPIN_TIMEOUT_READER(mfl_spin_timeouts_aggregate)
 
 extern "C" int mfl_weighted_sum(void* dst, int dst_dtype, const void* const* srcs, const double* weights,
                                 int n_src, int src_dtype, size_t numel, float* acc_f32, int accumulate,
@@ -450,6 +468,17 @@ extern "C" int mfl_rolling_update(void* community, int dtype, float* scaled_sum,
   MFL_ARG(z != 0.0 || !community, "rolling_update: z must be non-zero when a community model is written");
   if (numel == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
+  // float-family models with a community output take the vectorised fold kernel (16-byte accesses, all loads of a
+  // unit in flight together); everything else keeps the element-wise kernel below
+  if (community && is_float_fast(dtype) && aligned16(community) && aligned16(scaled_sum) && aligned16(x_new) &&
+      aligned16(x_old)) {
+    mfl_segment sg{0, numel, dtype, 0};
+    const uint64_t off = 0;
+    void* outs[1] = {community};
+    const int blocks = (int)std::min<size_t>((numel / 8 + 255) / 256 + 1, (size_t)sm_count() * 4);
+    return mfl_async_fold(x_new, w_new, x_old, w_old, 1.0, 1.0 / z, scaled_sum, &off, &sg, 1, outs, nullptr, 1,
+                          nullptr, 0, nullptr, 0, nullptr, blocks, stream);
+  }
   int blocks = (int)std::min<size_t>((numel + 255) / 256, (size_t)sm_count() * 8);
   const float inv_z = community ? (float)(1.0 / z) : 0.f;
   MFL_DISPATCH_ALL(dtype, T,
@@ -499,6 +528,9 @@ static int fused_aggregate_impl(const void* const* src_slots, const double* weig
             "fused_aggregate: segment %d misaligned or bad dtype", s);
   }
   local.install_f32 = install_f32;
+  MFL_ARG(!install_f32 || (!segments[0].exact && is_float_fast(segments[0].dtype) && aligned16(install_f32)),
+          "fused_aggregate: the fp32 install needs segment 0 to be a float-family, non-exact segment and a 16-byte "
+          "aligned destination");
   MFL_ARG(n_mc >= 0 && n_mc <= MFL_MAX_MC_SRC, "fused_aggregate: n_mc=%d outside [0,%d]", n_mc, MFL_MAX_MC_SRC);
   MFL_ARG(n_mc == 0 || (mc_out && world > 1), "fused_aggregate: NVLS mode needs a multicast output and world > 1");
   local.n_mc = n_mc;

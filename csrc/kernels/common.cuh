@@ -181,17 +181,68 @@ __device__ __forceinline__ void store_from_float(void* p, int dt, size_t i, floa
 // ---- system-scope flag primitives (K13) ----------------------------------------------------
 // put: flip the peer's flag 0 -> 1 (release); wait: flip our own flag 1 -> 0 (acquire).
 // Self-resetting, so no epoch bookkeeping and the pads can be reused by back-to-back launches.
+//
+// Every spin is bounded: a rank that never shows up (dead process, a launch the host never made) must not wedge the
+// GPU.  After kSpinTimeoutNs the waiter gives up, counts the event in g_spin_timeouts (read it with
+// mfl_spin_timeouts()) and carries on; the result of that launch is garbage and the fabric has to be rebuilt, but
+// the device stays usable.
+constexpr unsigned long long kSpinTimeoutNs = 20ull * 1000 * 1000 * 1000;
+// one counter per translation unit (the library is built without relocatable device code); a unit that spins
+// exports a reader with MFL_SPIN_TIMEOUT_READER and mfl_spin_timeouts() in runtime.cu adds them up
+static __device__ unsigned int g_spin_timeouts = 0;
+#define MFL_SPIN_TIMEOUT_READER(name)                                                          \
+  extern "C" int name(void) {                                                                  \
+    unsigned int n = 0;                                                                        \
+    if (cudaMemcpyFromSymbol(&n, ::mfl::g_spin_timeouts, sizeof(n)) != cudaSuccess) return -1; \
+    return (int)n;                                                                             \
+  }
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+struct SpinGuard {
+  unsigned long long t0 = 0;
+  unsigned int n = 0;
+  __device__ __forceinline__ bool expired() {  // true once the budget is used up
+    if ((++n & 0x3ff) != 0) return false;
+    const unsigned long long now = global_ns();
+    if (t0 == 0) { t0 = now; return false; }
+    if (now - t0 < kSpinTimeoutNs) return false;
+    atomicAdd(&g_spin_timeouts, 1u);
+    return true;
+  }
+};
 __device__ __forceinline__ void flag_put(uint32_t* addr) {
   uint32_t old;
+  SpinGuard g;
   do {
     asm volatile("atom.global.release.sys.cas.b32 %0, [%1], 0, 1;" : "=r"(old) : "l"(addr) : "memory");
-  } while (old != 0u);
+  } while (old != 0u && !g.expired());
 }
 __device__ __forceinline__ void flag_wait(uint32_t* addr) {
   uint32_t old;
+  SpinGuard g;
   do {
     asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], 1, 0;" : "=r"(old) : "l"(addr) : "memory");
-  } while (old != 1u);
+  } while (old != 1u && !g.expired());
+}
+// Monotonic 64-bit counters (version numbers, per-learner "task n is published"): one writer, any readers.
+__device__ __forceinline__ void counter_publish(unsigned long long* addr, unsigned long long v) {
+  asm volatile("st.global.release.sys.u64 [%0], %1;" :: "l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long counter_read(const unsigned long long* addr) {
+  unsigned long long v;
+  asm volatile("ld.global.acquire.sys.u64 %0, [%1];" : "=l"(v) : "l"(addr) : "memory");
+  return v;
+}
+// returns false on timeout
+__device__ __forceinline__ bool counter_wait_ge(const unsigned long long* addr, unsigned long long v) {
+  SpinGuard g;
+  while (counter_read(addr) < v)
+    if (g.expired()) return false;
+  return true;
 }
 
 // Block-level barrier with the same block index on every peer.  pads[t] is rank t's pad

@@ -32,6 +32,15 @@ using namespace mfl;
 
 extern "C" const char* mfl_last_error(void) { return g_err; }
 
+// Number of in-kernel waits on this device that gave up after their time budget (common.cuh: SpinGuard).  Reads
+// device symbols, so it synchronises with the device: for tests and error paths, not for the hot loop.
+extern "C" int mfl_spin_timeouts_aggregate(void);
+extern "C" int mfl_spin_timeouts_async(void);
+extern "C" int mfl_spin_timeouts(void) {
+  const int a = mfl_spin_timeouts_aggregate(), b = mfl_spin_timeouts_async();
+  return (a < 0 || b < 0) ? -1 : a + b;
+}
+
 extern "C" int mfl_sm_count(int device) {
   int n = 0;
   if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1;

@@ -49,11 +49,7 @@ int mfl_weighted_sum(void* dst, int dst_dtype, const void* const* srcs, const do
 int mfl_rolling_update(void* community, int dtype, float* scaled_sum, const void* x_new, double w_new,
                        const void* x_old, double w_old, double z, size_t numel, void* stream);
 
-/* ---- K1 fused over NVLink: reduce-scatter + all-gather (+ fp32 install) in ONE launch -----
- * Every rank launches the same call.  Rank r owns shard r of each segment, reads it from every
- * source slot (peer-mapped pointers), applies weights, and stores the result into EVERY rank's
- * output buffer; in-kernel flag barriers over the signal pads order the phases.
- */
+/* One dtype-homogeneous segment of a model arena (shared by the fused kernels below). */
 typedef struct {
   uint64_t offset_bytes;   /* start of the segment inside every slot / output buffer */
   uint64_t numel;
@@ -61,6 +57,44 @@ typedef struct {
   int32_t exact;           /* reference truncation semantics for this segment */
 } mfl_segment;
 
+/* ---- K3 fused over NVLink: one asynchronous community update in one launch on the executor GPU ----------
+ * state = decay * state + w_new * x_new - w_old * x_old   (fp32, local to the caller)
+ * C     = cast(state * post_scale), stored into EVERY rank's community buffer: through mc_out (a multicast
+ *         address, one multimem.st per 16 bytes) when non-NULL, else with peer stores to out_bufs[0..world).
+ * FedRec (federated_recency.cc:27-94): decay 1, post_scale 1/z, x_old = the learner's previous contribution.
+ * FedAsync (extension): decay 1 - a_t, w_new = a_t, post_scale 1, x_old NULL.
+ * x_new / x_old may be peer-mapped slots of another GPU.  Integer ("exact") segments copy x_new.
+ * Ordering: if wait_flag is non-NULL the kernel first waits until *wait_flag >= wait_value (the slot's owner
+ * released it with mfl_flag_signal); when every CTA has fenced its stores the last one publishes new_version into
+ * version_flags[0..world) (release, system scope).  done_counter is a zero-initialised device word owned by the
+ * caller (it resets itself).  Pass version_flags = done_counter = NULL for a purely local update.
+ * state_elem_offsets[s] is the element offset of segment s inside `state` (multiples of 4). */
+int mfl_async_fold(const void* x_new, double w_new, const void* x_old, double w_old, double decay,
+                   double post_scale, float* state, const uint64_t* state_elem_offsets,
+                   const mfl_segment* segments, int n_segments, void* const* out_bufs, void* mc_out, int world,
+                   unsigned long long* const* version_flags, unsigned long long new_version,
+                   const unsigned long long* wait_flag, unsigned long long wait_value,
+                   unsigned int* done_counter, int n_blocks, void* stream);
+/* Monotonic 64-bit counters in (peer-mapped) device memory: release-store on the stream / bounded wait on the
+ * stream.  Never enqueue a wait and the signal it waits for on the SAME GPU in different streams - order those
+ * with CUDA events instead (two kernels of one GPU are not guaranteed to run concurrently). */
+int mfl_flag_signal(unsigned long long* flag, unsigned long long value, void* stream);
+int mfl_flag_wait(const unsigned long long* flag, unsigned long long value, void* stream);
+/* Copy the newest community model (version v = *version_flag, buffer v % n_comm) into a learner's working arena
+ * and, optionally, segment 0 as fp32 master weights.  status[0] receives v; status[1] counts CTAs that observed
+ * more than n_comm - 2 newer versions by the time they finished (a possibly torn copy - retry). */
+int mfl_snapshot_install(const void* const* community_bufs, int n_comm, const unsigned long long* version_flag,
+                         unsigned long long* status, void* dst, size_t nbytes, float* master_f32,
+                         const mfl_segment* segment0, int n_blocks, void* stream);
+/* In-kernel waits that ran out of their 20 s budget on the current device since the library was loaded
+ * (synchronises with the device; for tests and error paths). */
+int mfl_spin_timeouts(void);
+
+/* ---- K1 fused over NVLink: reduce-scatter + all-gather (+ fp32 install) in ONE launch -----
+ * Every rank launches the same call.  Rank r owns shard r of each segment, reads it from every
+ * source slot (peer-mapped pointers), applies weights, and stores the result into EVERY rank's
+ * output buffer; in-kernel flag barriers over the signal pads order the phases.
+ */
 int mfl_fused_aggregate(const void* const* src_slots, const double* weights, int n_src,
                         void* const* out_bufs, uint32_t* const* signal_pads, int rank, int world,
                         const mfl_segment* segments, int n_segments,

@@ -19,6 +19,12 @@ the other.  Extensions use fresh field numbers only:
   asynchronous mixing rule.
 * ``ProtocolSpecs.task_deadline_secs = 15``: controller-side eviction of
   learners that never report (fixes reference quirk Q9).
+* ``JoinFederationRequest.fabric = 15`` (``FabricMembership``): a learner that
+  hosts a rank of the on-box NVLink fabric says so when it joins.
+* ``LearnerService.AggregateOnDevice``: the controller's command to the GPU
+  processes to run the aggregation kernels over the device slots it names
+  (the reference has no counterpart: its controller sums protobuf bytes on the
+  CPU, ``controller.cc:795-950``).
 """
 from __future__ import annotations
 
@@ -388,8 +394,11 @@ _controller_msgs = [
          rep("metadata", 1, "FederatedTaskRuntimeMetadata"), f("json_metadata", 2, "string")),
     _Msg("GetParticipatingLearnersRequest"),
     _Msg("GetParticipatingLearnersResponse", rep("learner", 1, "LearnerDescriptor")),
+    _Msg("FabricMembership",  # extension: this learner is rank `rank` of a `world`-GPU peer-memory fabric
+         f("fabric_id", 1, "string"), f("rank", 2, "uint32"), f("world", 3, "uint32"),
+         f("staging_slots", 4, "uint32")),
     _Msg("JoinFederationRequest", f("server_entity", 1, "ServerEntity"),
-         f("local_dataset_spec", 2, "DatasetSpec")),
+         f("local_dataset_spec", 2, "DatasetSpec"), f("fabric", 15, "FabricMembership")),
     _Msg("JoinFederationResponse", f("ack", 1, "Ack"), f("learner_id", 2, "string"),
          f("auth_token", 3, "string"), f("ssl_config", 4, "SSLConfig")),
     _Msg("LearnerLocalModelResponse", f("server_entity", 1, "ServerEntity"),
@@ -405,7 +414,7 @@ _controller_msgs = [
 ]
 
 LEARNER = "metisfl/proto/learner.proto"
-LEARNER_RPCS = ["EvaluateModel", "GetServicesHealthStatus", "RunTask", "ShutDown"]
+LEARNER_RPCS = ["EvaluateModel", "GetServicesHealthStatus", "RunTask", "ShutDown", "AggregateOnDevice"]
 _learner_msgs = [
     _Msg("EvaluateModelRequest",
          f("model", 1, "Model"),
@@ -417,6 +426,30 @@ _learner_msgs = [
     _Msg("RunTaskRequest", f("federated_model", 1, "FederatedModel"),
          f("task", 2, "LearningTask"), f("hyperparameters", 3, "Hyperparameters")),
     _Msg("RunTaskResponse", f("ack", 1, "Ack")),
+    # ---- extension: controller-commanded aggregation over device slots -------------------------
+    _Msg("DeviceModelSource",
+         f("learner_id", 1, "string"),
+         f("device_rank", 2, "uint32"), f("slot", 3, "uint32"), f("version", 4, "uint64"),
+         f("weight", 5, "double"),
+         f("has_previous", 6, "bool"), f("previous_slot", 7, "uint32"), f("previous_weight", 8, "double"),
+         f("staged_model", 9, "Model")),       # off-box learner: wire model, unpacked into a staging slot (K12)
+    _Msg("AggregateOnDeviceRequest",
+         f("rule", 1, "string"),               # FedAvg | FedStride | FedRec | FedAsync
+         f("global_iteration", 2, "uint32"),
+         rep("sources", 3, "DeviceModelSource"),
+         f("mix", 4, "double"),                # FedAsync: alpha * s(staleness)
+         f("z", 5, "double"),                  # FedRec: normaliser after this fold
+         f("first_block", 6, "bool"), f("last_block", 7, "bool"),
+         f("quantify", 8, "bool"),
+         f("return_model_bytes", 9, "bool"),
+         f("executor_rank", 10, "uint32")),
+    _Msg("AggregateOnDeviceResponse",
+         f("ack", 1, "Ack"),
+         f("device_ms", 2, "double"),          # CUDA-event time of this rank's launch(es)
+         rep("quantifiers", 3, "TensorQuantifier"),
+         f("community_ref", 4, "Model"),       # control-only: metadata + device_slot references
+         f("community_model", 5, "Model"),     # with bytes, only when asked for
+         f("version", 6, "uint64")),
 ]
 
 _TSFILE = "google/protobuf/timestamp.proto"

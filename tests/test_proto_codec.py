@@ -81,7 +81,11 @@ def test_contract_field_numbers():
     assert num(controller_pb2.MarkTaskCompletedRequest, "task") == 3
     assert model_pb2.DType.FLOAT64 == 9 and model_pb2.DType.BFLOAT16 == 11
     svc = controller_pb2.DESCRIPTOR.services_by_name["ControllerService"]
-    assert len(svc.methods) == 12 and len(learner_pb2.DESCRIPTOR.services_by_name["LearnerService"].methods) == 4
+    lsvc = learner_pb2.DESCRIPTOR.services_by_name["LearnerService"]
+    # the reference's 4 learner RPCs first and unchanged, then the AggregateOnDevice extension
+    assert len(svc.methods) == 12 and [m.name for m in lsvc.methods][:4] == [
+        "EvaluateModel", "GetServicesHealthStatus", "RunTask", "ShutDown"]
+    assert [m.name for m in lsvc.methods][4:] == ["AggregateOnDevice"]
 
 
 def test_factories_build_the_oneofs():
