@@ -67,6 +67,13 @@ def lib():
         L.mfl_fabric_enable_peers.argtypes = [i, i]
         L.mfl_fabric_barrier.argtypes = [C.POINTER(vp), i, i, i, vp]
         L.mfl_sm_count.argtypes = [i]
+        ull = C.c_ulonglong
+        L.mfl_async_fold.argtypes = [vp, d, vp, d, d, d, vp, C.POINTER(C.c_uint64), C.POINTER(Segment), i,
+                                     C.POINTER(vp), vp, i, C.POINTER(vp), ull, vp, ull, vp, i, vp]
+        L.mfl_flag_signal.argtypes = [vp, ull, vp]
+        L.mfl_flag_wait.argtypes = [vp, ull, vp]
+        L.mfl_snapshot_install.argtypes = [C.POINTER(vp), i, vp, vp, vp, sz, vp, C.POINTER(Segment), i, vp]
+        L.mfl_spin_timeouts.argtypes = []
         _LIB = L
     return _LIB
 
@@ -103,6 +110,16 @@ def wire(t_or_dtype) -> int:
 
 def voidp_array(ptrs):
     return (C.c_void_p * len(ptrs))(*[C.c_void_p(p) for p in ptrs])
+
+
+def segment_array(segments):
+    """``(offset_bytes, numel, torch dtype or wire code, exact)`` rows -> ``mfl_segment[]``."""
+    segs = (Segment * len(segments))()
+    for s, (off, numel, dt, exact) in zip(segs, segments):
+        s.offset_bytes, s.numel = int(off), int(numel)
+        s.dtype = dt if isinstance(dt, int) else wire(dt)
+        s.exact = int(bool(exact))
+    return segs
 
 
 def double_array(vals):

@@ -140,11 +140,7 @@ def fused_aggregate(src_slot_ptrs: Sequence[int], weights: Sequence[float], out_
     NVSwitch and multicast back (NVLS); the slots must then hold pre-scaled models and all learners participate.
     """
     L = _lib.lib()
-    segs = (_lib.Segment * len(segments))()
-    for s, (off, numel, dt, exact) in zip(segs, segments):
-        s.offset_bytes, s.numel = int(off), int(numel)
-        s.dtype = dt if isinstance(dt, int) else _lib.wire(dt)
-        s.exact = int(bool(exact))
+    segs = _lib.segment_array(segments)
     if n_blocks is None:
         n_blocks = default_fused_blocks()
     if mc_src_ptrs:
@@ -163,3 +159,49 @@ def fused_aggregate(src_slot_ptrs: Sequence[int], weights: Sequence[float], out_
 
 def default_fused_blocks() -> int:
     return 296
+
+
+# ---- K3 fused over NVLink (csrc/kernels/async_fold.cu) ----------------------------------------------------
+def async_fold(x_new_ptr: int, w_new: float, x_old_ptr: int, w_old: float, decay: float, post_scale: float,
+               state: torch.Tensor, state_elem_offsets: Sequence[int], segments, out_ptrs: Sequence[int],
+               mc_out_ptr: int = 0, version_flag_ptrs: Optional[Sequence[int]] = None, new_version: int = 0,
+               wait_flag_ptr: int = 0, wait_value: int = 0, done_counter: Optional[torch.Tensor] = None,
+               n_blocks: int = 64, stream=None):
+    """One asynchronous community update on the calling GPU (FedRec: ``decay=1, post_scale=1/z``; FedAsync:
+    ``decay=1-a, w_new=a``): reads the finisher's slot(s) through (peer) pointers, updates the fp32 ``state`` and
+    stores the new community model into every rank's buffer, then releases ``new_version`` to every rank."""
+    import ctypes as C
+    L = _lib.lib()
+    segs = _lib.segment_array(segments)
+    offs = (C.c_uint64 * len(state_elem_offsets))(*[int(o) for o in state_elem_offsets])
+    flags = _lib.voidp_array(version_flag_ptrs) if version_flag_ptrs else None
+    rc = L.mfl_async_fold(int(x_new_ptr), float(w_new), int(x_old_ptr) or None, float(w_old), float(decay),
+                          float(post_scale), state.data_ptr(), offs, segs, len(segments),
+                          _lib.voidp_array(out_ptrs), int(mc_out_ptr) or None, len(out_ptrs), flags,
+                          int(new_version), int(wait_flag_ptr) or None, int(wait_value),
+                          _lib.ptr(done_counter) or None, int(n_blocks), _lib.stream_ptr(stream))
+    _lib.check(rc, "mfl_async_fold")
+
+
+def flag_signal(flag_ptr: int, value: int, stream=None):
+    _lib.check(_lib.lib().mfl_flag_signal(int(flag_ptr), int(value), _lib.stream_ptr(stream)), "mfl_flag_signal")
+
+
+def flag_wait(flag_ptr: int, value: int, stream=None):
+    _lib.check(_lib.lib().mfl_flag_wait(int(flag_ptr), int(value), _lib.stream_ptr(stream)), "mfl_flag_wait")
+
+
+def snapshot_install(community_ptrs: Sequence[int], version_flag_ptr: int, status: torch.Tensor, dst: torch.Tensor,
+                     nbytes: int, master: Optional[torch.Tensor], segment0, n_blocks: int = 0, stream=None):
+    """Install the newest community model (rotating buffers, picked by the version counter) into ``dst`` and,
+    if given, segment 0 into the fp32 ``master``; ``status`` (2 x uint64 on the device) gets the version read and
+    the torn-read count."""
+    seg = _lib.segment_array([segment0]) if segment0 is not None else None
+    rc = _lib.lib().mfl_snapshot_install(_lib.voidp_array(community_ptrs), len(community_ptrs),
+                                         int(version_flag_ptr), status.data_ptr(), dst.data_ptr(), int(nbytes),
+                                         _lib.ptr(master) or None, seg, int(n_blocks), _lib.stream_ptr(stream))
+    _lib.check(rc, "mfl_snapshot_install", launches=2)
+
+
+def spin_timeouts() -> int:
+    return int(_lib.lib().mfl_spin_timeouts())

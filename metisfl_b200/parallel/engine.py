@@ -79,6 +79,11 @@ class EngineConfig:
     overlap_wgrad: bool = True           # convolution weight gradients on a side stream (ops/conv.py), CUDA only
     use_b200_linear: bool = True         # nn.Linear forward/backward on the tcgen05 GEMM (K10) when bf16 on CUDA
     seed: int = 1234
+    ring: Optional[int] = None           # publish slots per learner (the device lineage): FedRec keeps the previous
+                                         # contribution, so 2; every other rule 1
+    staging_slots: int = 0               # extra slots per rank for models of off-box learners (unpacked by K12)
+    executor_rank: int = 0               # asynchronous rules: the GPU that owns the fp32 rolling state and folds
+    fold_blocks: int = 64                # CTAs of one asynchronous fold (it shares the executor's GPU with training)
 
 
 class FederationEngine:
@@ -107,10 +112,22 @@ class FederationEngine:
         nb = self.layout.total_bytes
         # symmetric buffers: community model + k publish slots per rank
         want_mc = (cfg.nvls is True or (cfg.nvls is None and self.world >= 4)) and self.world > 1 and self.k <= 8
-        self.community = self.fabric.alloc(nb, multicast=want_mc)
-        self.slots = self.fabric.alloc(nb * self.k, multicast=want_mc)
-        self.pads = self.fabric.signal_pads(cfg.fused_blocks)
         sync_rule = cfg.rule in ("FedAvg", "FedStride")
+        self.async_rule = not sync_rule
+        self.ring = int(cfg.ring or (2 if cfg.rule == "FedRec" else 1))
+        self.n_slots = self.k * self.ring + int(cfg.staging_slots)
+        # asynchronous rules rotate the community model through three buffers (version v lives in buffer v % 3) so
+        # that a learner copying version v is not overwritten by the folds producing v + 1 and v + 2
+        self.n_comm = 3 if self.async_rule else 1
+        if self.async_rule:
+            want_mc = (cfg.nvls is True or (cfg.nvls is None and self.world >= 4)) and self.world > 1
+        self.community = self.fabric.alloc(nb * self.n_comm, multicast=want_mc)
+        self.slots = self.fabric.alloc(nb * self.n_slots, multicast=want_mc and sync_rule)
+        self.pads = self.fabric.signal_pads(cfg.fused_blocks)
+        # control words (uint64): [0] community version, [8 + g] "task n of learner g is published"
+        self.ctrl = self.fabric.alloc(8 * (8 + self.world * self.k))
+        self.task_counter = [0] * self.k                       # tasks started per local learner
+        self.version = 0                                       # community updates folded so far
         # NVLS aggregation: the switch adds, so learners publish w_l * theta_l; that needs weights known before the
         # task ends (example counts / participant counts) and every learner in every round
         self.nvls = bool(want_mc and self.community.mc_ptr and self.slots.mc_ptr and sync_rule
@@ -124,8 +141,11 @@ class FederationEngine:
         if not self.direct_install:
             self.community.local[:nb].copy_(self.arena.state[:nb])
         self.trainer = LocalTrainer(self.arena, cfg.optimizer, loss_fn, cfg.use_cuda_graph)
-        self.slot_views = [self.layout.views(self.slots.local[j * nb:(j + 1) * nb]) for j in range(self.k)]
-        self.community_views = self.layout.views(self.community.local)
+        self.slot_views = [self.layout.views(self.slots.local[j * nb:(j + 1) * nb]) for j in range(self.n_slots)]
+        self._comm_views = [self.layout.views(self.community.local[b * nb:(b + 1) * nb]) for b in range(self.n_comm)]
+        if self.n_comm > 1:
+            for b in range(1, self.n_comm):
+                self.community.local[b * nb:(b + 1) * nb].copy_(self.community.local[:nb])
         ex = list(examples_per_learner) if examples_per_learner is not None else \
             [cfg.num_train_examples] * self.num_learners
         assert len(ex) == self.num_learners
@@ -137,42 +157,56 @@ class FederationEngine:
         # async state (FedRec / FedAsync)
         self.learner_version = [0] * self.num_learners       # community iteration a learner started from
         self.contributed = [False] * self.num_learners
-        self.rec_z = 0.0
-        self.rec_w = [0.0] * self.num_learners
-        self._rec_S = None
+        self._remote_tasks = {}
         self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._pinned_loss = None
+        self._init_async_state()
         self.fabric.host_barrier()
+
+    # ------------------------------------------------------------------------------------------
+    @property
+    def community_views(self):
+        """Typed segment views of the CURRENT community model (the buffer of ``self.version``)."""
+        return self._comm_views[self.version % self.n_comm]
+
+    def community_bytes(self) -> torch.Tensor:
+        nb, b = self.layout.total_bytes, self.version % self.n_comm
+        return self.community.local[b * nb:(b + 1) * nb]
+
+    def publish_slot(self, j: int, task_no: Optional[int] = None) -> int:
+        """Slot index (inside this rank's slot buffer) that task ``task_no`` of local learner ``j`` publishes into."""
+        n = self.task_counter[j] if task_no is None else task_no
+        return j * self.ring + (max(n, 1) - 1) % self.ring
 
     # ------------------------------------------------------------------------------------------
     def learner_id(self, local_index: int) -> int:
         return self.rank * self.k + local_index
 
-    def _slot_ptr(self, rank: int, j: int) -> int:
-        return self.slots.ptrs[rank] + j * self.layout.total_bytes
+    def _slot_ptr(self, rank: int, slot: int) -> int:
+        return self.slots.ptrs[rank] + slot * self.layout.total_bytes
 
-    def _publish_buffers(self, j: int, scale: float = 1.0):
+    def _publish_buffers(self, slot: int, scale: float = 1.0):
         """Non-trainable segments (BatchNorm statistics ...) are copied into the slot after the task
         (pre-scaled like the trainable ones when the aggregation runs in the switch)."""
         for i, s in enumerate(self.layout.segments):
             if not s.trainable:
                 if scale != 1.0 and not s.exact:
-                    torch.mul(self.arena.seg[i], scale, out=self.slot_views[j][i])
+                    torch.mul(self.arena.seg[i], scale, out=self.slot_views[slot][i])
                 else:
-                    self.slot_views[j][i].copy_(self.arena.seg[i], non_blocking=True)
+                    self.slot_views[slot][i].copy_(self.arena.seg[i], non_blocking=True)
                 self.gpu_launches += 1
 
-    def _publish_all(self, j: int, scale: float = 1.0):
+    def _publish_all(self, slot: int, scale: float = 1.0):
         nb = self.layout.total_bytes
         if scale == 1.0:
-            self.slots.local[j * nb:(j + 1) * nb].copy_(self.arena.state[:nb], non_blocking=True)
+            self.slots.local[slot * nb:(slot + 1) * nb].copy_(self.arena.state[:nb], non_blocking=True)
             self.gpu_launches += 1
             return
         for i, s in enumerate(self.layout.segments):
             if s.exact:
-                self.slot_views[j][i].copy_(self.arena.seg[i], non_blocking=True)
+                self.slot_views[slot][i].copy_(self.arena.seg[i], non_blocking=True)
             else:
-                torch.mul(self.arena.seg[i], scale, out=self.slot_views[j][i])
+                torch.mul(self.arena.seg[i], scale, out=self.slot_views[slot][i])
             self.gpu_launches += 1
 
     def _static_weight(self, learner: int) -> float:
@@ -182,19 +216,27 @@ class FederationEngine:
         return float(w[learner])
 
     # ------------------------------------------------------------------------------------------
-    def train_learner(self, j: int, batches: Sequence, publish_scale: Optional[float] = None):
+    def train_learner(self, j: int, batches: Sequence, publish_scale: Optional[float] = None,
+                      min_version: Optional[int] = None, cancel=None):
         """Run one learning task for local learner ``j``; returns the device loss of the last step.
         ``publish_scale`` defaults to the learner's aggregation weight in NVLS mode and to 1 otherwise.
 
         ``batches`` is a sequence of ``(x, y)``; pinned host tensors are copied with a prefetching
-        side stream into the CUDA graph's static inputs.
+        side stream into the CUDA graph's static inputs.  Asynchronous rules first install the newest
+        community model (at least ``min_version``) and, when the task is done, release "task n of this learner is
+        published" to the executor.  ``cancel`` (a ``threading.Event``) pre-empts between optimizer steps; a
+        pre-empted task publishes nothing and returns ``None``.
         """
         tr, arena = self.trainer, self.arena
         nb = self.layout.total_bytes
         if publish_scale is None:
             publish_scale = self._static_weight(self.learner_id(j)) if self.nvls else 1.0
         self._slot_scale[j] = float(publish_scale)
-        if not self.direct_install:
+        self.task_counter[j] += 1
+        slot = self.publish_slot(j)
+        if self.async_rule:
+            self._install_community(j, min_version)
+        elif not self.direct_install:
             arena.load_state_bytes(self.community.local[:nb])
             self.gpu_launches += 1 + sum(1 for s, m, v in zip(self.layout.segments, arena.master, arena.seg)
                                          if s.trainable and m is not v)
@@ -205,10 +247,14 @@ class FederationEngine:
         loss = None
         n = len(batches)
         if n == 0:
-            self._publish_all(j, publish_scale)
+            self._publish_all(slot, publish_scale)
+            self._signal_ready(j)
             return None
         on_cuda = self.device.type == "cuda"
         for s, (x, y) in enumerate(batches):
+            if cancel is not None and cancel.is_set():
+                self.task_counter[j] -= 1
+                return None
             last = s == n - 1
             if on_cuda and not x.is_cuda:
                 sx, sy = tr.input_buffers(x, y)
@@ -222,19 +268,30 @@ class FederationEngine:
                     x = x.contiguous(memory_format=torch.channels_last)
             loss = tr.forward_backward(x, y)
             self.gpu_launches += 1
-            self.gpu_launches += tr.apply_optimizer(self.slot_views[j] if last else None, publish_scale)
-        self._publish_buffers(j, publish_scale)
+            self.gpu_launches += tr.apply_optimizer(self.slot_views[slot] if last else None, publish_scale)
+        self._publish_buffers(slot, publish_scale)
+        self._signal_ready(j)
         self.completed_batches[self.learner_id(j)] += n
         # the CUDA graph writes its loss into one static tensor: detach this task's value from it
         return loss.clone() if self.k > 1 else loss
 
     # ------------------------------------------------------------------------------------------
-    def aggregate_sync(self, participants: Optional[Sequence[int]] = None):
-        """FedAvg / FedStride over all (or the given) learners: ONE fused launch per GPU."""
+    def aggregate_sync(self, participants: Optional[Sequence[int]] = None, weights: Optional[Sequence[float]] = None,
+                       sources: Optional[Sequence] = None, accumulate: bool = False):
+        """FedAvg / FedStride over all (or the given) learners: ONE fused launch per GPU.
+
+        ``weights`` overrides the scaling factors computed here (the controller computes them on the service
+        path); ``sources`` = ``[(rank, slot index)]`` names the slots explicitly (staging slots of off-box learners
+        included) instead of deriving them from ``participants``; ``accumulate`` folds the current community
+        model in with weight 1 (one block of a FedStride stream commanded from outside)."""
         cfg = self.cfg
         ids = list(range(self.num_learners)) if participants is None else list(participants)
-        w = scaling_factors(cfg.scaling, [self.examples[i] for i in ids],
-                            [max(1, self.completed_batches[i]) for i in ids], self.num_learners)
+        if sources is not None:
+            assert weights is not None and len(weights) == len(sources)
+            return self._aggregate_sources(list(sources), list(weights), accumulate)
+        w = list(weights) if weights is not None else scaling_factors(
+            cfg.scaling, [self.examples[i] for i in ids],
+            [max(1, self.completed_batches[i]) for i in ids], self.num_learners)
         stride = cfg.stride_length if (cfg.rule == "FedStride" and cfg.stride_length > 0) else len(ids)
         stride = min(stride, 64)
         install = self.arena.master[0] if (self.direct_install and self.arena.master[0] is not self.arena.seg[0]) else None
@@ -242,12 +299,12 @@ class FederationEngine:
             return self._aggregate_host(ids, w)
         scaled = [abs(self._slot_scale[j] - w_full) < 1e-12 for j, w_full in
                   ((j, self._static_weight(self.learner_id(j)) if self.nvls else 1.0) for j in range(self.k))]
-        use_nvls = self.nvls and participants is None and stride >= len(ids) and all(scaled)
+        use_nvls = self.nvls and participants is None and weights is None and stride >= len(ids) and all(scaled)
         if self.nvls and not use_nvls and any(sc != 1.0 for sc in self._slot_scale):
             raise RuntimeError("slots hold pre-scaled models (NVLS publish) but this aggregation needs the "
                                "peer-pointer path: pass publish_scale=1.0 to train_learner or set nvls=False")
         if stride >= len(ids):
-            srcs = [self._slot_ptr(i // self.k, i % self.k) for i in ids]
+            srcs = [self._slot_ptr(i // self.k, (i % self.k) * self.ring) for i in ids]
             mc = [self.slots.mc_ptr + j * self.layout.total_bytes for j in range(self.k)] if use_nvls else None
             agg_ops.fused_aggregate(srcs, w, self.community.ptrs, self.pads.ptrs, self.rank, self.world,
                                     self.layout.segment_table(), install_f32=install, n_blocks=cfg.fused_blocks,
@@ -259,7 +316,7 @@ class FederationEngine:
             first = True
             for b in range(0, len(ids), stride):
                 blk = ids[b:b + stride]
-                srcs = [self._slot_ptr(i // self.k, i % self.k) for i in blk]
+                srcs = [self._slot_ptr(i // self.k, (i % self.k) * self.ring) for i in blk]
                 ws = w[b:b + stride]
                 if not first:
                     srcs = [self.community.ptrs[self.rank]] + srcs
@@ -271,12 +328,35 @@ class FederationEngine:
                 self.gpu_launches += 1
                 first = False
         self.global_iteration += 1
-        if not self.direct_install:
-            pass  # learners install the community model at the start of their next task
         if cfg.quantify:
             self.quantify_community()
 
-    def _aggregate_host(self, ids, w):
+    def _aggregate_sources(self, sources, weights, accumulate: bool):
+        """One fused launch over explicitly named slots (the controller-commanded path)."""
+        install = self.arena.master[0] if (self.direct_install and self.arena.master[0] is not self.arena.seg[0]) else None
+        nb = self.layout.total_bytes
+        if self.device.type != "cuda" or not self.fabric.peer_mapped:
+            return self._aggregate_host(None, weights, sources=sources, accumulate=accumulate)
+        srcs = [self._slot_ptr(int(r), int(sl)) for r, sl in sources]
+        ws = list(weights)
+        if accumulate:
+            srcs = [self.community.ptrs[self.rank]] + srcs
+            ws = [1.0] + ws
+        if any(sc != 1.0 for sc in self._slot_scale):
+            raise RuntimeError("slots hold pre-scaled models (NVLS publish); controller-commanded aggregation needs "
+                               "publish_scale=1.0")
+        for b in range(0, len(srcs), 64):  # MFL_MAX_SRC sources per launch; later launches fold the running result in
+            blk, wb = srcs[b:b + 64], ws[b:b + 64]
+            if b > 0:
+                blk, wb = [self.community.ptrs[self.rank]] + blk[:63], [1.0] + wb[:63]
+            last = b + 64 >= len(srcs)
+            agg_ops.fused_aggregate(blk, wb, self.community.ptrs, self.pads.ptrs, self.rank, self.world,
+                                    self.layout.segment_table(), install_f32=install if last else None,
+                                    n_blocks=self.cfg.fused_blocks)
+            self.gpu_launches += 1
+        self.global_iteration += 1
+
+    def _aggregate_host(self, ids, w, sources=None, accumulate: bool = False):
         """CPU / non-peer-mapped path (gloo): gather slots, run the same math with the CPU ops."""
         import torch.distributed as dist
         nb = self.layout.total_bytes
@@ -285,14 +365,14 @@ class FederationEngine:
             dist.all_gather(gathered, self.slots.local, group=self.fabric.group)
         else:
             gathered = [self.slots.local]
+        pairs = list(sources) if sources is not None else [(i // self.k, (i % self.k) * self.ring) for i in ids]
         for si, s in enumerate(self.layout.segments):
             srcs = []
-            for i in ids:
-                r, j = divmod(i, self.k)
-                buf = gathered[r][j * nb:(j + 1) * nb]
+            for r, sl in pairs:
+                buf = gathered[int(r)][int(sl) * nb:(int(sl) + 1) * nb]
                 srcs.append(buf[s.byte_offset:s.byte_offset + s.nbytes].view(s.dtype))
             out = self.community_views[si]
-            agg_ops.weighted_sum(srcs, w, out=out, exact=s.exact)
+            agg_ops.weighted_sum(srcs, w, out=out, exact=s.exact, accumulate=accumulate)
             if self.device.type == "cuda":
                 self.gpu_launches += 1
         self.global_iteration += 1
@@ -302,51 +382,182 @@ class FederationEngine:
             self.quantify_community()
 
     # ------------------------------------------------------------------------------------------
-    def fold_async(self, learner: int):
-        """Asynchronous update after learner ``learner`` (global index, hosted on THIS rank when
-        world == 1, else any rank) published: FedRec recency swap or FedAsync mixing (K3)."""
+    # -- asynchronous rules (FedRec / FedAsync): one executor GPU folds, everybody else only publishes ---------
+    def _init_async_state(self):
+        """fp32 rolling state on the executor, completion counter, status words, streams and events."""
+        self._state = self._state_off = None
+        self.rec_z, self.rec_w = 0.0, {}
+        if not self.async_rule:
+            return
+        off, offs = 0, []
+        for sg in self.layout.segments:
+            offs.append(off)
+            if not sg.exact:
+                off += (sg.numel + 3) // 4 * 4
+        self._state_off = offs
+        self.is_executor = self.rank == self.cfg.executor_rank or not self.fabric.peer_mapped
+        if self.is_executor:
+            self._state = torch.zeros(max(off, 4), dtype=torch.float32, device=self.device)
+            if self.cfg.rule == "FedAsync":  # the state is the fp32 master of the community model itself
+                for si, sg in enumerate(self.layout.segments):
+                    if not sg.exact:
+                        self._state[offs[si]:offs[si] + sg.numel].copy_(self._comm_views[0][si])
+        cuda = self.device.type == "cuda"
+        self._done = torch.zeros(4, dtype=torch.int32, device=self.device) if cuda else None
+        self._status = torch.zeros(2, dtype=torch.int64, device=self.device) if cuda else None
+        self.fold_stream = torch.cuda.Stream(self.device) if cuda else None
+        self._train_events = [None] * self.k      # task of local learner j is published (executor-local ordering)
+        self._fold_events = {}                    # global learner -> event of its last fold (executor only)
+        self._need_version = [0] * self.k         # version a local learner's next task must at least see
+        if cuda:
+            self.ctrl.local.zero_()
+
+    def _ready_flag(self, learner: int) -> int:
+        return self.ctrl.ptrs[self.cfg.executor_rank if self.fabric.peer_mapped else 0] + 8 * (8 + learner)
+
+    def _install_community(self, j: int, min_version: Optional[int] = None):
+        """Newest community model -> arena (+ fp32 master), after this learner's previous fold."""
+        nb = self.layout.total_bytes
+        need = max(self._need_version[j], int(min_version or 0))
+        if self.device.type != "cuda":
+            self.arena.load_state_bytes(self.community_bytes())
+            return
+        g = self.learner_id(j)
+        if self.is_executor:
+            ev = self._fold_events.get(g)
+            if ev is not None:
+                torch.cuda.current_stream(self.device).wait_event(ev)
+        elif need > 0:
+            agg_ops.flag_wait(self.ctrl.ptrs[self.rank], need)  # bounded in-kernel wait on the local version word
+            self.gpu_launches += 1
+        master = self.arena.master[0] if self.arena.master[0] is not self.arena.seg[0] else None
+        seg0 = self.layout.segment_table()[0] if master is not None else None
+        comm = [self.community.ptrs[self.rank] + b * nb for b in range(self.n_comm)]
+        agg_ops.snapshot_install(comm, self.ctrl.ptrs[self.rank], self._status, self.arena.state, nb, master, seg0)
+        for si, (sg, m, v) in enumerate(zip(self.layout.segments, self.arena.master, self.arena.seg)):
+            if si > 0 and sg.trainable and m is not None and m is not v:
+                m.copy_(v)  # further low-precision trainable segments (none in the shipped models)
+        self.gpu_launches += 2
+
+    def _signal_ready(self, j: int):
+        if not self.async_rule or self.device.type != "cuda":
+            return
+        if self.is_executor:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self._train_events[j] = ev
+        else:
+            agg_ops.flag_signal(self._ready_flag(self.learner_id(j)), self.task_counter[j])
+            self.gpu_launches += 1
+
+    def fold_async(self, learner: int, staleness: Optional[float] = None, weight: Optional[float] = None,
+                   task_no: Optional[int] = None, mix: Optional[float] = None, z: Optional[float] = None,
+                   previous_weight: Optional[float] = None, slot: Optional[int] = None,
+                   previous_slot: Optional[int] = None):
+        """Fold the newest contribution of global learner ``learner`` into the community model (K3).
+
+        Every rank calls this for every fold, in the same order - that is how they agree on version numbers -
+        but only the executor launches anything: its kernel waits for the owner's "published" counter, reads
+        the slot (and for FedRec the previous one) over NVLink, updates the fp32 state and pushes the new
+        community model and version to every GPU.  ``mix`` / ``z`` / the weights default to what the rule and this
+        engine's own bookkeeping give (the service path passes the controller's numbers)."""
         cfg = self.cfg
+        assert self.async_rule, f"fold_async: rule {cfg.rule} is synchronous"
         r, j = divmod(learner, self.k)
         nb = self.layout.total_bytes
-        assert self.world == 1 or self.fabric.peer_mapped, "async folding needs peer-mapped slots"
-        staleness = self.global_iteration - self.learner_version[learner]
+        if task_no is None:
+            task_no = self.task_counter[j] if r == self.rank else self._remote_tasks.setdefault(learner, 0) + 1
+        if r != self.rank:
+            self._remote_tasks[learner] = task_no
+        if slot is None:
+            slot = j * self.ring + (task_no - 1) % self.ring
+        if staleness is None:
+            staleness = self.version - self.learner_version[learner]
+        x_old_slot = None
         if cfg.rule == "FedAsync":
-            a = cfg.fedasync_alpha * staleness_factor(cfg.staleness_fn, staleness, cfg.staleness_a, cfg.staleness_b)
-            for si, s in enumerate(self.layout.segments):
-                x = self.slot_views[j][si] if r == self.rank else None
-                assert x is not None, "remote async folds are issued by the owning rank"
-                c = self.community_views[si]
-                if s.exact:
-                    c.copy_(x)  # integer bookkeeping variables: take the newest
-                else:
-                    agg_ops.weighted_sum([c, x], [1.0 - a, a], out=c)
-                self.gpu_launches += 1
-        elif cfg.rule == "FedRec":
-            w_new = float(self.examples[learner]) if cfg.scaling != "NumParticipants" else 1.0
-            if self._rec_S is None:
-                self._rec_S = [torch.zeros(s.numel, dtype=torch.float32, device=self.device)
-                               if not s.exact else None for s in self.layout.segments]
-                self._rec_prev = [None] * self.num_learners
-            prev = self._rec_prev[learner]
-            w_old = self.rec_w[learner]
-            self.rec_z += w_new - (w_old if prev is not None else 0.0)
-            for si, s in enumerate(self.layout.segments):
-                x = self.slot_views[j][si]
-                c = self.community_views[si]
-                if s.exact:
-                    c.copy_(x)
-                else:
-                    agg_ops.rolling_update(c, self._rec_S[si], x, w_new,
-                                           prev[si] if prev is not None else None, w_old, self.rec_z)
-                self.gpu_launches += 1
-            # keep this contribution: it is what gets swapped out next time (lineage length 2)
-            self._rec_prev[learner] = [v.clone() for v in self.slot_views[j]]
-            self.rec_w[learner] = w_new
+            a = mix if mix is not None else cfg.fedasync_alpha * staleness_factor(
+                cfg.staleness_fn, staleness, cfg.staleness_a, cfg.staleness_b)
+            decay, w_new, w_old, post = 1.0 - a, a, 0.0, 1.0
         else:
-            raise ValueError(f"fold_async: rule {cfg.rule} is synchronous")
+            w_new = weight if weight is not None else (
+                float(self.examples[learner]) if cfg.scaling != "NumParticipants" else 1.0)
+            had = learner in self.rec_w
+            w_old = (previous_weight if previous_weight is not None else self.rec_w[learner]) if had else 0.0
+            if had:
+                x_old_slot = previous_slot if previous_slot is not None else j * self.ring + (task_no - 2) % self.ring
+                assert self.ring >= 2, "FedRec needs the previous contribution: ring >= 2"
+            self.rec_z = z if z is not None else self.rec_z + w_new - w_old
+            self.rec_w[learner] = w_new
+            decay, post = 1.0, 1.0 / self.rec_z
+        new_version = self.version + 1
+        out_buf = new_version % self.n_comm
+        if self.device.type == "cuda" and self.fabric.peer_mapped:
+            if self.is_executor:
+                cur = torch.cuda.current_stream(self.device)
+                wait_flag = 0
+                if r == self.rank:
+                    if self._train_events[j] is not None:
+                        self.fold_stream.wait_event(self._train_events[j])
+                    else:
+                        self.fold_stream.wait_stream(cur)
+                else:
+                    wait_flag = self._ready_flag(learner)
+                outs = [self.community.ptrs[t] + out_buf * nb for t in range(self.world)]
+                mc = self.community.mc_ptr + out_buf * nb if self.community.mc_ptr else 0
+                agg_ops.async_fold(
+                    self._slot_ptr(r, slot), w_new, self._slot_ptr(r, x_old_slot) if x_old_slot is not None else 0,
+                    w_old, decay, post, self._state, self._state_off, self.layout.segment_table(), outs, mc,
+                    [self.ctrl.ptrs[t] for t in range(self.world)], new_version, wait_flag, task_no, self._done,
+                    n_blocks=cfg.fold_blocks, stream=self.fold_stream)
+                ev = torch.cuda.Event()
+                ev.record(self.fold_stream)
+                self._fold_events[learner] = ev
+                self.gpu_launches += 1
+        else:
+            self._fold_host(r, slot, x_old_slot, w_new, w_old, decay, post, out_buf)
+        if r == self.rank:
+            self._need_version[j] = new_version
         self.contributed[learner] = True
-        self.global_iteration += 1
-        self.learner_version[learner] = self.global_iteration
+        self.version = new_version
+        self.global_iteration = new_version
+        self.learner_version[learner] = new_version
+
+    def _fold_host(self, r, slot, x_old_slot, w_new, w_old, decay, post, out_buf):
+        """CPU tier (gloo): the owner broadcasts its slot(s), every rank does the same arithmetic."""
+        import torch.distributed as dist
+        nb = self.layout.total_bytes
+
+        def fetch(sl):
+            buf = self.slots.local[sl * nb:(sl + 1) * nb].clone() if r == self.rank else \
+                torch.empty(nb, dtype=torch.uint8, device=self.device)
+            if self.world > 1:
+                dist.broadcast(buf, src=r, group=self.fabric.group)
+            return self.layout.views(buf)
+        xn = fetch(slot)
+        xo = fetch(x_old_slot) if x_old_slot is not None else None
+        for si, sg in enumerate(self.layout.segments):
+            out = self._comm_views[out_buf][si]
+            if sg.exact:
+                out.copy_(xn[si])
+                continue
+            st = self._state[self._state_off[si]:self._state_off[si] + sg.numel]
+            st.mul_(decay).add_(xn[si].float(), alpha=w_new)
+            if xo is not None:
+                st.add_(xo[si].float(), alpha=-w_old)
+            out.copy_((st * post).to(out.dtype))
+
+    def async_health(self) -> Dict:
+        """Torn community reads seen by this rank's installs and in-kernel waits that timed out (both should be 0)."""
+        if self.device.type != "cuda" or not self.async_rule:
+            return {"torn_reads": 0, "spin_timeouts": 0}
+        torch.cuda.synchronize(self.device)
+        return {"torn_reads": int(self._status[1].item()), "spin_timeouts": agg_ops.spin_timeouts()}
+
+    def sync_folds(self):
+        """Host-side join of the fold stream (executor) - call before reading the community model on the host."""
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self.fabric.host_barrier()
 
     # ------------------------------------------------------------------------------------------
     def quantify_community(self):
@@ -486,7 +697,7 @@ class FederationEngine:
 
         from metisfl_b200.ops import pack
         from metisfl_b200.proto import model_pb2
-        model = pack.arena_to_model_pb(SimpleNamespace(state=self.community.local, layout=self.layout))
+        model = pack.arena_to_model_pb(SimpleNamespace(state=self.community_bytes(), layout=self.layout))
         fm = model_pb2.FederatedModel(num_contributors=self.num_learners, global_iteration=self.global_iteration,
                                       model=model)
         tmp = path + ".tmp"
@@ -502,13 +713,76 @@ class FederationEngine:
         from metisfl_b200.proto import model_pb2
         with open(path, "rb") as f:
             fm = model_pb2.FederatedModel.FromString(f.read())
-        shim = SimpleNamespace(state=self.community.local, layout=self.layout, device=self.device,
-                               sync_master_from_model=lambda: None)
-        pack.unpack_model_into_arena(fm.model, shim)
+        self.install_community_model(fm.model)
         self.global_iteration = fm.global_iteration
+        return fm.global_iteration
+
+    def install_community_model(self, model_pb):
+        """Wire model (with bytes) -> this rank's community buffer(s), unpacked on the device (K12).  Used for the
+        initial ship of the community model and for resuming from a checkpoint."""
+        from types import SimpleNamespace
+
+        from metisfl_b200.ops import pack
+        nb = self.layout.total_bytes
+        shim = SimpleNamespace(state=self.community_bytes(), layout=self.layout, device=self.device,
+                               sync_master_from_model=lambda: None)
+        pack.unpack_model_into_arena(model_pb, shim)
+        cur = self.version % self.n_comm
+        for b in range(self.n_comm):
+            if b != cur:
+                self.community.local[b * nb:(b + 1) * nb].copy_(self.community_bytes())
+        if self.async_rule and self._state is not None and self.cfg.rule == "FedAsync":
+            for si, sg in enumerate(self.layout.segments):
+                if not sg.exact:
+                    self._state[self._state_off[si]:self._state_off[si] + sg.numel].copy_(self.community_views[si])
         if self.direct_install:
             self.arena.sync_master_from_model()
-        return fm.global_iteration
+
+    def stage_model(self, model_pb, staging_index: int) -> int:
+        """Unpack an off-box learner's wire model into staging slot ``staging_index`` of this rank (K12); returns the
+        slot index to name in an aggregation."""
+        from types import SimpleNamespace
+
+        from metisfl_b200.ops import pack
+        assert 0 <= staging_index < self.cfg.staging_slots, "not enough staging slots (EngineConfig.staging_slots)"
+        slot = self.k * self.ring + staging_index
+        nb = self.layout.total_bytes
+        shim = SimpleNamespace(state=self.slots.local[slot * nb:(slot + 1) * nb], layout=self.layout,
+                               device=self.device, sync_master_from_model=lambda: None)
+        pack.unpack_model_into_arena(model_pb, shim)
+        return slot
+
+    # -- control-only model references (TensorSpec.device_slot) ---------------------------------------------------
+    COMMUNITY_SLOT = 0xFFFFFFFF
+
+    def reference_model_pb(self, slot: int, version: int, rank: Optional[int] = None):
+        """``metisfl.Model`` that describes every variable (name, shape, dtype) but carries no bytes: each TensorSpec
+        points at ``slot`` of ``rank``'s slot buffer (``COMMUNITY_SLOT`` = the community buffer).  This is what
+        ``MarkTaskCompleted`` / ``RunTask`` / ``EvaluateModel`` carry between processes that share the fabric."""
+        from metisfl_b200.proto import model_pb2
+        from metisfl_b200.utils import dtypes
+        m = model_pb2.Model()
+        rank = self.rank if rank is None else rank
+        for info in self.layout.variables:
+            seg = self.layout.segments[info.segment]
+            var = m.variables.add(name=info.name, trainable=info.trainable)
+            spec = var.plaintext_tensor.tensor_spec
+            spec.length = info.numel
+            spec.dimensions.extend(info.shape)
+            spec.type.type = dtypes.torch_to_wire(seg.dtype)
+            spec.type.byte_order = model_pb2.DType.NA if seg.dtype.itemsize == 1 else model_pb2.DType.LITTLE_ENDIAN_ORDER
+            spec.device_slot.device_rank = rank
+            spec.device_slot.slot = slot
+            spec.device_slot.offset_bytes = seg.byte_offset + info.elem_offset * seg.dtype.itemsize
+            spec.device_slot.version = version
+        return m
+
+    def community_model_pb(self):
+        """The current community model WITH bytes (one device->host copy), e.g. for off-box learners or snapshots."""
+        from types import SimpleNamespace
+
+        from metisfl_b200.ops import pack
+        return pack.arena_to_model_pb(SimpleNamespace(state=self.community_bytes(), layout=self.layout))
 
     def community_state_dict(self) -> Dict[str, torch.Tensor]:
         views = self.community_views

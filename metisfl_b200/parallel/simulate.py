@@ -1,23 +1,27 @@
 """Event-driven simulation of heterogeneous learners for the asynchronous protocols (config #3).
 
 The reference exercises asynchrony with real learner processes of different speeds
-(``examples/config/fashionmnist/test_localhost_asynchronous_vanillasgd.yaml``); on one box with k
-logical learners per GPU the same behaviour is reproduced deterministically: every learner has a
-task duration, a learner's task reads the community model that is current when the task *starts*,
-and its result is folded when its completion time comes - with the staleness (community updates since
-it started) feeding FedAsync's weight or FedRec's recency swap.  Every rank replays the same global
-event order, so the cross-GPU folds (peer reads of the finishing learner's slot) stay in lockstep.
+(``examples/config/fashionmnist/test_localhost_asynchronous_vanillasgd.yaml``; the asynchronous scheduler
+re-schedules only the caller, ``asynchronous_scheduler.h:12-19``).  On one box with k logical learners per GPU
+the order of completions is made deterministic: every learner has a simulated task duration, completions are
+processed in simulated-time order, and each completion is one community update (FedAsync mixing with a
+staleness weight, or FedRec's recency swap, ``federated_recency.cc:27-94``).
+
+What actually runs is asynchronous.  Each GPU trains its own learners back to back on its stream; nothing on a
+GPU waits for another GPU's training.  The folds are executed by ONE GPU (the executor) on a separate stream, in
+the agreed order: its kernel (K3, ``csrc/kernels/async_fold.cu``) waits on the owner's "published" counter, reads
+the slot once over NVLink and multicasts the new community model and its version to all GPUs.  A learner's next
+task waits only for ITS OWN previous fold (a version counter / CUDA event) and then installs whatever community
+version is newest on its GPU - at least the one the simulated order promises, possibly a newer one, as in a real
+asynchronous federation.  The staleness used for FedAsync's weight is the simulated one (updates between a task's
+start and its fold in the agreed order).
 """
 from __future__ import annotations
 
 import heapq
 from typing import Callable, Dict, List, Sequence
 
-import torch
-
-from metisfl_b200.ops import aggregation as agg_ops
-from metisfl_b200.parallel.engine import FederationEngine, staleness_factor
-from metisfl_b200.parallel.fabric import _CudaMem
+from metisfl_b200.parallel.engine import FederationEngine
 
 
 class AsyncFederation:
@@ -36,27 +40,13 @@ class AsyncFederation:
         self.losses: Dict[int, float] = {}
         self.now = 0.0
         self.events = []
-        nb = engine.layout.total_bytes
-        # typed views of EVERY learner's slot (peer-mapped memory is addressable by torch kernels too)
-        self.views = []
-        for g in range(engine.num_learners):
-            r, j = divmod(g, engine.k)
-            if r == engine.rank or not engine.fabric.peer_mapped:
-                self.views.append(engine.slot_views[j] if r == engine.rank else None)
-            else:
-                raw = torch.as_tensor(_CudaMem(engine.slots.ptrs[r] + j * nb, nb), device=engine.device)
-                self.views.append(engine.layout.views(raw))
-        self._rec_S = None
-        self._rec_prev = [None] * engine.num_learners
-        self._rec_w = [0.0] * engine.num_learners
-        self._rec_z = 0.0
         for g in range(engine.num_learners):  # everybody starts from the initial community model
             self._start(g)
 
     def _start(self, g: int):
         e = self.e
         r, j = divmod(g, e.k)
-        self.started_at_version[g] = e.global_iteration
+        self.started_at_version[g] = e.version
         if r == e.rank:
             loss = e.train_learner(j, self.batches_fn(g, self.task_no[g]))
             if loss is not None:
@@ -65,39 +55,9 @@ class AsyncFederation:
         heapq.heappush(self.events, (self.now + self.durations[g], g))
 
     def _fold(self, g: int):
-        e, cfg = self.e, self.e.cfg
-        staleness = e.global_iteration - self.started_at_version[g]
+        staleness = self.e.version - self.started_at_version[g]
         self.staleness_log.append(staleness)
-        x_views = self.views[g]
-        e.fabric.device_barrier(0)  # the finishing learner's slot is complete and visible
-        if cfg.rule == "FedAsync":
-            a = cfg.fedasync_alpha * staleness_factor(cfg.staleness_fn, staleness, cfg.staleness_a, cfg.staleness_b)
-            for si, sg in enumerate(e.layout.segments):
-                c = e.community_views[si]
-                if sg.exact:
-                    c.copy_(x_views[si])
-                else:
-                    agg_ops.weighted_sum([c, x_views[si]], [1.0 - a, a], out=c)
-                e.gpu_launches += 1
-        else:  # FedRec: swap this learner's previous contribution for the new one
-            if self._rec_S is None:
-                self._rec_S = [torch.zeros(sg.numel, dtype=torch.float32, device=e.device) if not sg.exact else None
-                               for sg in e.layout.segments]
-            w_new = float(e.examples[g]) if cfg.scaling != "NumParticipants" else 1.0
-            prev, w_old = self._rec_prev[g], self._rec_w[g]
-            self._rec_z += w_new - (w_old if prev is not None else 0.0)
-            for si, sg in enumerate(e.layout.segments):
-                c = e.community_views[si]
-                if sg.exact:
-                    c.copy_(x_views[si])
-                else:
-                    agg_ops.rolling_update(c, self._rec_S[si], x_views[si], w_new,
-                                           prev[si] if prev is not None else None, w_old, self._rec_z)
-                e.gpu_launches += 1
-            self._rec_prev[g] = [v.clone() for v in x_views]
-            self._rec_w[g] = w_new
-        e.fabric.device_barrier(1)  # every rank has read the slot before its owner trains into it again
-        e.global_iteration += 1
+        self.e.fold_async(g, staleness=staleness, task_no=self.task_no[g])
 
     def run(self, n_updates: int):
         """Process ``n_updates`` completion events (= community updates)."""
