@@ -105,7 +105,15 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
                                                                thread_name_prefix="ctrl-fanout")
         self._channels = {}
         self._channels_lock = threading.Lock()
-        self.core = _core.Controller(params_pb_to_core(params_pb), self._send_run_tasks, self._send_evaluation_tasks)
+        self._agg_pool = concurrent.futures.ThreadPoolExecutor(max_workers=16, thread_name_prefix="ctrl-aggregate")
+        self._joined = set()
+        # on-box fabrics announced by joining learners: fabric_id -> {world, endpoints[rank], certs[rank], members}
+        self._fabrics = {}
+        self._fabric_of = {}     # learner id -> (fabric_id, rank)
+        self._fabric_lock = threading.Lock()
+        self.controller_rx_model_bytes = 0   # model payload bytes received through MarkTaskCompleted (diagnostics)
+        self.core = _core.Controller(params_pb_to_core(params_pb), self._send_run_tasks, self._send_evaluation_tasks,
+                                     self._aggregate_on_device)
         self._shutdown_event = threading.Event()
         self._server = None
         # checkpoint / resume: the durable format is the serialized FederatedModel itself
@@ -226,6 +234,7 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             self._server.stop(grace).wait()
             self._server = None
         self._rpc_pool.shutdown(wait=False, cancel_futures=True)
+        self._agg_pool.shutdown(wait=False, cancel_futures=True)
         with self._channels_lock:
             for ch, _ in self._channels.values():
                 ch.close()
@@ -247,11 +256,13 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
                 self._channels[learner_id] = (ch, learner_pb2_grpc.LearnerServiceStub(ch))
             return self._channels[learner_id][1]
 
-    def _send_run_tasks(self, items, federated_model_bytes):
+    def _send_run_tasks(self, items, federated_model_bytes, federated_model_ref_bytes=None):
         fm = model_pb2.FederatedModel.FromString(federated_model_bytes)
+        # learners on the fabric get the control-only twin (device-slot references, a few KB) when there is one
+        fm_ref = model_pb2.FederatedModel.FromString(federated_model_ref_bytes) if federated_model_ref_bytes else None
         for (lid, host, port, cert, iteration, updates, pct_valid) in items:
             req = learner_pb2.RunTaskRequest(
-                federated_model=fm,
+                federated_model=fm_ref if (fm_ref is not None and lid in self._fabric_of) else fm,
                 task=metis_pb2.LearningTask(global_iteration=iteration, num_local_updates=updates,
                                             training_dataset_percentage_for_stratified_validation=pct_valid,
                                             metrics=self._evaluation_metrics),
@@ -264,13 +275,85 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         except Exception as e:  # grpc.RpcError and friends: the core decides what to do (deadline)
             self.core.task_failed(lid, f"RunTask: {e}")
 
-    def _send_evaluation_tasks(self, learners, model_bytes, batch_size, eval_index, iteration):
+    def _send_evaluation_tasks(self, learners, model_bytes, batch_size, eval_index, iteration, model_ref_bytes=None):
         model = model_pb2.Model.FromString(model_bytes)
         E = learner_pb2.EvaluateModelRequest
         req = E(model=model, batch_size=batch_size, evaluation_dataset=[E.TRAINING, E.VALIDATION, E.TEST],
                 metrics=self._evaluation_metrics)
+        req_ref = None
+        if model_ref_bytes:
+            req_ref = E(model=model_pb2.Model.FromString(model_ref_bytes), batch_size=batch_size,
+                        evaluation_dataset=[E.TRAINING, E.VALIDATION, E.TEST], metrics=self._evaluation_metrics)
         for (lid, host, port, cert) in learners:
-            self._rpc_pool.submit(self._do_evaluate, lid, host, port, cert, req, eval_index)
+            r = req_ref if (req_ref is not None and lid in self._fabric_of) else req
+            self._rpc_pool.submit(self._do_evaluate, lid, host, port, cert, r, eval_index)
+
+    # -- device aggregation (called by the native core with its lock held: RPCs to learners only) ---------------
+    def _fabric_stub(self, fabric, rank):
+        host, _, port = fabric["endpoints"][rank].rpartition(":")
+        return self._stub_for("fabric:{}:{}".format(fabric["id"], rank), host, int(port), fabric["certs"][rank])
+
+    def _aggregate_on_device(self, req):
+        """``DeviceAggregateRequest`` (dict) -> dict for the core, or None when no fabric is known (host path)."""
+        with self._fabric_lock:
+            fabric = next(iter(self._fabrics.values()), None)
+        if fabric is None:
+            return None
+        try:
+            world = fabric["world"]
+            pb = learner_pb2.AggregateOnDeviceRequest(
+                rule=req["rule"], global_iteration=req["global_iteration"], mix=req["mix"], z=req["z"],
+                first_block=req["first_block"], last_block=req["last_block"], quantify=req["quantify"],
+                executor_rank=fabric["executor"])
+            for s in req["sources"]:
+                src = pb.sources.add(learner_id=s["learner_id"], device_rank=s["device_rank"], slot=s["slot"],
+                                     version=s["version"], weight=s["weight"], has_previous=s["has_previous"],
+                                     previous_slot=s["previous_slot"], previous_weight=s["previous_weight"])
+                if s["staged_model"] is not None:
+                    src.staged_model.CopyFrom(model_pb2.Model.FromString(s["staged_model"]))
+            # bytes of the new community model are only pulled off the device when somebody needs them: learners
+            # outside the fabric, or the snapshot writer
+            off_box = any(rec["id"] not in self._fabric_of for rec in self._learners_cache())
+            want_bytes = bool(req["last_block"] and (off_box or self._snapshot_dir))
+            asynchronous = req["rule"] in ("FedRec", "FedAsync")
+            # one-sided: only the executor GPU folds (its kernel reads the slot and pushes the result to everybody);
+            # without peer-mapped memory (CPU tier) the fold is a collective and every rank takes part
+            ranks = [fabric["executor"]] if (asynchronous and fabric["peer_mapped"]) else list(range(world))
+            if any(not fabric["endpoints"][r] for r in ranks):
+                return {"error": "fabric rank without a service endpoint"}
+
+            def call(rank):
+                r = learner_pb2.AggregateOnDeviceRequest()
+                r.CopyFrom(pb)
+                r.return_model_bytes = want_bytes and rank == fabric["executor"]
+                if rank != fabric["executor"]:   # the staging GPU alone unpacks off-box models
+                    for src in r.sources:
+                        if len(src.staged_model.variables):
+                            keep = src.staged_model.variables[0]
+                            src.ClearField("staged_model")
+                            src.staged_model.variables.add(name=keep.name)  # marker: "this source is staged"
+                return self._fabric_stub(fabric, rank).AggregateOnDevice(r, timeout=120)
+
+            if len(ranks) == 1:
+                resps = [call(ranks[0])]
+            else:
+                resps = list(self._agg_pool.map(call, ranks))
+            bad = [r for r in resps if not r.ack.status]
+            if bad:
+                return {"error": bad[0].ack.message or "AggregateOnDevice refused"}
+            lead = resps[ranks.index(fabric["executor"])]
+            out = {"model_ref": lead.community_ref.SerializeToString(),
+                   "device_ms": max(r.device_ms for r in resps),   # max over the ranks that ran the kernel
+                   "quantifiers": [(q.tensor_non_zeros, q.tensor_zeros, q.tensor_size_bytes) for q in lead.quantifiers],
+                   "model_bytes": lead.community_model.SerializeToString() if want_bytes else None, "error": None}
+            return out
+        except Exception as e:  # grpc.RpcError and friends
+            return {"error": "{}: {}".format(type(e).__name__, e)}
+
+    def _learners_cache(self):
+        # the core's lock is held by our caller; membership is mirrored here at join / leave time
+        with self._fabric_lock:
+            return [{"id": lid} for lid in self._joined]
 
     def _do_evaluate(self, lid, host, port, cert, req, eval_index):
         try:
@@ -323,6 +406,19 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
                 ds.num_validation_examples, ds.num_test_examples, cert)
         except _core.ControllerError as e:
             self._abort(context, e)
+        with self._fabric_lock:
+            self._joined.add(learner_id)
+            if request.HasField("fabric") and request.fabric.world > 0:
+                fb = request.fabric
+                entry = self._fabrics.setdefault(fb.fabric_id, {
+                    "id": fb.fabric_id, "world": fb.world, "executor": 0, "peer_mapped": fb.peer_mapped,
+                    "endpoints": list(fb.endpoints) or [""] * fb.world,
+                    "certs": list(fb.public_certificates) or [b""] * fb.world, "members": {}})
+                if not entry["endpoints"][fb.rank]:
+                    entry["endpoints"][fb.rank] = "{}:{}".format(se.hostname, se.port)
+                    entry["certs"][fb.rank] = cert
+                entry["members"][fb.rank] = learner_id
+                self._fabric_of[learner_id] = (fb.fabric_id, fb.rank)
         return controller_pb2.JoinFederationResponse(ack=_ack(), learner_id=learner_id, auth_token=token)
 
     def LeaveFederation(self, request, context):
@@ -334,10 +430,15 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             ch = self._channels.pop(request.learner_id, None)
         if ch:
             ch[0].close()
+        with self._fabric_lock:
+            self._joined.discard(request.learner_id)
         return controller_pb2.LeaveFederationResponse(ack=_ack())
 
     def MarkTaskCompleted(self, request, context):
         md = request.task.execution_metadata
+        self.controller_rx_model_bytes += sum(len(v.plaintext_tensor.tensor_spec.value) +
+                                              len(v.ciphertext_tensor.tensor_spec.value)
+                                              for v in request.task.model.variables)
         try:
             self.core.learner_completed_task(
                 request.learner_id, request.auth_token, request.task.model.SerializeToString(),
@@ -363,8 +464,16 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
 
     def GetRuntimeMetadataLineage(self, request, context):
         resp = controller_pb2.GetRuntimeMetadataLineageResponse()
+        timed = False
         for d in self.core.get_runtime_metadata_lineage(request.num_backtracks):
             resp.metadata.append(self._metadata_pb(d))
+            timed = timed or bool(d.get("device_timed"))
+        # controller-wide counters that have no field of their own in the reference schema
+        resp.json_metadata = json.dumps({
+            "model_bytes_received": self.controller_rx_model_bytes,
+            "aggregation_failures": self.core.aggregation_failures(),
+            "aggregation_durations_device_timed": timed,
+            "fabric_learners": len(self._fabric_of)})
         return resp
 
     def GetCommunityModelEvaluationLineage(self, request, context):

@@ -96,6 +96,42 @@ class DriverSessionBase(object):
         self._driver_learner_grpc_clients = self._create_driver_learner_grpc_clients()
         self._federation_statistics = dict()
         self._init_homomorphic_encryption()
+        self._fabric_specs = self._plan_device_fabric()
+
+    # -- device fabric ------------------------------------------------------------------------------
+    def _plan_device_fabric(self):
+        """Decide whether the learners form an on-box NVLink fabric (models stay in HBM, messages carry device-slot
+        references) and give every learner its rank.  Returns ``{learner index: "rank=..,world=..,..."}``."""
+        env = self.federation_environment
+        want = env.device_fabric
+        want = str(want).lower() if not isinstance(want, bool) else want
+        if want in (False, "false", "off", "no", "0") or self.neural_engine == "echo" or self.launcher == "ssh":
+            return {}
+        rule = env.global_model_config.aggregation_rule.aggregation_rule_name
+        n = len(env.learners)
+        ok = rule in ("FedAvg", "FedStride", "FedRec", "FedAsync") and self._he_scheme is None
+        ok = ok and (self.launcher == "local" or n == 1)   # one process is one rank: in-process only with one learner
+        forced = want in (True, "true", "on", "yes", "1")
+        if not forced:
+            ok = ok and torch.cuda.is_available() and n <= torch.cuda.device_count() and n <= 16
+        if not ok:
+            if forced:
+                raise RuntimeError("DeviceFabric was requested but rule {} / launcher {} / {} learners cannot run on "
+                                   "one fabric".format(rule, self.launcher, n))
+            return {}
+        import socket
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+        s.close()
+        dtype = env.model_dtype or (self._model_dtype and {torch.bfloat16: "bf16", torch.float32: "fp32",
+                                                           torch.float16: "fp16"}.get(self._model_dtype))
+        specs = {}
+        for i in range(n):
+            t = "rank={},world={},init=tcp://127.0.0.1:{},id=fabric0,rule={},staging=2,executor=0".format(i, n, port, rule)
+            specs[i] = t + (",dtype={}".format(dtype) if dtype else "")
+        MetisLogger.info("Device fabric: %d learner(s), rule %s, models stay on the GPUs", n, rule)
+        return specs
 
     # -- helpers ----------------------------------------------------------------------------------
     def _describe_model(self, model):
@@ -196,7 +232,7 @@ class DriverSessionBase(object):
             model_hyperparameters_pb_ser=p.model_hyperparams.SerializeToString(),
             model_store_config_pb_ser=p.model_store_config.SerializeToString())
 
-    def _init_learner_cmd(self, learner, model_dir, recipes, device):
+    def _init_learner_cmd(self, learner, model_dir, recipes, device, fabric=None):
         return MetisInitServicesCmdFactory.init_learner_target(
             learner_server_entity_pb_ser=self._server_entity_pb(learner).SerializeToString(),
             controller_server_entity_pb_ser=self._server_entity_pb(self.federation_environment.controller).SerializeToString(),
@@ -205,7 +241,8 @@ class DriverSessionBase(object):
             validation_dataset=learner.dataset_configs.validation_dataset_path,
             test_dataset=learner.dataset_configs.test_dataset_path,
             train_dataset_recipe=recipes[0], validation_dataset_recipe=recipes[1] or "",
-            test_dataset_recipe=recipes[2] or "", neural_engine=self.neural_engine, device=device) + (
+            test_dataset_recipe=recipes[2] or "", neural_engine=self.neural_engine, device=device,
+            fabric=fabric) + (
                 " --echo_sleep_secs={}".format(self.echo_sleep_secs) if self.neural_engine == "echo" else "")
 
     # -- launchers --------------------------------------------------------------------------------
@@ -253,7 +290,8 @@ class DriverSessionBase(object):
                               learner.dataset_configs.train_dataset_path, recipes[0],
                               learner.dataset_configs.validation_dataset_path, recipes[1] or "",
                               learner.dataset_configs.test_dataset_path, recipes[2] or "", device=dev,
-                              learner_credentials_fp=os.path.join(self.working_dir, "learner_credentials"))
+                              learner_credentials_fp=os.path.join(self.working_dir, "learner_credentials"),
+                              fabric=self._fabric_specs.get(index))
             svc = LearnerServicer(lrn, servicer_workers=5)
             svc.init_servicer()
             t = threading.Thread(target=svc.wait_servicer, daemon=True)
@@ -271,8 +309,15 @@ class DriverSessionBase(object):
             cmd += self._init_learner_cmd(learner, os.path.join(remote_dir, self._save_model_dir_name), rr, device)
             self._ssh_run(learner, cmd, files=files, remote_dir=remote_dir)
         else:
-            env = {"CUDA_VISIBLE_DEVICES": cuda} if cuda else {}
-            self._popen(f"learner{index}", self._init_learner_cmd(learner, self._save_model_dir, recipes, device), env)
+            fabric = self._fabric_specs.get(index)
+            if fabric and torch.cuda.is_available():
+                # peers map each other's memory: every GPU stays visible and the learner is told which one is its own
+                env = {}
+                device = "cuda:{}".format(learner.cuda_devices[0] if learner.cuda_devices else index)
+            else:
+                env = {"CUDA_VISIBLE_DEVICES": cuda} if cuda else {}
+            self._popen(f"learner{index}", self._init_learner_cmd(learner, self._save_model_dir, recipes, device,
+                                                                 fabric=fabric), env)
 
     def _ssh_run(self, remote, cmd, files, remote_dir=None):
         """Reference-style remote launch over SSH/SFTP (fabric); runs in a background thread."""

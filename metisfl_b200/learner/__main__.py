@@ -35,7 +35,7 @@ def init_learner(a, block=True):
         train_dataset_fp=a.train_dataset, train_dataset_recipe_pkl=a.train_dataset_recipe,
         validation_dataset_fp=a.validation_dataset, validation_dataset_recipe_pkl=a.validation_dataset_recipe,
         test_dataset_fp=a.test_dataset, test_dataset_recipe_pkl=a.test_dataset_recipe, device=a.device,
-        learner_credentials_fp=a.credentials_dir)
+        learner_credentials_fp=a.credentials_dir, fabric=a.fabric or None)
     servicer = LearnerServicer(learner=learner, servicer_workers=5)
     servicer.init_servicer()
     if block:
@@ -58,6 +58,8 @@ def main():
     ap.add_argument("-z", "--test_dataset_recipe", type=str, default="")
     ap.add_argument("--device", type=str, default=None)
     ap.add_argument("--logical_learners", type=int, default=1)
+    ap.add_argument("--fabric", type=str, default="",
+                    help="host a rank of the on-box NVLink fabric: rank=R,world=W,init=tcp://127.0.0.1:PORT,rule=FedAvg")
     ap.add_argument("--credentials_dir", type=str, default="/tmp/metis/learner/")
     ap.add_argument("--echo_sleep_secs", type=float, default=3.0, help="task duration of the echo backend")
     init_learner(ap.parse_args())

@@ -1,0 +1,308 @@
+"""Learner backend for federations whose models never leave the GPUs.
+
+Reference flow: ``RunTask`` ships the whole community model to the learner, the learner trains,
+``MarkTaskCompleted`` ships the whole local model back (``learner.py:197-206``), the controller averages protobuf
+bytes on the CPU (``controller.cc:795-950``) and ``EvaluateModel`` ships the result out again.  Here the learner
+process hosts one rank of the on-box fabric (``parallel/engine.py``): it trains on an arena-backed module, the last
+optimizer step publishes into a peer-visible slot, and every message that used to carry the model carries a
+*reference* to it instead (``TensorSpec.device_slot``) - a few KB of metadata.  The controller keeps all of its
+policy (scheduling, selection, scaling factors, lineage, runtime metadata) and, at the barrier, tells the GPU
+processes which slots to aggregate with which weights (``LearnerService.AggregateOnDevice``); the fused kernels
+(K1 / K3) do the rest over NVLink.  Only the very first community model arrives as bytes (the driver ships it to
+the controller, ``driver_session.py:334-342``) and is unpacked on the device (K12).
+"""
+from __future__ import annotations
+
+import math
+import threading
+import time
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from metisfl_b200.models.model_proto_factory import ModelProtoFactory
+from metisfl_b200.models.torch_model_ops import _Batches, load_torch_model, optim_hyper_from_pb
+from metisfl_b200.models.trainer import cross_entropy_loss
+from metisfl_b200.parallel.arena import ModelArena
+from metisfl_b200.parallel.engine import EngineConfig, FederationEngine
+from metisfl_b200.proto import learner_pb2, model_pb2
+from metisfl_b200.utils.metis_logger import MetisLogger
+from metisfl_b200.utils.proto_messages_factory import MetisProtoMessages
+
+
+@dataclass
+class FabricSpec:
+    """Where this learner sits in the on-box fabric and which aggregation it has to be able to run."""
+    rank: int = 0
+    world: int = 1
+    init_method: str = ""            # torch.distributed rendezvous, e.g. tcp://127.0.0.1:29511 (unused when world == 1)
+    fabric_id: str = "fabric0"
+    rule: str = "FedAvg"             # FedAvg | FedStride | FedRec | FedAsync
+    staging_slots: int = 2           # per rank, for models of learners outside the fabric
+    executor_rank: int = 0
+    model_dtype: Optional[str] = None
+
+    @staticmethod
+    def parse(text: str) -> "FabricSpec":
+        """``rank=0,world=8,init=tcp://127.0.0.1:29511,rule=FedAvg,...`` (the learner CLI's ``--fabric``)."""
+        kv = dict(p.split("=", 1) for p in text.split(",") if "=" in p)
+        return FabricSpec(rank=int(kv.get("rank", 0)), world=int(kv.get("world", 1)), init_method=kv.get("init", ""),
+                          fabric_id=kv.get("id", "fabric0"), rule=kv.get("rule", "FedAvg"),
+                          staging_slots=int(kv.get("staging", 2)), executor_rank=int(kv.get("executor", 0)),
+                          model_dtype=kv.get("dtype"))
+
+    def to_text(self) -> str:
+        t = "rank={},world={},init={},id={},rule={},staging={},executor={}".format(
+            self.rank, self.world, self.init_method, self.fabric_id, self.rule, self.staging_slots, self.executor_rank)
+        return t + (",dtype=" + self.model_dtype if self.model_dtype else "")
+
+
+def _has_bytes(model_pb) -> bool:
+    return len(model_pb.variables) > 0 and len(model_pb.variables[0].plaintext_tensor.tensor_spec.value) > 0
+
+
+def _ref_of(model_pb):
+    if not len(model_pb.variables):
+        return None
+    spec = model_pb.variables[0].plaintext_tensor.tensor_spec
+    return spec.device_slot if spec.HasField("device_slot") else None
+
+
+class DeviceBackend:
+    """One per learner process: a ``FederationEngine`` rank plus a private evaluation copy of the module."""
+
+    def __init__(self, model_dir: str, device, fabric: FabricSpec, loss_fn=None, endpoint=None, certificate=b""):
+        self.fabric = fabric
+        self._endpoint, self._certificate = endpoint, certificate or b""
+        self.device = torch.device(device if device is not None else ("cuda" if torch.cuda.is_available() else "cpu"))
+        if fabric.world > 1 and not dist.is_initialized():
+            if self.device.type == "cuda":
+                torch.cuda.set_device(self.device)
+                dist.init_process_group("nccl", init_method=fabric.init_method, rank=fabric.rank,
+                                        world_size=fabric.world, device_id=self.device)
+            else:
+                dist.init_process_group("gloo", init_method=fabric.init_method, rank=fabric.rank,
+                                        world_size=fabric.world)
+        dtype = {"bf16": torch.bfloat16, "fp32": torch.float32, "fp16": torch.float16, None: None}[fabric.model_dtype]
+        if dtype is None:
+            dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
+        module = load_torch_model(model_dir)
+        if loss_fn is None:
+            from metisfl_b200.models.torch_model_ops import _overrides
+            loss_fn = module.loss_fn if _overrides(module, "loss_fn") else cross_entropy_loss
+        self.loss_fn = loss_fn
+        # the controller owns the scaling factors, so nothing is pre-scaled at publish time (no in-switch reduction);
+        # the working copy is separate from the community buffer so that evaluation of version v and training from
+        # version v can overlap
+        cfg = EngineConfig(learners_per_gpu=1, model_dtype=dtype, rule=fabric.rule, nvls=False,
+                           staging_slots=fabric.staging_slots, executor_rank=fabric.executor_rank,
+                           direct_install=False)
+        self.engine = FederationEngine(lambda: module, cfg, loss_fn=loss_fn, device=self.device)
+        eval_module = load_torch_model(model_dir)
+        if self.device.type == "cuda":
+            eval_module = eval_module.to(memory_format=torch.channels_last)
+            if dtype == torch.bfloat16:
+                from metisfl_b200.ops import gemm as _gemm
+                _gemm.use_b200_linear(eval_module)
+        self.eval_arena = ModelArena(eval_module, self.device, dtype)
+        assert self.eval_arena.layout.total_bytes == self.engine.layout.total_bytes
+        # every rank learns every rank's service endpoint, so the controller can command the whole fabric as soon as
+        # ONE of its learners has joined (the fused kernel needs all ranks to launch)
+        self._peers = self.engine.fabric.all_gather_object((self._endpoint or "", bytes(self._certificate)))
+        self._comm_lock = threading.Lock()   # community buffer: aggregation writes, evaluation / install read
+        self._installed_bytes_iteration = None
+        self._known_version = 0
+
+    # -- membership -----------------------------------------------------------------------------------------------
+    def membership_pb(self):
+        from metisfl_b200.proto import controller_pb2
+        return controller_pb2.FabricMembership(fabric_id=self.fabric.fabric_id, rank=self.fabric.rank,
+                                               world=self.fabric.world, staging_slots=self.fabric.staging_slots,
+                                               peer_mapped=bool(self.engine.fabric.peer_mapped),
+                                               endpoints=[p[0] for p in self._peers],
+                                               public_certificates=[p[1] for p in self._peers])
+
+    # -- community model --------------------------------------------------------------------------------------------
+    def _adopt(self, model_pb, iteration=None):
+        """Make the engine's community buffer hold the model the message talks about."""
+        eng = self.engine
+        if _has_bytes(model_pb):
+            key = (iteration, len(model_pb.variables))
+            with self._comm_lock:
+                live = eng.async_rule and eng.version > 0  # folds are already landing in the buffers: keep them
+                if (self._installed_bytes_iteration != key or iteration is None) and not live:
+                    eng.install_community_model(model_pb)
+                    self._installed_bytes_iteration = key
+            return None
+        ref = _ref_of(model_pb)
+        if ref is not None and eng.async_rule:
+            self._known_version = max(self._known_version, int(ref.version))
+            if not eng.is_executor or eng.version < self._known_version:
+                eng.version = max(eng.version, self._known_version)
+        return ref
+
+    # -- training ---------------------------------------------------------------------------------------------------
+    def train(self, train_dataset, learning_task_pb, hyperparameters_pb, model_pb, cancel_event=None):
+        eng = self.engine
+        ref = self._adopt(model_pb, learning_task_pb.global_iteration)
+        eng.trainer.set_hyper(optim_hyper_from_pb(hyperparameters_pb.optimizer))
+        batch_size = hyperparameters_pb.batch_size or 32
+        total_steps = max(1, int(learning_task_pb.num_local_updates))
+        src = _Batches(train_dataset, batch_size, shuffle=True, pin=self.device.type == "cuda",
+                       seed=learning_task_pb.global_iteration)
+        spe = max(1, src.steps_per_epoch)
+        batches = []
+        while len(batches) < total_steps:
+            for x, y in src:
+                if x.shape[0] != src.batch_size and len(batches) > 0:
+                    continue  # ragged tail batches would re-capture the CUDA graph: skipped, like drop_last
+                batches.append((x, y))
+                if len(batches) >= total_steps:
+                    break
+        cuda = self.device.type == "cuda"
+        if cuda:
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+        wall0 = time.perf_counter()
+        loss = eng.train_learner(0, batches, publish_scale=1.0,
+                                 min_version=int(ref.version) if (ref is not None and eng.async_rule) else None,
+                                 cancel=cancel_event)
+        if loss is None and (cancel_event is not None and cancel_event.is_set()):
+            return None
+        if cuda:
+            t1.record()
+            t1.synchronize()
+            total_ms = t0.elapsed_time(t1)   # device time of the whole task (CUDA events on the training stream)
+        else:
+            total_ms = (time.perf_counter() - wall0) * 1e3
+        steps = len(batches)
+        ms_per_batch = total_ms / max(1, steps)
+        stats = {"loss": [float(loss)]} if loss is not None else {}
+        slot = eng.publish_slot(0)
+        local_ref = eng.reference_model_pb(slot, version=eng.task_counter[0])
+        meta = ModelProtoFactory.CompletedLearningTaskProtoMessage(
+            weights_values=[], weights_trainable=[], weights_names=[], train_stats=stats,
+            completed_epochs=steps / spe, global_iteration=learning_task_pb.global_iteration,
+            completes_batches=steps, batch_size=batch_size, processing_ms_per_epoch=ms_per_batch * spe,
+            processing_ms_per_batch=ms_per_batch).construct_task_execution_metadata_pb()
+        return MetisProtoMessages.construct_completed_learning_task_pb(
+            model_pb=local_ref, task_execution_metadata_pb=meta,
+            aux_metadata='{{"device_timed": {}, "fabric_rank": {}}}'.format("true" if cuda else "false", eng.rank))
+
+    # -- evaluation -------------------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def evaluate(self, model_pb, datasets, batch_size, metrics):
+        """``datasets`` = {code: dataset or None}; returns {code: {metric: value}}."""
+        eng = self.engine
+        nb = eng.layout.total_bytes
+        self._adopt(model_pb)
+        with self._comm_lock:
+            if self.device.type == "cuda" and eng.async_rule and not eng.is_executor:
+                # a fold may be landing: take a consistent snapshot through the version counter
+                from metisfl_b200.ops import aggregation as agg_ops
+                comm = [eng.community.ptrs[eng.rank] + b * nb for b in range(eng.n_comm)]
+                agg_ops.snapshot_install(comm, eng.ctrl.ptrs[eng.rank], eng._status, self.eval_arena.state, nb,
+                                         None, None)
+            else:
+                self.eval_arena.state[:nb].copy_(eng.community_bytes()[:nb], non_blocking=True)
+            if self.device.type == "cuda":
+                torch.cuda.current_stream(self.device).synchronize()
+        module = self.eval_arena.module
+        module.eval()
+        out = {}
+        for code, ds in datasets.items():
+            if ds is None or not ds.get_size():
+                out[code] = {}
+                continue
+            loss_sum = torch.zeros((), device=self.device)
+            correct = torch.zeros((), device=self.device)
+            seen, classification = 0, False
+            for x, y in _Batches(ds, batch_size or 100, shuffle=False, pin=self.device.type == "cuda"):
+                x = x.to(self.device, non_blocking=True)
+                y = y.to(self.device, non_blocking=True)
+                if x.is_floating_point():
+                    x = x.to(self.eval_arena.model_dtype)
+                    if x.dim() == 4 and self.device.type == "cuda":
+                        x = x.contiguous(memory_format=torch.channels_last)
+                logits = module(x)
+                loss_sum += self.loss_fn(logits, y).float() * x.shape[0]
+                if logits.dim() == 2 and not y.is_floating_point():
+                    classification = True
+                    correct += (logits.argmax(dim=-1) == y).sum()
+                seen += x.shape[0]
+            res = {"loss": float(loss_sum) / max(1, seen)}
+            if classification:
+                res["accuracy"] = float(correct) / max(1, seen)
+            if metrics:
+                res = {k: v for k, v in res.items() if k in metrics or k == "loss"} or res
+            out[code] = res
+        return out
+
+    # -- aggregation (commanded by the controller) ------------------------------------------------------------------
+    def aggregate(self, req) -> "learner_pb2.AggregateOnDeviceResponse":
+        eng = self.engine
+        cuda = self.device.type == "cuda"
+        resp = learner_pb2.AggregateOnDeviceResponse()
+        with self._comm_lock:
+            # device time of the launch(es), on the stream they run on
+            tstream = None
+            if cuda:
+                tstream = eng.fold_stream if eng.async_rule else torch.cuda.current_stream(self.device)
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record(tstream)
+            wall0 = time.perf_counter()
+            if not eng.async_rule:
+                sources, weights, staged = [], [], 0
+                for src in req.sources:
+                    if len(src.staged_model.variables):
+                        if eng.rank == req.executor_rank:
+                            slot = eng.stage_model(src.staged_model, staged)
+                        else:
+                            slot = eng.k * eng.ring + staged
+                        sources.append((req.executor_rank, slot))
+                        staged += 1
+                    else:
+                        sources.append((src.device_rank, src.slot))
+                    weights.append(src.weight)
+                eng.aggregate_sync(sources=sources, weights=weights, accumulate=not req.first_block)
+                version = eng.global_iteration
+            else:
+                assert len(req.sources) == 1, "asynchronous rules fold one learner at a time"
+                src = req.sources[0]
+                learner = int(src.device_rank) * eng.k
+                eng.version = max(eng.version, self._known_version)
+                if req.rule == "FedAsync":
+                    eng.fold_async(learner, mix=req.mix, task_no=int(src.version), slot=int(src.slot))
+                else:
+                    eng.fold_async(learner, weight=src.weight, z=req.z, task_no=int(src.version), slot=int(src.slot),
+                                   previous_weight=src.previous_weight if src.has_previous else None,
+                                   previous_slot=int(src.previous_slot) if src.has_previous else None)
+                version = eng.version
+                self._known_version = version
+            if cuda:
+                t1.record(tstream)
+                t1.synchronize()
+                resp.device_ms = t0.elapsed_time(t1)
+            else:
+                resp.device_ms = (time.perf_counter() - wall0) * 1e3
+            if req.quantify and req.last_block:
+                eng.quantify_community()
+                rep = eng.quantifier_report()
+                for info in eng.layout.variables:
+                    nz, z, nbytes = rep[info.name]
+                    resp.quantifiers.add(tensor_non_zeros=int(nz), tensor_zeros=int(z), tensor_size_bytes=int(nbytes))
+            resp.version = version
+            resp.community_ref.CopyFrom(eng.reference_model_pb(eng.COMMUNITY_SLOT, version))
+            if req.return_model_bytes:
+                resp.community_model.CopyFrom(eng.community_model_pb())
+        from metisfl_b200.learner.learner_servicer import _ack
+        resp.ack.CopyFrom(_ack(True))
+        return resp
+
+    def close(self):
+        try:
+            self.engine.close()
+        except Exception as e:  # peers may already be gone at shutdown
+            MetisLogger.warning("fabric close: %r", e)

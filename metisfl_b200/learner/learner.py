@@ -38,7 +38,7 @@ class Learner(object):
                  nn_engine, model_dir, train_dataset_fp, train_dataset_recipe_pkl, validation_dataset_fp="",
                  validation_dataset_recipe_pkl="", test_dataset_fp="", test_dataset_recipe_pkl="",
                  recreate_queue_task_worker=False, learner_credentials_fp="/tmp/metis/learner/", device=None,
-                 model_ops=None):
+                 model_ops=None, fabric=None):
         self.learner_server_entity = learner_server_entity
         self._controller_server_entity = controller_server_entity
         self._he_scheme_config_pb = he_scheme_config_pb
@@ -57,6 +57,23 @@ class Learner(object):
         self._cancel_event = threading.Event()
         self._model_lock = threading.Lock()  # one task at a time touches the model backend
         self._model_ops = model_ops
+        # a FabricSpec (or its text form) makes this learner a rank of the on-box NVLink fabric: models stay in HBM
+        # and the messages carry device-slot references (learner/device_backend.py)
+        self._fabric = fabric
+        self._device_backend = None
+        if fabric is not None:
+            from metisfl_b200.learner.device_backend import DeviceBackend, FabricSpec
+            spec = FabricSpec.parse(fabric) if isinstance(fabric, str) else fabric
+            # collective: every rank of the fabric constructs its backend before any of them serves RPCs
+            cert = b""
+            ssl = learner_server_entity.ssl_config
+            if ssl.enable_ssl:
+                from metisfl_b200.utils.ssl_configurator import SSLConfigurator
+                pub = SSLConfigurator.gen_public_ssl_config_pb_as_stream(ssl)
+                cert = pub.ssl_config_stream.public_certificate_stream
+            self._device_backend = DeviceBackend(
+                model_dir, device, spec, certificate=cert,
+                endpoint="{}:{}".format(learner_server_entity.hostname, learner_server_entity.port))
         self._datasets = None
         self._he_scheme = None
         self._learner_controller_client = GRPCControllerClient(self._controller_server_entity, max_workers=1)
@@ -139,7 +156,8 @@ class Learner(object):
         is_reg = issubclass(cls_tr, ModelDatasetRegression)
         self._learner_id, self._auth_token, status = self._learner_controller_client.join_federation(
             self.learner_server_entity, self._learner_id_fp, self._auth_token_fp, n_tr, s_tr, n_va, s_va, n_te, s_te,
-            is_cls, is_reg, request_retries=10, request_timeout=30, block=True)
+            is_cls, is_reg, request_retries=10, request_timeout=30, block=True,
+            fabric_pb=self._device_backend.membership_pb() if self._device_backend is not None else None)
         return status
 
     def leave_federation(self):
@@ -152,6 +170,14 @@ class Learner(object):
                        verbose=False):
         train, valid, test = self._load_model_datasets()
         E = learner_pb2.EvaluateModelRequest
+        if self._device_backend is not None:
+            want = {code: (ds if code in evaluation_datasets_pb else None)
+                    for code, ds in ((E.TRAINING, train), (E.VALIDATION, valid), (E.TEST, test))}
+            res = self._device_backend.evaluate(model_pb, want, batch_size, list(metrics_pb.metric))
+            mk = lambda d: ModelProtoFactory.ModelEvaluationProtoMessage(d).construct_model_evaluation_pb()
+            return MetisProtoMessages.construct_model_evaluations_pb(
+                training_evaluation_pb=mk(res[E.TRAINING]), validation_evaluation_pb=mk(res[E.VALIDATION]),
+                test_evaluation_pb=mk(res[E.TEST]))
         with self._model_lock:
             with LearnerEvaluator(self._model_ops_factory(), model_pb) as ev:
                 res = {}
@@ -178,6 +204,9 @@ class Learner(object):
     def model_train(self, learning_task_pb: metis_pb2.LearningTask, hyperparameters_pb: metis_pb2.Hyperparameters,
                     model_pb: model_pb2.Model, verbose=False, cancel_event=None):
         train, valid, test = self._load_model_datasets()
+        if self._device_backend is not None:
+            with self._model_lock:
+                return self._device_backend.train(train, learning_task_pb, hyperparameters_pb, model_pb, cancel_event)
         with self._model_lock:
             with LearnerTrainer(self._model_ops_factory(), model_pb) as tr:
                 return tr.train_model(train, learning_task_pb, hyperparameters_pb, valid, test, verbose,
@@ -202,6 +231,12 @@ class Learner(object):
         fut = self._eval_pool.submit(self.model_evaluate, model_pb, batch_size, evaluation_dataset_pb, metrics_pb,
                                      verbose)
         return fut.result() if block else fut
+
+    def aggregate_on_device(self, request_pb):
+        """Controller-commanded aggregation over device slots (``LearnerService.AggregateOnDevice``)."""
+        if self._device_backend is None:
+            raise RuntimeError("this learner does not host a fabric rank")
+        return self._device_backend.aggregate(request_pb)
 
     def run_inference_task(self):
         raise NotImplementedError("Not yet implemented.")
@@ -242,3 +277,5 @@ class Learner(object):
     def close(self):
         """Release the controller channel (after ``leave_federation``)."""
         self._learner_controller_client.shutdown()
+        if self._device_backend is not None:
+            self._device_backend.close()

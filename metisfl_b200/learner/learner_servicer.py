@@ -74,6 +74,20 @@ class LearnerServicer(learner_pb2_grpc.LearnerServiceServicer):
             cancel_running_tasks=True, block=False, verbose=False)
         return LearnerServiceProtoMessages.construct_run_task_response_pb(_ack(bool(accepted)))
 
+    def AggregateOnDevice(self, request, context):
+        """Extension RPC (no reference counterpart): run the aggregation kernels over the device slots the controller
+        names.  Answers with the device-timed duration, the quantifier counts and a reference to the new community
+        model."""
+        import grpc
+        try:
+            return self.learner.aggregate_on_device(request)
+        except Exception as e:
+            MetisLogger.error("AggregateOnDevice failed: %r", e)
+            context.set_code(grpc.StatusCode.FAILED_PRECONDITION)
+            context.set_details(repr(e))
+            from metisfl_b200.proto import learner_pb2
+            return learner_pb2.AggregateOnDeviceResponse(ack=_ack(False, repr(e)))
+
     def ShutDown(self, request, context):
         self.__not_serving_event.set()
         # answer first, then tear down (the caller must not wait for a possibly long drain)

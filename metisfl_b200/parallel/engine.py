@@ -84,6 +84,9 @@ class EngineConfig:
     staging_slots: int = 0               # extra slots per rank for models of off-box learners (unpacked by K12)
     executor_rank: int = 0               # asynchronous rules: the GPU that owns the fp32 rolling state and folds
     fold_blocks: int = 64                # CTAs of one asynchronous fold (it shares the executor's GPU with training)
+    direct_install: Optional[bool] = None  # train in place in the community buffer (one learner per GPU, synchronous
+                                           # rules); False keeps a separate working copy (service path: evaluation of
+                                           # version v overlaps training from version v)
 
 
 class FederationEngine:
@@ -135,7 +138,7 @@ class FederationEngine:
         if cfg.nvls and not self.nvls and self.world > 1:
             raise RuntimeError("EngineConfig.nvls=True but multicast memory / a static scaling rule is unavailable")
         self._slot_scale = [1.0] * self.k
-        self.direct_install = sync_rule and self.k == 1
+        self.direct_install = sync_rule and self.k == 1 and cfg.direct_install is not False
         storage = self.community.local if self.direct_install else None
         self.arena = ModelArena(module, self.device, cfg.model_dtype, storage=storage)
         if not self.direct_install:

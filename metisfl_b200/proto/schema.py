@@ -396,7 +396,10 @@ _controller_msgs = [
     _Msg("GetParticipatingLearnersResponse", rep("learner", 1, "LearnerDescriptor")),
     _Msg("FabricMembership",  # extension: this learner is rank `rank` of a `world`-GPU peer-memory fabric
          f("fabric_id", 1, "string"), f("rank", 2, "uint32"), f("world", 3, "uint32"),
-         f("staging_slots", 4, "uint32")),
+         f("staging_slots", 4, "uint32"),
+         rep("endpoints", 5, "string"),             # "host:port" of every rank's LearnerService, by rank
+         rep("public_certificates", 6, "bytes"),    # PEM streams by rank (empty without TLS)
+         f("peer_mapped", 7, "bool")),              # ranks read each other's HBM; false = CPU tier (collectives)
     _Msg("JoinFederationRequest", f("server_entity", 1, "ServerEntity"),
          f("local_dataset_spec", 2, "DatasetSpec"), f("fabric", 15, "FabricMembership")),
     _Msg("JoinFederationResponse", f("ack", 1, "Ack"), f("learner_id", 2, "string"),

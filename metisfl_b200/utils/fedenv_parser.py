@@ -231,6 +231,11 @@ class FederationEnvironment(object):
         self.controller = Controller(env.get("Controller"))
         self.learners = Learners(env.get("Learners"))
         self.launcher = str(env.get("Launcher", "local")).lower()
+        # DeviceFabric (extension): learners of this box form one NVLink peer-memory fabric and exchange device-slot
+        # references instead of model bytes.  "auto" = when CUDA is there, the rule has a device kernel and every
+        # learner is local (the driver decides); true / false force it.
+        self.device_fabric = env.get("DeviceFabric", "auto")
+        self.model_dtype = env.get("ModelDType")  # bf16 | fp32 | fp16; default: bf16 on CUDA, fp32 on CPU
         self.homomorphic_encryption = None
         if "HomomorphicEncryption" in env and env.get("HomomorphicEncryption"):
             self.homomorphic_encryption = HomomorphicEncryption(env.get("HomomorphicEncryption"))

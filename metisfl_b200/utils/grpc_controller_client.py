@@ -34,7 +34,7 @@ class GRPCControllerClient(GRPCServerClient):
     def join_federation(self, learner_server_entity, learner_id_fp, auth_token_fp, train_dataset_size,
                         train_dataset_specs, validation_dataset_size, validation_dataset_specs, test_dataset_size,
                         test_dataset_specs, is_classification, is_regression, request_retries=1,
-                        request_timeout=None, block=True):
+                        request_timeout=None, block=True, fabric_pb=None):
         # the controller only ever sees the learner's PUBLIC certificate
         public_entity = proto_factory.MetisProtoMessages.construct_server_entity_pb(
             hostname=learner_server_entity.hostname, port=learner_server_entity.port,
@@ -46,6 +46,8 @@ class GRPCControllerClient(GRPCServerClient):
             is_classification=is_classification, is_regression=is_regression)
         req = proto_factory.ControllerServiceProtoMessages.construct_join_federation_request_pb(
             server_entity_pb=public_entity, local_dataset_spec_pb=dataset_spec_pb)
+        if fabric_pb is not None:  # this learner hosts a rank of the on-box fabric
+            req.fabric.CopyFrom(fabric_pb)
 
         def _request(_timeout=None):
             try:

@@ -29,7 +29,7 @@ class MetisInitServicesCmdFactory(object):
     def init_learner_target(cls, learner_server_entity_pb_ser, controller_server_entity_pb_ser, he_scheme_pb_ser,
                             model_dir, train_dataset, train_dataset_recipe, validation_dataset="", test_dataset="",
                             validation_dataset_recipe="", test_dataset_recipe="", neural_engine="pytorch",
-                            device=None, logical_learners=None):
+                            device=None, logical_learners=None, fabric=None):
         return cls._cmd("learner", [
             ("learner_server_entity_protobuff_serialized_hexadecimal", learner_server_entity_pb_ser),
             ("controller_server_entity_protobuff_serialized_hexadecimal", controller_server_entity_pb_ser),
@@ -39,4 +39,4 @@ class MetisInitServicesCmdFactory(object):
              ("train_dataset_recipe", train_dataset_recipe),
              ("validation_dataset_recipe", validation_dataset_recipe),
              ("test_dataset_recipe", test_dataset_recipe), ("device", device),
-             ("logical_learners", logical_learners)])
+             ("logical_learners", logical_learners), ("fabric", fabric)])
