@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--seq-len", type=int, default=1024)
     ap.add_argument("--learners-per-gpu", type=int, default=1)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-stock", action="store_true", help="skip the stock PyTorch/cuDNN + NCCL arm (vs_baseline)")
+    ap.add_argument("--no-service", action="store_true", help="skip the DriverSession/gRPC sub-record (1 GPU only)")
     return ap.parse_args()
 
 
@@ -198,14 +200,103 @@ def main():
     launches = _lib.LAUNCHES - launches0
     clocks = sampler.stop() if sampler else None
 
-    t = torch.tensor([dev_ms, e2e_ms], device=device, dtype=torch.float64)
+    # ---- the product by itself: K1 only vs NCCL `buf *= w; all_reduce`, same buffers, same clocks ----------
+    nb = eng.layout.total_bytes
+    def time_loop(fn, iters=30):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fn(); fn()
+        barrier()
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        barrier()
+        return a.elapsed_time(b) / iters
+    k1_ms = time_loop(eng.aggregate_sync)
+    flat = torch.empty(eng.layout.segments[0].numel, dtype=torch.bfloat16, device=device).normal_()
+    def nccl_fedavg():
+        flat.mul_(1.0 / max(1, world))
+        if world > 1:
+            dist.all_reduce(flat)
+    nccl_ms = time_loop(nccl_fedavg)
+
+    # ---- check what the timed rounds produced: every rank holds the same community model, and it is the weighted
+    # average of the published slots (fp32 oracle through NCCL) within bf16 rounding --------------------------------
+    eng.aggregate_sync()
+    torch.cuda.synchronize()
+    comm = eng.community_views[0].float()
+    mine = eng.slot_views[0][0].float() if k == 1 else None
+    check = {"identical_across_ranks": True, "max_abs_err_vs_fp32_oracle": None}
+    digest = torch.stack([eng.community_bytes()[:nb].view(torch.int32).to(torch.int64).sum(),
+                          eng.community_bytes()[:nb].view(torch.int32)[::7].to(torch.int64).sum()])
+    if world > 1:
+        all_d = [torch.empty_like(digest) for _ in range(world)]
+        dist.all_gather(all_d, digest)
+        check["identical_across_ranks"] = all(torch.equal(all_d[0], d) for d in all_d)
+    if mine is not None:
+        scale = eng._slot_scale[0]
+        w_me = eng._static_weight(eng.learner_id(0))
+        oracle = mine * (w_me / scale)      # NVLS mode publishes w_l * theta_l already
+        if world > 1:
+            dist.all_reduce(oracle)
+        err = (oracle - comm).abs().max().item()
+        ref = oracle.abs().max().item()
+        check["max_abs_err_vs_fp32_oracle"] = err
+        check["oracle_abs_max"] = ref
+        assert err <= 2.0 ** -7 * max(ref, 1.0), f"community model is off the fp32 oracle by {err} (|max| {ref})"
+    assert check["identical_across_ranks"], "ranks disagree on the community model"
+
+    # ---- stock arm: plain PyTorch / cuDNN learner + NCCL FedAvg, the whole round -----------------------------
+    stock = None
+    if not args.no_stock and args.model == "resnet18":
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "bench"))
+        from stock import StockLearner
+        res = {}
+        for mode, graph in (("eager", False), ("cuda_graph", True)):
+            sl = StockLearner(device, (B, 3, 32, 32), graph=graph)
+            if graph and sl.graph is None:
+                res[mode] = None
+                continue
+            def stock_round(r):
+                for s_ in range(S):
+                    x, y = dev_pool[0][(r * S + s_) % len(dev_pool[0])]
+                    sl.step(x, y)
+                sl.fedavg(1.0 / world, world)
+            for r in range(3):
+                stock_round(r)
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for r in range(args.steps):
+                stock_round(r)
+            b.record()
+            barrier()
+            res[mode] = a.elapsed_time(b) / args.steps
+            del sl
+        stock = res
+
+    t = torch.tensor([dev_ms, e2e_ms, k1_ms, nccl_ms] + [stock[m] if stock and stock[m] else 0.0
+                                                         for m in ("eager", "cuda_graph")],
+                     device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = t.tolist()
+    dev_ms, e2e_ms, k1_ms, nccl_ms, stock_eager_ms, stock_graph_ms = t.tolist()
     n_params = eng.layout.num_params
     learners = eng.num_learners
     value = learners * n_params / (dev_ms * 1e-3)
     e2e_value = learners * n_params / (e2e_ms * 1e-3)
+    stock_best_ms = min([v for v in (stock_eager_ms, stock_graph_ms) if v > 0], default=0.0)
+    vs_baseline = (stock_best_ms / dev_ms) if stock_best_ms > 0 else None   # = value / stock value (same numerator)
+    link_gbs = 770.0  # measured peer-copy bandwidth per direction (B200_PROFILING.md)
+    # roofline of the aggregation alone: one model's worth of bytes has to leave and enter every GPU over NVLink
+    # ((world-1)/world of it with peer loads/stores, 1/world + 1/world per direction with the in-switch reduction);
+    # at world 1 it is an HBM copy of the slots
+    seg_bytes = sum(sg.nbytes for sg in eng.layout.segments)
+    if world > 1:
+        roof_ms = seg_bytes * (world - 1) / world / (link_gbs * 1e9) * 1e3
+    else:
+        roof_ms = seg_bytes * (k + 1) / (6553.9e9) * 1e3
     x0, y0 = pool[0][0]
     h2d = k * S * (x0.numel() * x0.element_size() + (y0.numel() * y0.element_size() if y0 is not x0 else 0))
     d2h = 4 * k
@@ -215,7 +306,7 @@ def main():
             "metric": "aggregated_params_per_sec (federation round: local training + fused FedAvg)",
             "value": value, "unit": "params/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": dev_ms, "round_time_s": dev_ms * 1e-3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random CIFAR-shaped batches, random-init weights)",
+            "vs_baseline": vs_baseline, "dtype": "bf16", "data": "synthetic (random CIFAR-shaped batches, random-init weights)",
             "impl": "ours",
             "config": {"model": args.model, "params": n_params, "learners": learners,
                        "learners_per_gpu": k, "protocol": "synchronous", "rule": "FedAvg",
@@ -228,6 +319,19 @@ def main():
             "e2e": {"value": e2e_value, "unit": "params/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "FederationEngine.run_round(pinned host batches) -> host losses"},
+            "baseline_arm": {"what": "stock PyTorch/cuDNN ResNet-18 (bf16 channels_last, fused SGD) + NCCL FedAvg "
+                                     "(buf *= w; all_reduce), same batch / local steps / GPUs, measured in this process; "
+                                     "vs_baseline = its best round time / ours (the reference publishes no number and "
+                                     "cannot be installed offline)",
+                             "ms_per_round_eager": stock_eager_ms or None,
+                             "ms_per_round_cuda_graph": stock_graph_ms or None},
+            "aggregation": {"k1_fused_ms": k1_ms, "nccl_scale_allreduce_ms": nccl_ms,
+                            "k1_vs_nccl": nccl_ms / k1_ms if k1_ms > 0 else None,
+                            "mode": "nvls" if eng.nvls else ("p2p" if world > 1 else "local"),
+                            "roofline_ms": roof_ms, "fraction_of_roofline": roof_ms / k1_ms if k1_ms > 0 else None,
+                            "roofline_def": "bytes that must cross NVLink per GPU and direction / 770 GB/s measured "
+                                            "(world 1: slot reads + community write / measured HBM copy)"},
+            "community_check": check,
             "gpu_launches": launches, "gpu_launches_per_round": launches / args.steps,
             "last_loss": last["loss"] if last else None,
         }))

@@ -102,3 +102,107 @@ def test_two_gloo_learner_processes_share_a_fabric(tmp_path, monkeypatch, rule, 
     for name in ("learner0", "learner1"):
         log = open(os.path.join(str(tmp_path / "w_w2"), name + ".log"), errors="replace").read()
         assert "Traceback" not in log, log[-3000:]
+
+
+# ---- GPU tier: the same control path on the kernels --------------------------------------------------------------
+def _resnet_recipe(n, seed):
+    def recipe():
+        from metisfl_b200.models.model_dataset import ModelDatasetClassification
+        rng = np.random.default_rng(seed)
+        y = rng.integers(0, 10, size=n)
+        x = rng.normal(size=(n, 3, 32, 32)).astype(np.float32) + (y[:, None, None, None] / 4.0).astype(np.float32)
+        return ModelDatasetClassification(x=x, y=y.astype(np.int64), size=n,
+                                          examples_per_class={int(c): int((y == c).sum()) for c in range(10)})
+    return recipe
+
+
+def _gpu_session(tmp_path, tag, monkeypatch, fabric, world, model, recipe_fn, rule="FedAvg", protocol=None, rounds=3,
+                 batch=32, n=64):
+    d = _env(**{"GlobalModelConfig.AggregationRule.Name": rule, "TerminationSignals.FederationRounds": rounds,
+                "LocalModelConfig.BatchSize": batch, "LocalModelConfig.LocalEpochs": 1})
+    fe = d["FederationEnvironment"]
+    base = fe["Learners"][0]
+    import copy
+    from test_e2e_cpu import _free_ports
+    ports = _free_ports(world)
+    fe["Learners"] = []
+    for r in range(world):
+        l = copy.deepcopy(base)
+        l["LearnerID"] = f"localhost-{r}"
+        l["GRPCServicer"]["Port"] = ports[r]
+        l["CudaDevices"] = [r]
+        fe["Learners"].append(l)
+    fe["DeviceFabric"] = fabric
+    fe["ModelDType"] = "bf16"
+    if protocol:
+        fe["CommunicationProtocol"]["Name"] = protocol
+        fe["ModelStoreConfig"]["LineageLength"] = 2
+    snap = tmp_path / f"snap_{tag}"
+    monkeypatch.setenv("METISFL_SNAPSHOT_DIR", str(snap))
+    torch.manual_seed(0)
+    s = DriverSession(FederationEnvironment(d), model(), recipe_fn(n, 1), None, recipe_fn(n, 3),
+                      working_dir=str(tmp_path / f"w_{tag}"), launcher="inprocess" if world == 1 else "local",
+                      banner=False, model_dtype=torch.bfloat16)
+    stats = s.run(request_every_secs=0.5)
+    return stats, str(snap)
+
+
+def _bf16_model(snapshot_dir):
+    import json
+    with open(os.path.join(snapshot_dir, "state.json")) as f:
+        state = json.load(f)
+    with open(os.path.join(snapshot_dir, state["community_model_file"]), "rb") as f:
+        fm = model_pb2.FederatedModel.FromString(f.read())
+    out = {}
+    for v in fm.model.variables:
+        spec = v.plaintext_tensor.tensor_spec
+        raw = np.frombuffer(spec.value, dtype=np.uint8).copy()
+        t = torch.from_numpy(raw)
+        dt = {8: torch.float32, 3: torch.int64, 11: torch.bfloat16}[spec.type.type]
+        out[v.name] = t.view(dt).float()
+    return out, fm.global_iteration
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_resnet18_three_rounds_through_driver_session_on_the_device_path(tmp_path, monkeypatch):
+    """Config #2 at world 1 through the public API: control-only MarkTaskCompleted, controller-commanded K1,
+    device-timed runtime metadata, K4 quantifier counts; community model compared with the host (CPU oracle) path."""
+    from metisfl_b200.models.zoo import ResNet18
+    stats, snap = _gpu_session(tmp_path, "dev", monkeypatch, True, 1, ResNet18, _resnet_recipe)
+    c = _counters(stats)
+    assert c["model_bytes_received"] == 0 and c["aggregation_durations_device_timed"] and c["aggregation_failures"] == 0
+    md = [m for m in stats["federation_runtime_metadata"]["metadata"] if m.get("model_aggregation_block_duration_ms")]
+    assert len(md) >= 3
+    # CUDA-event durations of one fused launch on an 11 M-parameter model: far below a millisecond-scale RPC
+    assert all(0.0 < m["model_aggregation_block_duration_ms"][0] < 5.0 for m in md)
+    assert len(md[0]["model_tensor_quantifiers"]) == 122  # ResNet-18 state: 62 parameters + 60 buffers
+    dev_model, it_dev = _bf16_model(snap)
+    stats_h, snap_h = _gpu_session(tmp_path, "host", monkeypatch, False, 1, ResNet18, _resnet_recipe)
+    assert _counters(stats_h)["model_bytes_received"] > 20_000_000
+    host_model, it_host = _bf16_model(snap_h)
+    assert set(dev_model) == set(host_model)
+    assert all(torch.isfinite(v).all() for v in dev_model.values())
+    if it_dev == it_host:
+        worst = max((dev_model[k] - host_model[k]).abs().max().item() for k in dev_model
+                    if "num_batches_tracked" not in k)
+        assert worst < 0.1, worst
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("world,rule,protocol", [(2, "FedAvg", None), (2, "FedAsync", "Asynchronous"),
+                                                 (2, "FedRec", "Asynchronous"), (4, "FedAvg", None),
+                                                 (8, "FedAvg", None)])
+def test_multi_gpu_fabric_through_driver_session(tmp_path, monkeypatch, world, rule, protocol):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    stats, snap = _gpu_session(tmp_path, f"w{world}", monkeypatch, True, world, FashionMnistMLP,
+                               lambda n, seed: _recipe(n, seed), rule=rule, protocol=protocol, batch=32, n=128)
+    c = _counters(stats)
+    assert c["model_bytes_received"] == 0 and c["fabric_learners"] == world and c["aggregation_failures"] == 0
+    model, it = _bf16_model(snap)
+    assert it >= 2 and all(torch.isfinite(v).all() for v in model.values())
+    for r in range(world):
+        log = open(os.path.join(str(tmp_path / f"w_w{world}"), f"learner{r}.log"), errors="replace").read()
+        assert "Traceback" not in log, log[-3000:]
