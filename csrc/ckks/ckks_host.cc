@@ -8,31 +8,78 @@
 #include <fstream>
 #include <random>
 #include <sstream>
+#include <sys/random.h>
 #include <stdexcept>
 
 namespace mfl::ckks {
 
 namespace {
 
-struct Rng {  // xoshiro256** seeded through splitmix64
-  uint64_t s[4];
-  explicit Rng(uint64_t seed) {
-    for (auto& x : s) {
-      seed += 0x9e3779b97f4a7c15ull;
-      uint64_t z = seed;
-      z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
-      z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
-      x = z ^ (z >> 31);
-    }
+// ChaCha20 keystream generator (RFC 8439 block function).  All secret material of the scheme - the ternary secret,
+// the Gaussian errors, the encryption randomness u, e0, e1 - comes from a stream keyed with 256 bits of operating
+// system entropy (getrandom); the PUBLIC uniform polynomial a of a key pair is drawn from a second, independently
+// keyed stream, so nothing an observer of the public key sees is an output of the stream that produced the secret.
+// A caller-supplied 64-bit seed (tests, reproducible demos) expands to a key deterministically and is NOT secure.
+struct Rng {
+  uint32_t key[8], nonce[3], counter = 0;
+  uint32_t block[16];
+  int used = 16;
+  static uint32_t rotl(uint32_t x, int k) { return (x << k) | (x >> (32 - k)); }
+  static void quarter(uint32_t* x, int a, int b, int c, int d) {
+    x[a] += x[b]; x[d] = rotl(x[d] ^ x[a], 16);
+    x[c] += x[d]; x[b] = rotl(x[b] ^ x[c], 12);
+    x[a] += x[b]; x[d] = rotl(x[d] ^ x[a], 8);
+    x[c] += x[d]; x[b] = rotl(x[b] ^ x[c], 7);
   }
-  static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
+  void refill() {
+    uint32_t st[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u};
+    for (int i = 0; i < 8; ++i) st[4 + i] = key[i];
+    st[12] = counter++;
+    for (int i = 0; i < 3; ++i) st[13 + i] = nonce[i];
+    uint32_t x[16];
+    std::memcpy(x, st, sizeof(x));
+    for (int r = 0; r < 10; ++r) {
+      quarter(x, 0, 4, 8, 12); quarter(x, 1, 5, 9, 13); quarter(x, 2, 6, 10, 14); quarter(x, 3, 7, 11, 15);
+      quarter(x, 0, 5, 10, 15); quarter(x, 1, 6, 11, 12); quarter(x, 2, 7, 8, 13); quarter(x, 3, 4, 9, 14);
+    }
+    for (int i = 0; i < 16; ++i) block[i] = x[i] + st[i];
+    used = 0;
+    if (counter == 0) ++nonce[0];  // 256 GiB per nonce value; roll over into the nonce
+  }
+  // seed == 0: fresh OS entropy.  `stream` separates independent generators derived from one seed.
+  explicit Rng(uint64_t seed, uint64_t stream = 0) {
+    if (seed == 0) {
+      size_t got = 0;
+      while (got < sizeof(key)) {
+        const ssize_t n = getrandom(reinterpret_cast<char*>(key) + got, sizeof(key) - got, 0);
+        if (n <= 0) throw std::runtime_error("CKKS: the operating system entropy source is unavailable");
+        got += (size_t)n;
+      }
+    } else {  // deterministic, for tests only: splitmix64 expansion of the seed
+      uint64_t z0 = seed;
+      for (int i = 0; i < 4; ++i) {
+        z0 += 0x9e3779b97f4a7c15ull;
+        uint64_t z = z0;
+        z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+        z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+        z ^= z >> 31;
+        key[2 * i] = (uint32_t)z; key[2 * i + 1] = (uint32_t)(z >> 32);
+      }
+    }
+    nonce[0] = 0; nonce[1] = (uint32_t)stream; nonce[2] = (uint32_t)(stream >> 32);
+  }
   uint64_t next() {
-    const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
-    s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45);
+    if (used > 14) refill();
+    const uint64_t r = (uint64_t)block[used] | ((uint64_t)block[used + 1] << 32);
+    used += 2;
     return r;
   }
   double uniform() { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); }
-  int ternary() { return (int)(next() % 3) - 1; }
+  int ternary() {  // unbiased: reject the one 64-bit value class that does not divide evenly by 3
+    uint64_t x;
+    do x = next(); while (x >= UINT64_MAX - UINT64_MAX % 3);
+    return (int)(x % 3) - 1;
+  }
   int gaussian(double sigma) {
     double u1 = uniform(), u2 = uniform();
     if (u1 < 1e-300) u1 = 1e-300;
@@ -46,9 +93,11 @@ struct Rng {  // xoshiro256** seeded through splitmix64
   }
 };
 
+// 64 bits of OS entropy, used to key per-ciphertext streams of one Encrypt call
 uint64_t EntropySeed() {
-  std::random_device rd;
-  return ((uint64_t)rd() << 32) ^ rd() ^ ((uint64_t)rd() << 17);
+  uint64_t v = 0;
+  if (getrandom(&v, sizeof(v), 0) != (ssize_t)sizeof(v)) throw std::runtime_error("CKKS: getrandom failed");
+  return v | 1;
 }
 
 inline uint64_t SignedToMod(long long v, uint64_t q) {
@@ -290,7 +339,8 @@ void Scheme::DecodeCoeffs(const std::vector<double>& coeffs, size_t n, double* v
 // ---------------------------------------------------------------------------------------------
 void Scheme::KeyGen(uint64_t seed) {
   const uint32_t N = p_.n(), L = (uint32_t)p_.q.size();
-  Rng rng(seed ? seed : EntropySeed());
+  Rng rng(seed, /*stream=*/1);      // secret material: s and the errors
+  Rng pub(seed, /*stream=*/2);      // the public uniform polynomials (independently keyed when seed == 0)
   std::vector<int> s(N), e(N);
   for (auto& x : s) x = rng.ternary();
   sk_.assign((size_t)L * N, 0);
@@ -304,7 +354,7 @@ void Scheme::KeyGen(uint64_t seed) {
       const uint64_t q = p_.q[l];
       uint64_t* al = a + (size_t)l * N;
       uint64_t* bl = b + (size_t)l * N;
-      for (uint32_t i = 0; i < N; ++i) { al[i] = rng.below(q); bl[i] = SignedToMod(e[i], q); }
+      for (uint32_t i = 0; i < N; ++i) { al[i] = pub.below(q); bl[i] = SignedToMod(e[i], q); }
       NttForward(bl, tables_[l], p_.log_n);  // e in evaluation form; a is sampled directly in it
       const uint64_t* sl = &sk_[(size_t)l * N];
       for (uint32_t i = 0; i < N; ++i) {
@@ -341,10 +391,12 @@ std::string Scheme::Encrypt(const double* vals, size_t n, uint64_t seed) const {
   std::string out(sizeof(h) + (size_t)n_ct * ct_words(h) * 8, '\0');
   std::memcpy(out.data(), &h, sizeof(h));
   uint64_t* data = reinterpret_cast<uint64_t*>(out.data() + sizeof(h));
-  const uint64_t base = seed ? seed : EntropySeed();
+  // one 256-bit key per call (OS entropy unless a test seed is given), one ChaCha20 stream per ciphertext
+  const Rng master(seed, 0);
 #pragma omp parallel for schedule(dynamic)
   for (long c = 0; c < (long)n_ct; ++c) {
-    Rng rng(base + 0x9e3779b97f4a7c15ull * (uint64_t)(c + 1));
+    Rng rng = master;
+    rng.nonce[1] = (uint32_t)(c + 1); rng.nonce[2] = (uint32_t)((uint64_t)(c + 1) >> 32); rng.counter = 0; rng.used = 16;
     std::vector<double> m;
     const size_t off = (size_t)c * slots;
     EncodeCoeffs(vals + off, std::min<size_t>(slots, n - off), h.scale, m);

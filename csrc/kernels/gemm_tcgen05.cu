@@ -58,7 +58,34 @@ struct Epilogue {
   // operand majors: 0 = K-major (reduction index contiguous), 1 = MN-major (tensor map is [reduction rows, M or N
   // contiguous]; the tile arrives as 64 x 64 boxes, 8 KB apart, and the instruction descriptor transposes it)
   int32_t a_mn, b_mn;
+  // ---- convolution gradients on the same pipeline (K11) ------------------------------------------------------
+  // mode 0: plain GEMM / forward convolution (the `conv` flag above)
+  // mode 2: data gradient.  A = im2col of dY (rows = dX pixels of one stride-parity class, columns = (tap, k));
+  //         B = the filters W[K, R*S*C] read MN-major (a [64 k, 64 c] box per tap); k-block kb -> tap kb / kb_per_tap
+  // mode 3: weight gradient.  A = dY [P, K] read MN-major (M = output channels); B = im2col of X read MN-major:
+  //         one [64 pixels, 64 channels] im2col box per 64 columns of the (r, s, c) axis; the reduction runs over
+  //         the P = N*OH*OW output pixels
+  int32_t mode;
+  int32_t ntaps, kb_per_tap;
+  int8_t tap_ow[16], tap_oh[16], tap_w[16];   // im2col offsets of each tap and the filter tap it multiplies with
+  int32_t c_in;                               // mode 2: channels of dX = column pitch of one filter tap in W
+  // split-K: the k-blocks of a tile are divided among `splits` CTAs, each adds its fp32 partial tile into a
+  // zero-initialised workspace with TMA reduce-add stores (tmap_c is the workspace map); a finalize kernel
+  // converts it and re-zeroes the workspace
+  int32_t splits, kb_per_split;
+  // 4-D store (mode 2, stride 2): the 32 rows of an epilogue slab are a {64 c, bw, bh, bn} box of the strided
+  // parity-class view of dX
+  int32_t store4d, box_w, box_h, box_n, cls_w, cls_h;
 };
+
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
 
 template <int ACT> __device__ __forceinline__ float apply_act(float x) {
   if constexpr (ACT == 1) return fmaxf(x, 0.f);
@@ -89,6 +116,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   const int tiles_n = (ep.N + BN - 1) / BN, tiles_m = (ep.M + kBlockM - 1) / kBlockM;
   const int num_tiles = tiles_m * tiles_n;
   const int num_kb = (ep.K + kBlockK - 1) / kBlockK;
+  // work item w = tile * splits + split; a split owns k-blocks [split * kb_per_split, +kb_per_split) (clipped)
+  const int splits = ep.splits > 1 ? ep.splits : 1;
+  const int num_work = num_tiles * splits;
+  const int kbps = splits > 1 ? ep.kb_per_split : num_kb;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
@@ -115,16 +146,52 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
       uint32_t it = 0;  // k-block counter across all tiles of this CTA: the ring never drains
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int ohw = ep.out_h * ep.out_w;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int tile = w / splits, split = w - tile * splits;
         const int m0 = (tile / tiles_n) * kBlockM, n0 = (tile % tiles_n) * BN;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % kStages;
           const uint32_t phase = (it / kStages) & 1;
           mbar_wait(empty_bar + s, phase ^ 1);
-          mbar_expect_tx(full_bar + s, C::kStageBytes);
           uint8_t* a_dst = smem + (size_t)s * C::kStageBytes;
+          if (ep.mode == 3) {  // weight gradient
+            int nvalid = 0;
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) nvalid += (n0 + 64 * j < ep.N) ? 1 : 0;
+            mbar_expect_tx(full_bar + s, kABytes + (uint32_t)nvalid * 8192u);
+#pragma unroll
+            for (int j = 0; j < kBlockM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmap_a, full_bar + s, m0 + 64 * j, kb * kBlockK);
+            const int p0 = kb * kBlockK, img = p0 / ohw, rem = p0 - img * ohw;
+            const int oh = rem / ep.out_w, ow = rem - oh * ep.out_w;
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) {
+              const int nb = (n0 >> 6) + j;
+              if (nb * 64 < ep.N) {
+                const int tap = nb / ep.c_blocks, cb = nb - tap * ep.c_blocks;
+                tma_load_im2col_4d(a_dst + kABytes + j * 8192, &tmap_b, full_bar + s, cb * kBlockK,
+                                   ow * ep.stride - ep.pad, oh * ep.stride - ep.pad, img,
+                                   (uint16_t)(tap % ep.filt_s), (uint16_t)(tap / ep.filt_s));
+              }
+            }
+            continue;
+          }
+          mbar_expect_tx(full_bar + s, C::kStageBytes);
+          if (ep.mode == 2) {  // data gradient: A = im2col(dY) for tap kb / kb_per_tap, B = W tap, MN-major
+            const int tap = kb / ep.kb_per_tap, kk = kb - tap * ep.kb_per_tap;
+            const int img = m0 / ohw, rem = m0 - img * ohw;
+            const int oh = rem / ep.out_w, ow = rem - oh * ep.out_w;
+            tma_load_im2col_4d(a_dst, &tmap_a, full_bar + s, kk * kBlockK, ow - ep.pad, oh - ep.pad, img,
+                               (uint16_t)ep.tap_ow[tap], (uint16_t)ep.tap_oh[tap]);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(a_dst + kABytes + j * 8192, &tmap_b, full_bar + s, (int)ep.tap_w[tap] * ep.c_in + n0 + 64 * j,
+                          kk * kBlockK);
+            continue;
+          }
           if (ep.conv) {
-            const int img = m0 / (ep.out_h * ep.out_w), rem = m0 % (ep.out_h * ep.out_w);
+            const int img = m0 / ohw, rem = m0 % ohw;
             const int oh = rem / ep.out_w, ow = rem % ep.out_w;
             const int rs = kb / ep.c_blocks, cb = kb % ep.c_blocks;
             tma_load_im2col_4d(a_dst, &tmap_a, full_bar + s, cb * kBlockK, ow * ep.stride - ep.pad,
@@ -155,12 +222,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     const uint64_t a_kstep = ep.a_mn ? 128 : 2, b_kstep = ep.b_mn ? 128 : 2;
     const uint32_t a_lbo = ep.a_mn ? 512 : 1, b_lbo = ep.b_mn ? 512 : 1;
     uint32_t it = 0, t = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++t) {
+      const int split = w % splits;
+      const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
       const uint32_t buf = t & 1, use = t >> 1;
       mbar_wait(tmem_empty_bar + buf, (use & 1) ^ 1);  // epilogue has drained this accumulator
       tcgen05_fence_after();
       const uint32_t tmem_d = tmem_base + buf * BN;
-      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const int s = it % kStages;
         const uint32_t phase = (it / kStages) & 1;
         mbar_wait(full_bar + s, phase);
@@ -169,7 +238,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         const uint64_t adesc = make_sw128_desc(a_addr, a_lbo), bdesc = make_sw128_desc(a_addr + kABytes, b_lbo);
         if (elect_one()) {
           // +32 bytes per K step inside the 128-byte swizzle atom (encoded >> 4)
-          if (kb == 0) umma_f16_c<false>(tmem_d, adesc, bdesc, idesc);
+          if (kb == kb0) umma_f16_c<false>(tmem_d, adesc, bdesc, idesc);
           else umma_f16_c<true>(tmem_d, adesc, bdesc, idesc);
 #pragma unroll
           for (int k = 1; k < kBlockK / kUmmaK; ++k)
@@ -184,7 +253,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   } else if (warp >= 4) {  // ===== epilogue: TMEM -> registers -> global =====
     const int wq = warp & 3;  // TMEM lane quarter this warp may access
     uint32_t t = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++t) {
+      const int tile = w / splits;
       const int m0 = (tile / tiles_n) * kBlockM, n0 = (tile % tiles_n) * BN;
       const uint32_t buf = t & 1, use = t >> 1;
       mbar_wait(tmem_full_bar + buf, use & 1);
@@ -232,7 +302,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> async proxy
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);
+            if (splits > 1) {
+              tma_reduce_add_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);  // fp32 partial tile += into the workspace
+            } else if (ep.store4d) {
+              // rows m0 + wq*32 .. +31 of the parity-class pixel space = a {bw, bh, bn} box of the strided view of dX
+              const int r0 = m0 + wq * 32;
+              const int per_img = ep.cls_w * ep.cls_h;
+              const int img = r0 / per_img, rem = r0 - img * per_img;
+              tma_store_4d(&tmap_c, slab, n0 + c, rem % ep.cls_w, rem / ep.cls_w, img);
+            } else {
+              tma_store_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);
+            }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
         }
@@ -322,7 +402,7 @@ namespace mfl { namespace gemm {
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const Epilogue& ep, int bn,
                        int act, bool c32, cudaStream_t st) {
   const int tiles = ((ep.N + bn - 1) / bn) * ((ep.M + kBlockM - 1) / kBlockM);
-  const int grid = std::min(tiles, sm_count());
+  const int grid = std::min(tiles * std::max(1, (int)ep.splits), sm_count());
   int rc = 0;
 #define MFL_GEMM_LAUNCH(BN_, ACT_, F32_)                                                                          \
   do {                                                                                                            \
@@ -458,4 +538,178 @@ extern "C" int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int 
   if (int rc = make_map(&tc, y, m, k, k, 32, false)) return rc;
   Epilogue ep{y, nullptr, k, m, k, kk, 0, 0, 0, 1, 1, oh, ow, stride, pad, s, c / 64};
   return launch_gemm(ta, tb, tc, ep, bn, 0, false, (cudaStream_t)stream);
+}
+
+
+// =====================================================================================================================
+// K11 gradients: data gradient (stride 1 and, by stride-parity classes, stride 2) and weight gradient (split-K over the
+// output pixels) on the same persistent tcgen05 pipeline.  Reference counterpart: the framework convolution backward
+// under model.fit (keras_model_ops.py:156).
+// =====================================================================================================================
+namespace mfl { namespace gemm {
+
+// ws (fp32 [rows, cols], the split-K workspace) -> out (bf16, row pitch ld), optionally accumulating; re-zeroes ws
+__global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict__ ws, __nv_bfloat16* __restrict__ out,
+                                                              int rows, int cols, int64_t ld, int accumulate) {
+  const int64_t vec_per_row = cols / 8;
+  const int64_t total = (int64_t)rows * vec_per_row;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / vec_per_row, c = (i - r * vec_per_row) * 8;
+    float4* p = reinterpret_cast<float4*>(ws + r * cols + c);
+    const float4 a = p[0], b = p[1];
+    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    uint4* o = reinterpret_cast<uint4*>(out + r * ld + c);
+    if (accumulate) {
+      float f[8];
+      VecTraits<MFL_BFLOAT16>::unpack(*o, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += f[j];
+    }
+    *o = VecTraits<MFL_BFLOAT16>::pack(v);
+    p[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    p[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+static int make_im2col_map(CUtensorMap* map, const void* base, int n, int h, int wd, int c, int lower_w, int lower_h,
+                           int upper_w, int upper_h, int trav_stride, int pixels) {
+  bind_context();
+  EncodeIm2colFn fn = encode_im2col_fn();
+  MFL_ARG(fn != nullptr, "conv2d: cuTensorMapEncodeIm2col is not available from this driver");
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)wd, (cuuint64_t)h, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)wd * c * 2, (cuuint64_t)h * wd * c * 2};
+  int lower[2] = {lower_w, lower_h};
+  int upper[2] = {upper_w, upper_h};
+  cuuint32_t estr[4] = {1, (cuuint32_t)trav_stride, (cuuint32_t)trav_stride, 1};
+  CUresult res = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper,
+                    (cuuint32_t)kBlockK, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MFL_ARG(res == CUDA_SUCCESS, "conv2d: cuTensorMapEncodeIm2col failed with CUresult %d", (int)res);
+  return 0;
+}
+
+// strided parity-class view of dX for the 4-D epilogue store: {C, W/s, H/s, N}, box {64, bw, bh, bn}
+static int make_store4d_map(CUtensorMap* map, void* base, int n, int h, int wd, int c, int stride, int cls_w, int cls_h,
+                            int bw, int bh, int bnn) {
+  bind_context();
+  EncodeTiledFn fn = encode_fn();
+  MFL_ARG(fn != nullptr, "conv2d: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)cls_w, (cuuint64_t)cls_h, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)stride * c * 2, (cuuint64_t)stride * wd * c * 2, (cuuint64_t)h * wd * c * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bnn};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MFL_ARG(r == CUDA_SUCCESS, "conv2d dgrad: strided output tensor map failed with CUresult %d", (int)r);
+  return 0;
+}
+
+static bool pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+
+}}  // namespace mfl::gemm
+
+extern "C" size_t mfl_conv2d_wgrad_workspace_bytes(int c, int k, int r, int s) { return (size_t)k * r * s * c * sizeof(float); }
+
+// dW[K,R,S,C] (+)= sum over output pixels of dY[p, k] * X[p + (r, s), c].  ws: zero-initialised fp32 scratch of
+// mfl_conv2d_wgrad_workspace_bytes() bytes; it is handed back zeroed, so one buffer can serve every layer of a model on
+// one stream.  NHWC bf16, C % 64 == 0, K % 8 == 0.
+extern "C" int mfl_conv2d_wgrad_bf16(void* dw, const void* dy, const void* x, float* ws, int n, int h, int wd, int c, int k,
+                                     int r, int s, int stride, int pad, int accumulate, void* stream) {
+  using namespace mfl::gemm;
+  MFL_ARG(dw && dy && x && ws && n > 0 && h > 0 && wd > 0, "conv2d wgrad: null operand or empty shape");
+  MFL_ARG(c % 64 == 0 && k % 8 == 0, "conv2d wgrad: needs C %% 64 == 0 and K %% 8 == 0 (got C=%d K=%d)", c, k);
+  MFL_ARG(stride >= 1 && stride <= 8 && pad >= 0 && r >= 1 && s >= 1 && r * s <= 49, "conv2d wgrad: bad geometry");
+  const int oh = (h + 2 * pad - r) / stride + 1, ow = (wd + 2 * pad - s) / stride + 1;
+  const int P = n * oh * ow, rsc = r * s * c;
+  CUtensorMap ta, tb, tc;
+  if (int rc = make_map_mn(&ta, dy, k, P, k)) return rc;                         // A: dY [P, K], M = K contiguous
+  if (int rc = make_im2col_map(&tb, x, n, h, wd, c, -pad, -pad, pad - (s - 1), pad - (r - 1), stride, 64)) return rc;
+  if (int rc = make_map(&tc, ws, k, rsc, rsc, 32, true)) return rc;             // fp32 workspace [K, RSC]
+  const int bn = rsc > 128 ? 256 : (rsc > 64 ? 128 : 64);
+  Epilogue ep{};
+  ep.c = ws; ep.bias = nullptr; ep.ldc = rsc; ep.M = k; ep.N = rsc; ep.K = P;
+  ep.c_fp32 = 1; ep.tma_store = 1; ep.a_mn = 1; ep.b_mn = 1; ep.mode = 3;
+  ep.out_h = oh; ep.out_w = ow; ep.stride = stride; ep.pad = pad; ep.filt_s = s; ep.c_blocks = c / 64;
+  const int tiles = ((rsc + bn - 1) / bn) * ((k + kBlockM - 1) / kBlockM);
+  const int num_kb = (P + kBlockK - 1) / kBlockK;
+  // enough (tile, split) work items for about two per SM; every split owns at least one k-block
+  int splits = std::max(1, std::min(num_kb, (2 * sm_count() + tiles - 1) / tiles));
+  ep.kb_per_split = (num_kb + splits - 1) / splits;
+  ep.splits = (num_kb + ep.kb_per_split - 1) / ep.kb_per_split;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = launch_gemm(ta, tb, tc, ep, bn, 0, true, st)) return rc;
+  const int64_t vecs = (int64_t)k * rsc / 8;
+  const int blocks = (int)std::min<int64_t>((vecs + 255) / 256, (int64_t)sm_count() * 4);
+  splitk_finalize_kernel<<<blocks, 256, 0, st>>>(ws, static_cast<__nv_bfloat16*>(dw), k, rsc, rsc, accumulate);
+  return check(cudaGetLastError(), "splitk_finalize_kernel launch");
+}
+
+// dX[N,H,W,C] = sum_{r,s,k} dY[n, (h + pad - r) / stride, (w + pad - s) / stride, k] * W[k, r, s, c]  (exact divisions only).
+// stride 1: one launch over all R*S taps.  stride 2: one launch per (h mod 2, w mod 2) class - each class is a
+// stride-1 correlation of dY with the taps of matching parity (for 3x3 / pad 1: 1, 2, 2 and 4 taps: no wasted math) -
+// written through a strided 4-D tensor map.  NHWC bf16; K % 64 == 0, C % 8 == 0; stride 2 needs H/2 and W/2 powers of
+// two (<= 32) so that 32-row store slabs tile the class grid.
+extern "C" int mfl_conv2d_dgrad_bf16(void* dx, const void* dy, const void* w, int n, int h, int wd, int c, int k, int r,
+                                     int s, int stride, int pad, void* stream) {
+  using namespace mfl::gemm;
+  MFL_ARG(dx && dy && w && n > 0 && h > 0 && wd > 0, "conv2d dgrad: null operand or empty shape");
+  MFL_ARG(k % 64 == 0 && c % 8 == 0, "conv2d dgrad: needs K %% 64 == 0 and C %% 8 == 0 (got C=%d K=%d)", c, k);
+  MFL_ARG((stride == 1 || stride == 2) && r * s <= 16 && pad >= 0 && pad < r && pad < s, "conv2d dgrad: bad geometry");
+  const int oh = (h + 2 * pad - r) / stride + 1, ow = (wd + 2 * pad - s) / stride + 1;
+  MFL_ARG(oh > 0 && ow > 0, "conv2d dgrad: empty output");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int rsc = r * s * c;
+  CUtensorMap ta, tb, tc;
+  if (int rc = make_map_mn(&tb, w, rsc, k, rsc)) return rc;   // B: W [K, RSC]: rows = reduction k, columns contiguous
+  const int bn = c > 128 ? 256 : (c > 64 ? 128 : 64);
+  if (stride == 2) {
+    MFL_ARG(h % 2 == 0 && wd % 2 == 0 && h / 2 == oh && wd / 2 == ow && pow2(oh) && pow2(ow) && c % 64 == 0,
+            "conv2d dgrad: stride 2 needs even H, W with H/2, W/2 powers of two and C %% 64 == 0");
+    MFL_CUDA(cudaMemsetAsync(dx, 0, (size_t)n * h * wd * c * 2, st));  // classes without a tap (1x1 filters) stay zero
+  }
+  for (int ph = 0; ph < stride; ++ph) {
+    for (int pw = 0; pw < stride; ++pw) {
+      Epilogue ep{};
+      int dmin_h = 1 << 20, dmax_h = -(1 << 20), dmin_w = 1 << 20, dmax_w = -(1 << 20);
+      int th[16], tw_[16], tf[16], nt = 0;
+      for (int rr = 0; rr < r; ++rr) {
+        if ((ph + pad - rr) % stride != 0) continue;
+        const int dh = (ph + pad - rr) / stride;   // may be negative: C division is exact here
+        for (int ss = 0; ss < s; ++ss) {
+          if ((pw + pad - ss) % stride != 0) continue;
+          const int dw_ = (pw + pad - ss) / stride;
+          th[nt] = dh; tw_[nt] = dw_; tf[nt] = rr * s + ss; ++nt;
+          dmin_h = std::min(dmin_h, dh); dmax_h = std::max(dmax_h, dh);
+          dmin_w = std::min(dmin_w, dw_); dmax_w = std::max(dmax_w, dw_);
+        }
+      }
+      if (nt == 0) continue;
+      const int cls_h = (h - ph + stride - 1) / stride, cls_w = (wd - pw + stride - 1) / stride;
+      // base pixel of class position (h', w') is (h' + dmin); tap t reads base + (d_t - dmin)
+      ep.mode = 2; ep.ntaps = nt; ep.kb_per_tap = k / 64; ep.c_in = c;
+      for (int t = 0; t < nt; ++t) {
+        ep.tap_oh[t] = (int8_t)(th[t] - dmin_h); ep.tap_ow[t] = (int8_t)(tw_[t] - dmin_w); ep.tap_w[t] = (int8_t)tf[t];
+      }
+      // im2col box: base positions [dmin, dmin + cls - 1] per axis; upper corner = (last base) - (dim - 1) - window + 1 ...
+      // in the driver's convention: #positions = dim + upper - lower - (window - 1), window = dmax - dmin + 1
+      const int win_h = dmax_h - dmin_h + 1, win_w = dmax_w - dmin_w + 1;
+      const int upper_h = cls_h - oh + dmin_h, upper_w = cls_w - ow + dmin_w;
+      (void)win_h; (void)win_w;
+      if (int rc = make_im2col_map(&ta, dy, n, oh, ow, k, dmin_w, dmin_h, upper_w, upper_h, 1, kBlockM)) return rc;
+      ep.c = dx; ep.ldc = c; ep.M = n * cls_h * cls_w; ep.N = c; ep.K = nt * k;
+      ep.c_fp32 = 0; ep.tma_store = 1; ep.a_mn = 0; ep.b_mn = 1;
+      ep.out_h = cls_h; ep.out_w = cls_w; ep.stride = 1; ep.pad = -dmin_h;  // the kernel subtracts `pad` from both axes
+      MFL_ARG(dmin_h == dmin_w, "conv2d dgrad: asymmetric tap windows are not supported");
+      if (stride == 1) {
+        if (int rc = make_map(&tc, dx, ep.M, c, c, 32, false)) return rc;
+      } else {
+        const int bw = std::min(cls_w, 32), bh = std::min(cls_h, 32 / bw), bnn = 32 / (bw * bh);
+        ep.store4d = 1; ep.box_w = bw; ep.box_h = bh; ep.box_n = bnn; ep.cls_w = cls_w; ep.cls_h = cls_h;
+        char* base = static_cast<char*>(dx) + ((size_t)ph * wd + pw) * c * 2;
+        if (int rc = make_store4d_map(&tc, base, n, h, wd, c, stride, cls_w, cls_h, bw, bh, bnn)) return rc;
+      }
+      if (int rc = launch_gemm(ta, tb, tc, ep, bn, 0, false, st)) return rc;
+    }
+  }
+  return 0;
 }

@@ -70,6 +70,20 @@ def _ref_of(model_pb):
     return spec.device_slot if spec.HasField("device_slot") else None
 
 
+def _on_device(fn):
+    """The RPC / task threads that call into the backend start with CUDA device 0 current; the kernels launch on the
+    CALLING thread's current device and stream, so every entry point first makes the backend's GPU current."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *args, **kwargs):
+        if self.device.type == "cuda":
+            with torch.cuda.device(self.device):
+                return fn(self, *args, **kwargs)
+        return fn(self, *args, **kwargs)
+    return wrapper
+
+
 class DeviceBackend:
     """One per learner process: a ``FederationEngine`` rank plus a private evaluation copy of the module."""
 
@@ -77,9 +91,10 @@ class DeviceBackend:
         self.fabric = fabric
         self._endpoint, self._certificate = endpoint, certificate or b""
         self.device = torch.device(device if device is not None else ("cuda" if torch.cuda.is_available() else "cpu"))
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
         if fabric.world > 1 and not dist.is_initialized():
             if self.device.type == "cuda":
-                torch.cuda.set_device(self.device)
                 dist.init_process_group("nccl", init_method=fabric.init_method, rank=fabric.rank,
                                         world_size=fabric.world, device_id=self.device)
             else:
@@ -144,6 +159,7 @@ class DeviceBackend:
         return ref
 
     # -- training ---------------------------------------------------------------------------------------------------
+    @_on_device
     def train(self, train_dataset, learning_task_pb, hyperparameters_pb, model_pb, cancel_event=None):
         eng = self.engine
         ref = self._adopt(model_pb, learning_task_pb.global_iteration)
@@ -192,6 +208,7 @@ class DeviceBackend:
             aux_metadata='{{"device_timed": {}, "fabric_rank": {}}}'.format("true" if cuda else "false", eng.rank))
 
     # -- evaluation -------------------------------------------------------------------------------------------------
+    @_on_device
     @torch.no_grad()
     def evaluate(self, model_pb, datasets, batch_size, metrics):
         """``datasets`` = {code: dataset or None}; returns {code: {metric: value}}."""
@@ -241,6 +258,7 @@ class DeviceBackend:
         return out
 
     # -- aggregation (commanded by the controller) ------------------------------------------------------------------
+    @_on_device
     def aggregate(self, req) -> "learner_pb2.AggregateOnDeviceResponse":
         eng = self.engine
         cuda = self.device.type == "cuda"
@@ -301,6 +319,7 @@ class DeviceBackend:
         resp.ack.CopyFrom(_ack(True))
         return resp
 
+    @_on_device
     def close(self):
         try:
             self.engine.close()

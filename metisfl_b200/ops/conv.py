@@ -1,8 +1,17 @@
-"""Front-end of the implicit-GEMM convolution (K11) and an autograd-aware ``conv2d`` built on it.
+"""Front-end of the implicit-GEMM convolution family (K11) and an autograd-aware ``conv2d`` built on it.
 
-Forward and the stride-1 data gradient run on the tcgen05 kernel (the data gradient is the same
-convolution with spatially flipped, channel-transposed filters and padding ``R-1-p``); the weight
-gradient and stride-2 data gradients still go through ATen (cuDNN) - see DESIGN.md for the gap.
+Forward, data gradient (stride 1 and 2) and weight gradient all run on the persistent tcgen05 pipeline of
+``csrc/kernels/gemm_tcgen05.cu``:
+
+* forward: A = im2col TMA of the activations, B = filters (K-major);
+* data gradient: A = im2col TMA of dY, B = the SAME filter tensor read MN-major through the tensor map (no flipped /
+  transposed copy is made); stride 2 is split into its four (h mod 2, w mod 2) classes, each a stride-1 correlation
+  with the taps of matching parity, written through a strided 4-D tensor map;
+* weight gradient: A = dY read MN-major, B = im2col TMA boxes of the activations read MN-major, the reduction over
+  the N*OH*OW output pixels split over the SMs and combined with TMA reduce-add stores into an fp32 workspace; a
+  finalize kernel adds it into the (bf16) gradient arena.
+
+The weight gradient is issued on a side stream (it is only needed by the optimizer), see below.
 Tensors are NHWC (``torch.channels_last``) bf16.  Reference counterpart: the framework convolutions
 under ``model.fit`` (``keras_model_ops.py:156``).
 """
@@ -27,6 +36,10 @@ def _bind():
         L.mfl_conv2d_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
         L.mfl_conv3x3_supported.argtypes = [i, i, i, i, i]
         L.mfl_conv3x3_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
+        L.mfl_conv2d_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, vp]
+        L.mfl_conv2d_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        L.mfl_conv2d_wgrad_workspace_bytes.restype = C.c_size_t
+        L.mfl_conv2d_wgrad_workspace_bytes.argtypes = [i, i, i, i]
         _BOUND = True
     return L
 
@@ -75,6 +88,69 @@ def conv3x3(x: torch.Tensor, w: torch.Tensor, stats: torch.Tensor = None) -> tor
     return y
 
 
+def _pow2(v: int) -> bool:
+    return v > 0 and (v & (v - 1)) == 0
+
+
+def dgrad_supported(x_shape, w_shape, stride: int, pad: int) -> bool:
+    n, c, h, wd = x_shape
+    k, _, r, s = w_shape
+    if k % 64 != 0 or c % 8 != 0 or pad >= r or pad >= s or r * s > 16:
+        return False
+    if stride == 1:
+        return True
+    if stride != 2 or c % 64 != 0 or h % 2 or wd % 2:
+        return False
+    oh, ow = (h + 2 * pad - r) // 2 + 1, (wd + 2 * pad - s) // 2 + 1
+    return oh == h // 2 and ow == wd // 2 and _pow2(oh) and _pow2(ow)
+
+
+def conv2d_dgrad(gy: torch.Tensor, w: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:
+    """dX of ``conv2d(x, w, stride, pad)``: gy [N,K,OH,OW] and w [K,C,R,S] channels_last bf16 -> [N,C,H,W]."""
+    n, c, h, wd = x_shape
+    k, _, r, s = w.shape
+    gy = gy.contiguous(memory_format=torch.channels_last)
+    w = w.contiguous(memory_format=torch.channels_last)
+    gx = torch.empty((n, c, h, wd), dtype=torch.bfloat16, device=gy.device, memory_format=torch.channels_last)
+    rc = _bind().mfl_conv2d_dgrad_bf16(gx.data_ptr(), gy.data_ptr(), w.data_ptr(), n, h, wd, c, k, r, s, stride, pad,
+                                       _lib.stream_ptr())
+    _lib.check(rc, "mfl_conv2d_dgrad_bf16", launches=stride * stride)
+    return gx
+
+
+_WS = {}   # (device, stream id) -> zeroed fp32 split-K workspace, handed back zeroed by every call
+
+
+def _workspace(device, nbytes: int, stream) -> torch.Tensor:
+    key = (device, stream.cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() * 4 < nbytes:
+        with torch.cuda.stream(stream):
+            ws = torch.zeros(max(nbytes // 4, 1 << 20), dtype=torch.float32, device=device)
+        _WS[key] = ws
+    return ws
+
+
+def conv2d_wgrad(gy: torch.Tensor, x: torch.Tensor, w_shape, stride: int, pad: int, out: torch.Tensor = None,
+                 accumulate: bool = False) -> torch.Tensor:
+    """dW of ``conv2d(x, w, stride, pad)``: [K,C,R,S] channels_last bf16 (``out += dW`` when ``accumulate``)."""
+    n, c, h, wd = x.shape
+    k, _, r, s = w_shape
+    gy = gy.contiguous(memory_format=torch.channels_last)
+    x = x.contiguous(memory_format=torch.channels_last)
+    if out is None:
+        out = torch.empty((k, c, r, s), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+        accumulate = False
+    assert out.is_contiguous(memory_format=torch.channels_last) and out.dtype == torch.bfloat16
+    L = _bind()
+    stream = torch.cuda.current_stream(x.device)
+    ws = _workspace(x.device, L.mfl_conv2d_wgrad_workspace_bytes(c, k, r, s), stream)
+    rc = L.mfl_conv2d_wgrad_bf16(out.data_ptr(), gy.data_ptr(), x.data_ptr(), ws.data_ptr(), n, h, wd, c, k, r, s, stride,
+                                 pad, int(accumulate), stream.cuda_stream)
+    _lib.check(rc, "mfl_conv2d_wgrad_bf16", launches=2)
+    return out
+
+
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, stride, pad):
@@ -87,19 +163,32 @@ class _Conv2dFn(torch.autograd.Function):
         x, w = ctx.saved_tensors
         stride, pad = ctx.stride, ctx.pad
         gy = gy.contiguous(memory_format=torch.channels_last)
-        k, c, r, s = w.shape
         gx = gw = None
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        if need_x and stride == 1 and k % 64 == 0 and c % 8 == 0 and r - 1 - pad >= 0:
-            # dX = conv(dY, flip(W)^T): filters [C, K, R, S] with both spatial axes reversed
-            wt = w.flip(2, 3).permute(1, 0, 2, 3).contiguous(memory_format=torch.channels_last)
-            gx = conv2d_fprop(gy, wt, 1, r - 1 - pad)
+        own_w = need_w and x.shape[1] % 64 == 0 and w.shape[0] % 8 == 0
+        if own_w:
+            # the weight gradient is off the critical path: side stream, accumulated straight into the flat arena
+            direct = OVERLAP_WGRAD and w.grad is not None and w.grad.dtype == torch.bfloat16 and \
+                w.grad.is_contiguous(memory_format=torch.channels_last)
+            if direct:
+                main = torch.cuda.current_stream(x.device)
+                side = _SIDE.stream(x.device)
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    conv2d_wgrad(gy, x, w.shape, stride, pad, out=w.grad, accumulate=True)
+                _SIDE.pending.append((gy, x))
+                _SIDE.dirty.add(x.device)
+            else:
+                gw = conv2d_wgrad(gy, x, w.shape, stride, pad)
+            need_w = False
+        if need_x and dgrad_supported(x.shape, w.shape, stride, pad):
+            gx = conv2d_dgrad(gy, w, x.shape, stride, pad)
             need_x = False
         if need_x or need_w:
-            gx2, gw, _ = torch.ops.aten.convolution_backward(
+            gx2, gw2, _ = torch.ops.aten.convolution_backward(
                 gy, x, w, None, [stride, stride], [pad, pad], [1, 1], False, [0, 0], 1, [need_x, need_w, False])
-            if need_x:
-                gx = gx2
+            gx = gx2 if need_x else gx
+            gw = gw2 if need_w else gw
         return gx, gw, None, None
 
 

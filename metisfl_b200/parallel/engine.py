@@ -84,6 +84,7 @@ class EngineConfig:
     staging_slots: int = 0               # extra slots per rank for models of off-box learners (unpacked by K12)
     executor_rank: int = 0               # asynchronous rules: the GPU that owns the fp32 rolling state and folds
     fold_blocks: int = 64                # CTAs of one asynchronous fold (it shares the executor's GPU with training)
+    standalone: bool = False             # ignore an initialised torch.distributed job: this engine is its own world
     direct_install: Optional[bool] = None  # train in place in the community buffer (one learner per GPU, synchronous
                                            # rules); False keeps a separate working copy (service path: evaluation of
                                            # version v overlaps training from version v)
@@ -96,7 +97,7 @@ class FederationEngine:
                  loss_fn: Callable = cross_entropy_loss, device=None, group=None,
                  examples_per_learner: Optional[Sequence[int]] = None):
         self.cfg = cfg = cfg or EngineConfig()
-        self.fabric = Fabric(device, group)
+        self.fabric = Fabric(device, group, standalone=cfg.standalone)
         self.device = self.fabric.device
         self.rank, self.world = self.fabric.rank, self.fabric.world
         self.k = cfg.learners_per_gpu

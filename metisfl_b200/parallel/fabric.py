@@ -43,9 +43,10 @@ class SymmetricBuffer:
 
 
 class Fabric:
-    def __init__(self, device=None, group=None):
+    def __init__(self, device=None, group=None, standalone: bool = False):
         self.group = group
-        self.distributed = dist.is_available() and dist.is_initialized()
+        # standalone: a world-1 fabric inside a process that is part of a larger job (oracles, evaluation copies)
+        self.distributed = dist.is_available() and dist.is_initialized() and not standalone
         self.rank = dist.get_rank(group) if self.distributed else 0
         self.world = dist.get_world_size(group) if self.distributed else 1
         if device is None:

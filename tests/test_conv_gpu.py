@@ -43,6 +43,34 @@ def test_conv_autograd_matches_reference(n, c, h, w, k, r, stride, pad):
     torch.testing.assert_close(wt.grad.float(), wr.grad, atol=2e-1, rtol=5e-2)
 
 
+@pytest.mark.parametrize("n,c,h,w,k,r,stride,pad", SHAPES[:8] + [(128, 64, 32, 32, 64, 3, 1, 1), (16, 256, 8, 8, 512, 3, 2, 1)])
+def test_conv_dgrad_and_wgrad_kernels_match_reference(n, c, h, w, k, r, stride, pad):
+    """The gradient kernels by themselves (no autograd): dgrad incl. stride 2 through the parity classes, wgrad through
+    split-K + TMA reduce-add, with and without accumulation; called twice to check the workspace comes back zeroed."""
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(n + c + k + r)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, r, r, generator=g) / (c * r * r) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last)
+    xr, wr = x.detach().float().requires_grad_(), wt.detach().float().requires_grad_()
+    yr = F.conv2d(xr, wr, None, stride, pad)
+    gy = (torch.randn(yr.shape, generator=g) / 4).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    yr.backward(gy.float())
+    assert conv.dgrad_supported(x.shape, wt.shape, stride, pad)
+    for _ in range(2):
+        gx = conv.conv2d_dgrad(gy, wt, x.shape, stride, pad)
+        assert gx.is_contiguous(memory_format=torch.channels_last)
+        err = (gx.float() - xr.grad).norm() / xr.grad.norm().clamp_min(1e-6)
+        assert err < 1e-2, float(err)
+        gw = conv.conv2d_wgrad(gy, x, wt.shape, stride, pad)
+        err = (gw.float() - wr.grad).norm() / wr.grad.norm().clamp_min(1e-6)
+        assert err < 1e-2, float(err)
+    acc = wt.detach().clone()
+    conv.conv2d_wgrad(gy, x, wt.shape, stride, pad, out=acc, accumulate=True)
+    want = wt.float() + wr.grad
+    assert (acc.float() - want).norm() / want.norm() < 1e-2
+
+
 def test_resnet18_with_b200_conv_tracks_cudnn():
     from metisfl_b200.models.zoo import ResNet18
     from metisfl_b200.ops import conv

@@ -33,7 +33,8 @@ def _final_model(snapshot_dir):
 
 def _run(tmp_path, tag, fabric, monkeypatch, n_learners=1, launcher="inprocess", rule="FedAvg", rounds=3,
          protocol=None):
-    d = _env(**{"GlobalModelConfig.AggregationRule.Name": rule, "TerminationSignals.FederationRounds": rounds})
+    d = _env(**{"GlobalModelConfig.AggregationRule.Name": rule, "TerminationSignals.FederationRounds": rounds,
+                "TerminationSignals.ExecutionCutoffTimeMins": 3})
     fe = d["FederationEnvironment"]
     fe["Learners"] = fe["Learners"][:n_learners]
     fe["DeviceFabric"] = fabric
@@ -119,7 +120,8 @@ def _resnet_recipe(n, seed):
 def _gpu_session(tmp_path, tag, monkeypatch, fabric, world, model, recipe_fn, rule="FedAvg", protocol=None, rounds=3,
                  batch=32, n=64):
     d = _env(**{"GlobalModelConfig.AggregationRule.Name": rule, "TerminationSignals.FederationRounds": rounds,
-                "LocalModelConfig.BatchSize": batch, "LocalModelConfig.LocalEpochs": 1})
+                "LocalModelConfig.BatchSize": batch, "LocalModelConfig.LocalEpochs": 1,
+                "TerminationSignals.ExecutionCutoffTimeMins": 2})
     fe = d["FederationEnvironment"]
     base = fe["Learners"][0]
     import copy
@@ -200,9 +202,11 @@ def test_multi_gpu_fabric_through_driver_session(tmp_path, monkeypatch, world, r
     stats, snap = _gpu_session(tmp_path, f"w{world}", monkeypatch, True, world, FashionMnistMLP,
                                lambda n, seed: _recipe(n, seed), rule=rule, protocol=protocol, batch=32, n=128)
     c = _counters(stats)
-    assert c["model_bytes_received"] == 0 and c["fabric_learners"] == world and c["aggregation_failures"] == 0
-    model, it = _bf16_model(snap)
-    assert it >= 2 and all(torch.isfinite(v).all() for v in model.values())
+    logs = ""
     for r in range(world):
         log = open(os.path.join(str(tmp_path / f"w_w{world}"), f"learner{r}.log"), errors="replace").read()
+        logs += f"\n--- learner{r}.log ---\n" + log[-2500:]
         assert "Traceback" not in log, log[-3000:]
+    assert c["model_bytes_received"] == 0 and c["fabric_learners"] == world and c["aggregation_failures"] == 0, logs
+    model, it = _bf16_model(snap)
+    assert it >= 2 and all(torch.isfinite(v).all() for v in model.values()), logs

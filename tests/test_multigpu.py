@@ -188,7 +188,7 @@ for rule in ("FedAsync", "FedRec"):
     ok = True
     if rank == 0:
         ce = FederationEngine(FashionMnistMLP, EngineConfig(learners_per_gpu=world * k, model_dtype=torch.float32, rule=rule,
-                              optimizer=OptimHyper("VanillaSGD", lr=0.05)), device="cpu")
+                              optimizer=OptimHyper("VanillaSGD", lr=0.05), standalone=True), device="cpu")
         cs = AsyncFederation(ce, durations, lambda gl, n: [(X[gl], Y[gl])])
         cs.run(6 * world * k)
         ref = torch.cat([v.float().flatten() for v in ce.community_state_dict().values()])
