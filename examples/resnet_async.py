@@ -31,11 +31,25 @@ pool = [(torch.randn(a.batch, 3, 32, 32, generator=g).to(torch.bfloat16).contigu
 # heterogeneous speeds: task durations spread over a 4x range, deterministic and identical on every rank
 durations = [1.0 + 3.0 * ((i * 37) % L) / max(1, L - 1) for i in range(L)]
 sim = AsyncFederation(eng, durations, lambda gl, n: [pool[(gl + n + s) % len(pool)] for s in range(a.local_steps)])
-sim.run(8)  # warm-up (CUDA graph capture, cuDNN autotune)
+sim.run(max(8, L))  # warm-up (CUDA graph capture, cuDNN autotune, every learner has folded once)
+eng.sync_folds()
 stats = {}
-ms = device_time_ms(lambda: stats.update(sim.run(a.updates)), dev, world)
+
+
+def timed():
+    stats.update(sim.run(a.updates))
+    if eng.fold_stream is not None:  # the executor's folds run on their own stream: the clock stops after the last one
+        torch.cuda.current_stream(dev).wait_stream(eng.fold_stream)
+
+
+ms = device_time_ms(timed, dev, world)
+eng.sync_folds()
+health = eng.async_health()
 finish(rank, world, {
     "config": "#3 ResNet-18 async", "rule": a.rule, "learners": L, "gpus": world, "community_updates": a.updates,
     "ms_per_update": ms / a.updates, "updates_per_s": a.updates / (ms * 1e-3),
     "aggregated_params_per_s": a.updates * eng.layout.num_params / (ms * 1e-3),
-    "mean_staleness": stats.get("mean_staleness"), "max_staleness": stats.get("max_staleness")}, engine=eng)
+    "mean_staleness": stats.get("mean_staleness"), "max_staleness": stats.get("max_staleness"),
+    "local_steps": a.local_steps, "batch": a.batch, "executor_health": health,
+    "mode": "one-sided folds by the executor GPU (K3), multicast push" if eng.community.mc_ptr else
+            "one-sided folds by the executor GPU (K3), peer stores"}, engine=eng)
