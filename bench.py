@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--seq-len", type=int, default=1024)
     ap.add_argument("--learners-per-gpu", type=int, default=1)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--own-conv", action="store_true", help="convolutions on the hand-written kernels instead of cuDNN")
     ap.add_argument("--no-stock", action="store_true", help="skip the stock PyTorch/cuDNN + NCCL arm (vs_baseline)")
     ap.add_argument("--no-service", action="store_true", help="skip the DriverSession/gRPC sub-record (1 GPU only)")
     return ap.parse_args()
@@ -123,7 +124,7 @@ def main():
     torch.backends.cudnn.benchmark = True
     cfg = EngineConfig(learners_per_gpu=args.learners_per_gpu, model_dtype=torch.bfloat16,
                        optimizer=OptimHyper("MomentumSGD", lr=0.02, momentum=0.9), rule="FedAvg",
-                       scaling="NumTrainingExamples", use_cuda_graph=not args.no_graph)
+                       scaling="NumTrainingExamples", use_cuda_graph=not args.no_graph, own_conv=args.own_conv)
     B, S = args.batch, args.local_steps
     if args.model == "resnet18":
         factory, loss_fn = zoo.ResNet18, None
@@ -314,6 +315,7 @@ def main():
                        "batch_per_learner": B, "seq_len": args.seq_len if args.model.startswith("gpt2") else None,
                        "parallelism": f"fed-dp{world}", "optimizer": "MomentumSGD(fused K2)",
                        "cuda_graph": not args.no_graph,
+                       "convolutions": "own tcgen05 kernels (K11/K11s/K15)" if args.own_conv else "cuDNN",
                        "l2": f"no flush: per-round working set (peak {peak_mb:.0f} MiB allocated) exceeds the 126 MB L2"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "params/s", "ms_per_step": e2e_ms,

@@ -343,7 +343,8 @@ void Controller::AfterBarrier(const std::vector<std::string>& to_schedule, const
         std::to_string(global_iteration_));
     aggregator_->Reset();
     store_->ResetState();
-    ++aggregation_failures_;
+    // "SKIP:" = the dispatcher declined on purpose (the device fabric is dissolving because learners are leaving)
+    if (std::string(e.what()).find("SKIP:") == std::string::npos) ++aggregation_failures_;
     pending_ref_.clear();
     model.reset();
   }

@@ -49,6 +49,11 @@ struct Params {
   int box_bytes;         // bytes one halo TMA delivers: (TH + 2) * Wp * 128
   int tiles_per_img, num_m_tiles, n_tiles;
   int a_stages;          // depth of the halo ring (2..kMaxAStages)
+  // data-gradient mode: the halo tile is dY (C = its channels, the reduction), K = channels of dX; the filter tensor
+  // is the forward one, read MN-major ([64 k, 64 c] boxes: reduction rows, output channels contiguous) and with the
+  // taps mirrored, so no transformed copy of the filters is ever made
+  int dgrad;
+  int w_cols_per_tap;    // column pitch of one tap in the [rows, 9 * cols] filter matrix
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2,
@@ -106,7 +111,11 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       mbar_expect_tx(w_bar, (uint32_t)(9 * cblocks * kBTileBytes));
       for (int cb = 0; cb < cblocks; ++cb)
         for (int tap = 0; tap < 9; ++tap)
-          tma_load_2d(filt + (size_t)(cb * 9 + tap) * kBTileBytes, &tmap_w, w_bar, tap * p.C + cb * kBlockK, n0);
+          if (p.dgrad)  // tile for halo tap `tap` = forward tap 8 - tap, rows = reduction block cb, columns = n0..n0+63
+            tma_load_2d(filt + (size_t)(cb * 9 + tap) * kBTileBytes, &tmap_w, w_bar, (8 - tap) * p.w_cols_per_tap + n0,
+                        cb * kBlockK);
+          else
+            tma_load_2d(filt + (size_t)(cb * 9 + tap) * kBTileBytes, &tmap_w, w_bar, tap * p.C + cb * kBlockK, n0);
       uint32_t it = 0;
       for (int mt = m_first; mt < p.num_m_tiles; mt += m_step) {
         const int img = mt / p.tiles_per_img, h0 = (mt % p.tiles_per_img) * p.TH;
@@ -119,7 +128,8 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       }
     }
   } else if (warp == 1) {  // ===== MMA issuer: the whole warp runs the loop, one elected lane issues =====
-    const uint32_t idesc = make_idesc<kBN>();
+    const uint32_t idesc = make_idesc<kBN>() | (p.dgrad ? (1u << 16) : 0u);  // B is MN-major in data-gradient mode
+    const uint64_t b_kstep = p.dgrad ? 128 : 2;  // 16 reduction rows of 128 B vs 32 B inside the swizzle row
     mbar_wait(w_bar, 0);
     uint32_t it = 0, t = 0;
     for (int mt = m_first; mt < p.num_m_tiles; mt += m_step, ++t) {
@@ -142,7 +152,7 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
           for (int q = 1; q < 36; ++q) {  // q = tap * 4 + k: 9 taps x 4 K-steps of 16 channels, straight-line
             const int tap = q >> 2, k = q & 3, r = tap / 3, sx = tap - 3 * r;
             umma_f16_c<true>(tmem_d, a0 + (uint64_t)r * row + (uint64_t)sx * px + (uint64_t)(k * 2),
-                             b0 + (uint64_t)(tap * (kBTileBytes >> 4) + k * 2), idesc);
+                             b0 + (uint64_t)(tap * (kBTileBytes >> 4)) + (uint64_t)k * b_kstep, idesc);
           }
           umma_commit(a_empty + s);
         }
@@ -237,8 +247,23 @@ extern "C" int mfl_conv3x3_supported(int n, int h, int wd, int c, int k) {
 
 // y[N,H,W,K] = conv3x3(x[N,H,W,C], w[K,3,3,C]), stride 1, zero padding 1, NHWC bf16.
 // stats (optional): [2][K] fp32, ADDED to: per-channel sum and sum of squares of the stored outputs.
+static int conv3x3_impl(void* y, const void* x, const void* w, float* stats, int n, int h, int wd, int c, int k,
+                        int dgrad, void* stream);
+
 extern "C" int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* stats, int n, int h, int wd, int c, int k,
                                 void* stream) {
+  return conv3x3_impl(y, x, w, stats, n, h, wd, c, k, 0, stream);
+}
+
+// dX[N,H,W,C] of y = conv3x3(x, w[K,3,3,C]) (stride 1, padding 1) from dY[N,H,W,K]: the same kernel with dY as the halo
+// operand and the forward filters read MN-major with mirrored taps.  Shapes: mfl_conv3x3_supported(n, h, w, K, C).
+extern "C" int mfl_conv3x3_dgrad_bf16(void* dx, const void* dy, const void* w, int n, int h, int wd, int c, int k,
+                                      void* stream) {
+  return conv3x3_impl(dx, dy, w, nullptr, n, h, wd, /*reduction channels=*/k, /*output channels=*/c, 1, stream);
+}
+
+static int conv3x3_impl(void* y, const void* x, const void* w, float* stats, int n, int h, int wd, int c, int k,
+                        int dgrad, void* stream) {
   using namespace mfl;
   using namespace mfl::conv3;
   MFL_ARG(y && x && w, "conv3x3: null operand");
@@ -251,6 +276,8 @@ extern "C" int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* st
   p.y = static_cast<__nv_bfloat16*>(y);
   p.stats = stats;
   p.N = n; p.H = h; p.W = wd; p.C = c; p.K = k;
+  p.dgrad = dgrad;
+  p.w_cols_per_tap = dgrad ? k : c;   // the filter matrix is always the forward one: [K_fwd, 9 * C_fwd]
   p.Wp = wd + 2;
   p.TH = std::max(1, std::min(h, 128 / p.Wp));
   p.box_bytes = (p.TH + 2) * p.Wp * 128;
@@ -276,9 +303,10 @@ extern "C" int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* st
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     MFL_ARG(r == CUDA_SUCCESS, "conv3x3: activation tensor map failed with CUresult %d", (int)r);
   }
-  {  // filters as a [K, 9 * C] row-major matrix, box {64, 64}
-    cuuint64_t dims[2] = {(cuuint64_t)9 * c, (cuuint64_t)k};
-    cuuint64_t strides[1] = {(cuuint64_t)9 * c * 2};
+  {  // filters as a [K, 9 * C] row-major matrix (forward orientation), box {64, 64}
+    const int wc = dgrad ? k : c, wk = dgrad ? c : k;
+    cuuint64_t dims[2] = {(cuuint64_t)9 * wc, (cuuint64_t)wk};
+    cuuint64_t strides[1] = {(cuuint64_t)9 * wc * 2};
     cuuint32_t box[2] = {64, (cuuint32_t)kBN};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = fn(&tw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w), dims, strides, box, estr,

@@ -69,12 +69,16 @@ struct Epilogue {
   int32_t ntaps, kb_per_tap;
   int8_t tap_ow[16], tap_oh[16], tap_w[16];   // im2col offsets of each tap and the filter tap it multiplies with
   int32_t c_in;                               // mode 2: channels of dX = column pitch of one filter tap in W
+  // mode 2 with stride 2: the (h mod 2, w mod 2) classes of dX are independent problems over the same dY; one launch
+  // walks all of them (work item = class * tiles + tile); class q uses taps [cls_tap0[q], cls_tap0[q] + cls_ntaps[q])
+  int32_t n_cls;
+  int8_t cls_tap0[4], cls_ntaps[4], cls_ph[4], cls_pw[4];
   // split-K: the k-blocks of a tile are divided among `splits` CTAs, each adds its fp32 partial tile into a
   // zero-initialised workspace with TMA reduce-add stores (tmap_c is the workspace map); a finalize kernel
   // converts it and re-zeroes the workspace
   int32_t splits, kb_per_split;
-  // 4-D store (mode 2, stride 2): the 32 rows of an epilogue slab are a {64 c, bw, bh, bn} box of the strided
-  // parity-class view of dX
+  // strided store (mode 2, stride 2): dX is seen as {C, w mod 2, W/2, h mod 2, N*H/2}; the 32 rows of an epilogue
+  // slab are a {64 c, 1, bw, 1, bh} box of it
   int32_t store4d, box_w, box_h, box_n, cls_w, cls_h;
 };
 
@@ -82,9 +86,10 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, const 
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
                ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
 }
-__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2, int c3) {
-  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
-               ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2, int c3,
+                                             int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+               ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
 }
 
 template <int ACT> __device__ __forceinline__ float apply_act(float x) {
@@ -118,8 +123,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   const int num_kb = (ep.K + kBlockK - 1) / kBlockK;
   // work item w = tile * splits + split; a split owns k-blocks [split * kb_per_split, +kb_per_split) (clipped)
   const int splits = ep.splits > 1 ? ep.splits : 1;
-  const int num_work = num_tiles * splits;
-  const int kbps = splits > 1 ? ep.kb_per_split : num_kb;
+  const int n_cls = ep.n_cls > 1 ? ep.n_cls : 1;
+  const int work_per_cls = num_tiles * splits;
+  const int num_work = work_per_cls * n_cls;
+  const int kbps = splits > 1 ? ep.kb_per_split : (1 << 30);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_a) : "memory");
@@ -148,9 +155,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       uint32_t it = 0;  // k-block counter across all tiles of this CTA: the ring never drains
       const int ohw = ep.out_h * ep.out_w;
       for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
-        const int tile = w / splits, split = w - tile * splits;
+        const int cls = w / work_per_cls, wi = w - cls * work_per_cls;
+        const int tile = wi / splits, split = wi - tile * splits;
         const int m0 = (tile / tiles_n) * kBlockM, n0 = (tile % tiles_n) * BN;
-        const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+        const int nkb = ep.n_cls ? (int)ep.cls_ntaps[cls] * ep.kb_per_tap : num_kb;
+        const int kb0 = split * kbps, kb1 = min(nkb, kb0 + kbps);
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % kStages;
           const uint32_t phase = (it / kStages) & 1;
@@ -179,7 +188,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
           }
           mbar_expect_tx(full_bar + s, C::kStageBytes);
           if (ep.mode == 2) {  // data gradient: A = im2col(dY) for tap kb / kb_per_tap, B = W tap, MN-major
-            const int tap = kb / ep.kb_per_tap, kk = kb - tap * ep.kb_per_tap;
+            const int tl = kb / ep.kb_per_tap, kk = kb - tl * ep.kb_per_tap;
+            const int tap = (ep.n_cls ? (int)ep.cls_tap0[cls] : 0) + tl;
             const int img = m0 / ohw, rem = m0 - img * ohw;
             const int oh = rem / ep.out_w, ow = rem - oh * ep.out_w;
             tma_load_im2col_4d(a_dst, &tmap_a, full_bar + s, kk * kBlockK, ow - ep.pad, oh - ep.pad, img,
@@ -223,8 +233,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     const uint32_t a_lbo = ep.a_mn ? 512 : 1, b_lbo = ep.b_mn ? 512 : 1;
     uint32_t it = 0, t = 0;
     for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++t) {
-      const int split = w % splits;
-      const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+      const int cls = w / work_per_cls, split = (w - cls * work_per_cls) % splits;
+      const int nkb = ep.n_cls ? (int)ep.cls_ntaps[cls] * ep.kb_per_tap : num_kb;
+      const int kb0 = split * kbps, kb1 = min(nkb, kb0 + kbps);
       const uint32_t buf = t & 1, use = t >> 1;
       mbar_wait(tmem_empty_bar + buf, (use & 1) ^ 1);  // epilogue has drained this accumulator
       tcgen05_fence_after();
@@ -254,7 +265,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     const int wq = warp & 3;  // TMEM lane quarter this warp may access
     uint32_t t = 0;
     for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++t) {
-      const int tile = w / splits;
+      const int cls = w / work_per_cls;
+      const int tile = (w - cls * work_per_cls) / splits;
       const int m0 = (tile / tiles_n) * kBlockM, n0 = (tile % tiles_n) * BN;
       const uint32_t buf = t & 1, use = t >> 1;
       mbar_wait(tmem_full_bar + buf, use & 1);
@@ -305,11 +317,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             if (splits > 1) {
               tma_reduce_add_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);  // fp32 partial tile += into the workspace
             } else if (ep.store4d) {
-              // rows m0 + wq*32 .. +31 of the parity-class pixel space = a {bw, bh, bn} box of the strided view of dX
+              // rows m0 + wq*32 .. +31 of the class's pixel grid = a {bw, bh} box of the strided view of dX
               const int r0 = m0 + wq * 32;
-              const int per_img = ep.cls_w * ep.cls_h;
-              const int img = r0 / per_img, rem = r0 - img * per_img;
-              tma_store_4d(&tmap_c, slab, n0 + c, rem % ep.cls_w, rem / ep.cls_w, img);
+              tma_store_5d(&tmap_c, slab, n0 + c, (int)ep.cls_pw[cls], r0 % ep.cls_w, (int)ep.cls_ph[cls], r0 / ep.cls_w);
             } else {
               tma_store_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);
             }
@@ -402,7 +412,7 @@ namespace mfl { namespace gemm {
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const Epilogue& ep, int bn,
                        int act, bool c32, cudaStream_t st) {
   const int tiles = ((ep.N + bn - 1) / bn) * ((ep.M + kBlockM - 1) / kBlockM);
-  const int grid = std::min(tiles * std::max(1, (int)ep.splits), sm_count());
+  const int grid = std::min(tiles * std::max(1, (int)ep.splits) * std::max(1, (int)ep.n_cls), sm_count());
   int rc = 0;
 #define MFL_GEMM_LAUNCH(BN_, ACT_, F32_)                                                                          \
   do {                                                                                                            \
@@ -510,8 +520,35 @@ static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int6
 // Replaces the framework convolutions under the learners' training loop (keras_model_ops.py:156).  The A
 // operand is never materialised: the TMA unit gathers 128 output pixels x 64 channels per filter tap
 // straight into the swizzled shared-memory tile the tensor core reads (im2col tensor map).
-extern "C" int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, int r,
-                                     int s, int stride, int pad, void* stream) {
+namespace mfl { namespace gemm {
+__global__ void splitk_finalize_kernel(float* __restrict__ ws, __nv_bfloat16* __restrict__ out, int rows, int cols,
+                                       int64_t ld, int accumulate);
+// Split the reduction of a convolution whose output has too few tiles to fill the machine (the 8x8 and 4x4 layers
+// of ResNet-18 give 32-64 tiles for 148 SMs): each (tile, split) work item adds its fp32 partial into `ws`.
+static void plan_splits(Epilogue& ep, int bn, const float* ws, size_t ws_bytes) {
+  const int tiles = ((ep.N + bn - 1) / bn) * ((ep.M + kBlockM - 1) / kBlockM);
+  const int num_kb = (ep.K + kBlockK - 1) / kBlockK;
+  ep.splits = 1;
+  ep.kb_per_split = num_kb;
+  if (!ws || (size_t)ep.M * ep.N * sizeof(float) > ws_bytes || tiles * 5 >= sm_count() * 4 || ep.N % 8 != 0) return;
+  int splits = std::min(num_kb / 4, (sm_count() + tiles - 1) / tiles);
+  if (splits < 2) return;
+  ep.kb_per_split = (num_kb + splits - 1) / splits;
+  ep.splits = (num_kb + ep.kb_per_split - 1) / ep.kb_per_split;
+  if (ep.splits < 2) { ep.splits = 1; ep.kb_per_split = num_kb; }
+}
+static int finalize_splits(const Epilogue& ep, float* ws, void* out, int64_t ld, cudaStream_t st) {
+  const int64_t vecs = (int64_t)ep.M * ep.N / 8;
+  const int blocks = (int)std::min<int64_t>((vecs + 255) / 256, (int64_t)sm_count() * 4);
+  splitk_finalize_kernel<<<blocks, 256, 0, st>>>(ws, static_cast<__nv_bfloat16*>(out), ep.M, ep.N, ld, 0);
+  return check(cudaGetLastError(), "splitk_finalize_kernel launch");
+}
+}}  // namespace mfl::gemm
+
+// ws / ws_bytes: optional zero-initialised fp32 scratch (handed back zeroed) that lets small-output layers split
+// their reduction over more SMs; pass NULL / 0 to run without it.
+extern "C" int mfl_conv2d_fprop_bf16_ws(void* y, const void* x, const void* w, float* ws, size_t ws_bytes, int n, int h,
+                                        int wd, int c, int k, int r, int s, int stride, int pad, void* stream) {
   using namespace mfl::gemm;
   MFL_ARG(y && x && w && n > 0 && h > 0 && wd > 0, "conv2d: null operand or empty shape");
   MFL_ARG(c % 64 == 0 && k % 8 == 0, "conv2d: needs C %% 64 == 0 and K %% 8 == 0 (got C=%d K=%d)", c, k);
@@ -535,11 +572,23 @@ extern "C" int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int 
   const int m = n * oh * ow, kk = r * s * c;
   const int bn = k > 128 ? 256 : (k > 64 ? 128 : 64);
   if (int rc = make_map(&tb, w, k, kk, kk, bn)) return rc;
-  if (int rc = make_map(&tc, y, m, k, k, 32, false)) return rc;
   Epilogue ep{y, nullptr, k, m, k, kk, 0, 0, 0, 1, 1, oh, ow, stride, pad, s, c / 64};
-  return launch_gemm(ta, tb, tc, ep, bn, 0, false, (cudaStream_t)stream);
+  plan_splits(ep, bn, ws, ws_bytes);
+  const bool split = ep.splits > 1;
+  if (split) {
+    ep.c = ws; ep.c_fp32 = 1;
+    if (int rc = make_map(&tc, ws, m, k, k, 32, true)) return rc;
+  } else {
+    if (int rc = make_map(&tc, y, m, k, k, 32, false)) return rc;
+  }
+  if (int rc = launch_gemm(ta, tb, tc, ep, bn, 0, split, (cudaStream_t)stream)) return rc;
+  return split ? finalize_splits(ep, ws, y, k, (cudaStream_t)stream) : 0;
 }
 
+extern "C" int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, int r,
+                                     int s, int stride, int pad, void* stream) {
+  return mfl_conv2d_fprop_bf16_ws(y, x, w, nullptr, 0, n, h, wd, c, k, r, s, stride, pad, stream);
+}
 
 // =====================================================================================================================
 // K11 gradients: data gradient (stride 1 and, by stride-parity classes, stride 2) and weight gradient (split-K over the
@@ -549,8 +598,8 @@ extern "C" int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int 
 namespace mfl { namespace gemm {
 
 // ws (fp32 [rows, cols], the split-K workspace) -> out (bf16, row pitch ld), optionally accumulating; re-zeroes ws
-__global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict__ ws, __nv_bfloat16* __restrict__ out,
-                                                              int rows, int cols, int64_t ld, int accumulate) {
+__global__ void splitk_finalize_kernel(float* __restrict__ ws, __nv_bfloat16* __restrict__ out, int rows, int cols,
+                                       int64_t ld, int accumulate) {
   const int64_t vec_per_row = cols / 8;
   const int64_t total = (int64_t)rows * vec_per_row;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -589,16 +638,16 @@ static int make_im2col_map(CUtensorMap* map, const void* base, int n, int h, int
 }
 
 // strided parity-class view of dX for the 4-D epilogue store: {C, W/s, H/s, N}, box {64, bw, bh, bn}
-static int make_store4d_map(CUtensorMap* map, void* base, int n, int h, int wd, int c, int stride, int cls_w, int cls_h,
-                            int bw, int bh, int bnn) {
+// strided view of dX for the stride-2 epilogue store: {C, w mod 2, W/2, h mod 2, N*H/2}, box {64, 1, bw, 1, bh}
+static int make_store5d_map(CUtensorMap* map, void* base, int n, int h, int wd, int c, int bw, int bh) {
   bind_context();
   EncodeTiledFn fn = encode_fn();
   MFL_ARG(fn != nullptr, "conv2d: cuTensorMapEncodeTiled is not available from this driver");
-  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)cls_w, (cuuint64_t)cls_h, (cuuint64_t)n};
-  cuuint64_t strides[3] = {(cuuint64_t)stride * c * 2, (cuuint64_t)stride * wd * c * 2, (cuuint64_t)h * wd * c * 2};
-  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bnn};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  cuuint64_t dims[5] = {(cuuint64_t)c, 2, (cuuint64_t)wd / 2, 2, (cuuint64_t)n * h / 2};
+  cuuint64_t strides[4] = {(cuuint64_t)c * 2, (cuuint64_t)2 * c * 2, (cuuint64_t)wd * c * 2, (cuuint64_t)2 * wd * c * 2};
+  cuuint32_t box[5] = {64, 1, (cuuint32_t)bw, 1, (cuuint32_t)bh};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MFL_ARG(r == CUDA_SUCCESS, "conv2d dgrad: strided output tensor map failed with CUresult %d", (int)r);
   return 0;
@@ -649,8 +698,14 @@ extern "C" int mfl_conv2d_wgrad_bf16(void* dw, const void* dy, const void* x, fl
 // stride-1 correlation of dY with the taps of matching parity (for 3x3 / pad 1: 1, 2, 2 and 4 taps: no wasted math) -
 // written through a strided 4-D tensor map.  NHWC bf16; K % 64 == 0, C % 8 == 0; stride 2 needs H/2 and W/2 powers of
 // two (<= 32) so that 32-row store slabs tile the class grid.
+extern "C" int mfl_conv2d_dgrad_bf16_ws(void* dx, const void* dy, const void* w, float* ws, size_t ws_bytes, int n,
+                                        int h, int wd, int c, int k, int r, int s, int stride, int pad, void* stream);
 extern "C" int mfl_conv2d_dgrad_bf16(void* dx, const void* dy, const void* w, int n, int h, int wd, int c, int k, int r,
                                      int s, int stride, int pad, void* stream) {
+  return mfl_conv2d_dgrad_bf16_ws(dx, dy, w, nullptr, 0, n, h, wd, c, k, r, s, stride, pad, stream);
+}
+extern "C" int mfl_conv2d_dgrad_bf16_ws(void* dx, const void* dy, const void* w, float* ws, size_t ws_bytes, int n,
+                                        int h, int wd, int c, int k, int r, int s, int stride, int pad, void* stream) {
   using namespace mfl::gemm;
   MFL_ARG(dx && dy && w && n > 0 && h > 0 && wd > 0, "conv2d dgrad: null operand or empty shape");
   MFL_ARG(k % 64 == 0 && c % 8 == 0, "conv2d dgrad: needs K %% 64 == 0 and C %% 8 == 0 (got C=%d K=%d)", c, k);
@@ -665,51 +720,68 @@ extern "C" int mfl_conv2d_dgrad_bf16(void* dx, const void* dy, const void* w, in
   if (stride == 2) {
     MFL_ARG(h % 2 == 0 && wd % 2 == 0 && h / 2 == oh && wd / 2 == ow && pow2(oh) && pow2(ow) && c % 64 == 0,
             "conv2d dgrad: stride 2 needs even H, W with H/2, W/2 powers of two and C %% 64 == 0");
-    MFL_CUDA(cudaMemsetAsync(dx, 0, (size_t)n * h * wd * c * 2, st));  // classes without a tap (1x1 filters) stay zero
+    if (r * s < 4)  // fewer taps than classes (1x1 filters): the untouched classes of dX are zero
+      MFL_CUDA(cudaMemsetAsync(dx, 0, (size_t)n * h * wd * c * 2, st));
   }
-  for (int ph = 0; ph < stride; ++ph) {
+  // tap tables of the stride-parity classes (one class when stride == 1), heaviest class first
+  struct Cls { int ph, pw, nt, dmin, dmax; int th[16], tw[16], tf[16]; };
+  Cls cls[4];
+  int ncls = 0;
+  for (int ph = 0; ph < stride; ++ph)
     for (int pw = 0; pw < stride; ++pw) {
-      Epilogue ep{};
-      int dmin_h = 1 << 20, dmax_h = -(1 << 20), dmin_w = 1 << 20, dmax_w = -(1 << 20);
-      int th[16], tw_[16], tf[16], nt = 0;
+      Cls q{}; q.ph = ph; q.pw = pw; q.dmin = 1 << 20; q.dmax = -(1 << 20);
       for (int rr = 0; rr < r; ++rr) {
         if ((ph + pad - rr) % stride != 0) continue;
-        const int dh = (ph + pad - rr) / stride;   // may be negative: C division is exact here
+        const int dh = (ph + pad - rr) / stride;   // exact division, may be negative
         for (int ss = 0; ss < s; ++ss) {
           if ((pw + pad - ss) % stride != 0) continue;
           const int dw_ = (pw + pad - ss) / stride;
-          th[nt] = dh; tw_[nt] = dw_; tf[nt] = rr * s + ss; ++nt;
-          dmin_h = std::min(dmin_h, dh); dmax_h = std::max(dmax_h, dh);
-          dmin_w = std::min(dmin_w, dw_); dmax_w = std::max(dmax_w, dw_);
+          q.th[q.nt] = dh; q.tw[q.nt] = dw_; q.tf[q.nt] = rr * s + ss; ++q.nt;
+          q.dmin = std::min(q.dmin, std::min(dh, dw_)); q.dmax = std::max(q.dmax, std::max(dh, dw_));
         }
       }
-      if (nt == 0) continue;
-      const int cls_h = (h - ph + stride - 1) / stride, cls_w = (wd - pw + stride - 1) / stride;
-      // base pixel of class position (h', w') is (h' + dmin); tap t reads base + (d_t - dmin)
-      ep.mode = 2; ep.ntaps = nt; ep.kb_per_tap = k / 64; ep.c_in = c;
-      for (int t = 0; t < nt; ++t) {
-        ep.tap_oh[t] = (int8_t)(th[t] - dmin_h); ep.tap_ow[t] = (int8_t)(tw_[t] - dmin_w); ep.tap_w[t] = (int8_t)tf[t];
-      }
-      // im2col box: base positions [dmin, dmin + cls - 1] per axis; upper corner = (last base) - (dim - 1) - window + 1 ...
-      // in the driver's convention: #positions = dim + upper - lower - (window - 1), window = dmax - dmin + 1
-      const int win_h = dmax_h - dmin_h + 1, win_w = dmax_w - dmin_w + 1;
-      const int upper_h = cls_h - oh + dmin_h, upper_w = cls_w - ow + dmin_w;
-      (void)win_h; (void)win_w;
-      if (int rc = make_im2col_map(&ta, dy, n, oh, ow, k, dmin_w, dmin_h, upper_w, upper_h, 1, kBlockM)) return rc;
-      ep.c = dx; ep.ldc = c; ep.M = n * cls_h * cls_w; ep.N = c; ep.K = nt * k;
-      ep.c_fp32 = 0; ep.tma_store = 1; ep.a_mn = 0; ep.b_mn = 1;
-      ep.out_h = cls_h; ep.out_w = cls_w; ep.stride = 1; ep.pad = -dmin_h;  // the kernel subtracts `pad` from both axes
-      MFL_ARG(dmin_h == dmin_w, "conv2d dgrad: asymmetric tap windows are not supported");
-      if (stride == 1) {
-        if (int rc = make_map(&tc, dx, ep.M, c, c, 32, false)) return rc;
-      } else {
-        const int bw = std::min(cls_w, 32), bh = std::min(cls_h, 32 / bw), bnn = 32 / (bw * bh);
-        ep.store4d = 1; ep.box_w = bw; ep.box_h = bh; ep.box_n = bnn; ep.cls_w = cls_w; ep.cls_h = cls_h;
-        char* base = static_cast<char*>(dx) + ((size_t)ph * wd + pw) * c * 2;
-        if (int rc = make_store4d_map(&tc, base, n, h, wd, c, stride, cls_w, cls_h, bw, bh, bnn)) return rc;
-      }
-      if (int rc = launch_gemm(ta, tb, tc, ep, bn, 0, false, st)) return rc;
+      if (q.nt) cls[ncls++] = q;
+    }
+  MFL_ARG(ncls >= 1, "conv2d dgrad: no filter tap reaches the input");
+  std::sort(cls, cls + ncls, [](const Cls& a, const Cls& b) { return a.nt > b.nt; });
+  int dmin = cls[0].dmin;
+  for (int q = 1; q < ncls; ++q) dmin = std::min(dmin, cls[q].dmin);
+  const int cls_h = h / stride, cls_w = wd / stride;   // stride 2: H, W even (checked above); stride 1: H, W
+  Epilogue ep{};
+  ep.mode = 2; ep.kb_per_tap = k / 64; ep.c_in = c;
+  int nt_total = 0;
+  for (int q = 0; q < ncls; ++q) {
+    ep.cls_tap0[q] = (int8_t)nt_total; ep.cls_ntaps[q] = (int8_t)cls[q].nt;
+    ep.cls_ph[q] = (int8_t)cls[q].ph; ep.cls_pw[q] = (int8_t)cls[q].pw;
+    for (int t = 0; t < cls[q].nt; ++t, ++nt_total) {
+      MFL_ARG(nt_total < 16, "conv2d dgrad: more than 16 filter taps");
+      // base pixel of class position (h', w') is (h' + dmin, w' + dmin); tap t reads base + (d_t - dmin)
+      ep.tap_oh[nt_total] = (int8_t)(cls[q].th[t] - dmin); ep.tap_ow[nt_total] = (int8_t)(cls[q].tw[t] - dmin);
+      ep.tap_w[nt_total] = (int8_t)cls[q].tf[t];
     }
   }
+  ep.n_cls = ncls; ep.ntaps = nt_total;
+  // im2col box of base positions: [dmin, dmin + cls - 1] per axis -> #positions = dim + upper - lower = cls
+  if (int rc = make_im2col_map(&ta, dy, n, oh, ow, k, dmin, dmin, cls_w - ow + dmin, cls_h - oh + dmin, 1, kBlockM)) return rc;
+  ep.c = dx; ep.ldc = c; ep.M = n * cls_h * cls_w; ep.N = c; ep.K = cls[0].nt * k;  // K of the heaviest class (grid sizing)
+  ep.c_fp32 = 0; ep.tma_store = 1; ep.a_mn = 0; ep.b_mn = 1;
+  ep.out_h = cls_h; ep.out_w = cls_w; ep.stride = 1; ep.pad = -dmin;  // the kernel subtracts `pad` from both axes
+  bool split = false;
+  if (stride == 1) {
+    plan_splits(ep, bn, ws, ws_bytes);
+    split = ep.splits > 1;
+    if (split) {
+      ep.c = ws; ep.c_fp32 = 1;
+      if (int rc = make_map(&tc, ws, ep.M, c, c, 32, true)) return rc;
+    } else if (int rc = make_map(&tc, dx, ep.M, c, c, 32, false)) return rc;
+  } else {
+    const int bw = std::min(cls_w, 32), bh = 32 / bw;
+    MFL_ARG((n * cls_h) % bh == 0, "conv2d dgrad: N * H/2 must be a multiple of %d", bh);
+    ep.store4d = 1; ep.box_w = bw; ep.box_h = bh; ep.cls_w = cls_w; ep.cls_h = cls_h;
+    if (int rc = make_store5d_map(&tc, dx, n, h, wd, c, bw, bh)) return rc;
+  }
+  if (int rc = launch_gemm(ta, tb, tc, ep, bn, 0, split, st)) return rc;
+  if (split)
+    if (int rc = finalize_splits(ep, ws, dx, c, st)) return rc;
   return 0;
 }

@@ -161,6 +161,7 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
                 MetisLogger.warning("heartbeat miss %d/%d for %s: %s", self._missed[lid], self._heartbeat_misses, lid,
                                     getattr(e, "code", lambda: e)())
                 if self._missed[lid] >= self._heartbeat_misses:
+                    self._mark_fabric_dissolving(lid)
                     if self.core.evict_learner(lid, "evicted: heartbeat lost"):
                         evicted.append(lid)
                     self._missed.pop(lid, None)
@@ -299,6 +300,10 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             fabric = next(iter(self._fabrics.values()), None)
         if fabric is None:
             return None
+        if fabric.get("dissolving"):
+            # a member of the fabric has left (shutdown in progress): the fused kernel needs every rank, so there is
+            # nothing to launch any more - the round keeps the previous community model
+            return {"error": "SKIP: device fabric is dissolving (a member left the federation)"}
         try:
             world = fabric["world"]
             pb = learner_pb2.AggregateOnDeviceRequest(
@@ -422,6 +427,7 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         return controller_pb2.JoinFederationResponse(ack=_ack(), learner_id=learner_id, auth_token=token)
 
     def LeaveFederation(self, request, context):
+        self._mark_fabric_dissolving(request.learner_id)  # before the core re-checks the barrier without this learner
         try:
             self.core.remove_learner(request.learner_id, request.auth_token)
         except _core.ControllerError as e:
@@ -433,6 +439,12 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         with self._fabric_lock:
             self._joined.discard(request.learner_id)
         return controller_pb2.LeaveFederationResponse(ack=_ack())
+
+    def _mark_fabric_dissolving(self, learner_id):
+        with self._fabric_lock:
+            member = self._fabric_of.get(learner_id)
+            if member is not None and member[0] in self._fabrics:
+                self._fabrics[member[0]]["dissolving"] = True
 
     def MarkTaskCompleted(self, request, context):
         md = request.task.execution_metadata

@@ -36,8 +36,14 @@ def _bind():
         L.mfl_conv2d_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
         L.mfl_conv3x3_supported.argtypes = [i, i, i, i, i]
         L.mfl_conv3x3_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
+        L.mfl_conv3x3_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
+        L.mfl_conv_stem_supported.argtypes = [i, i]
+        L.mfl_conv_stem_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
+        L.mfl_conv_stem_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, vp]
         L.mfl_conv2d_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, vp]
         L.mfl_conv2d_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        L.mfl_conv2d_fprop_bf16_ws.argtypes = [vp, vp, vp, vp, C.c_size_t, i, i, i, i, i, i, i, i, i, vp]
+        L.mfl_conv2d_dgrad_bf16_ws.argtypes = [vp, vp, vp, vp, C.c_size_t, i, i, i, i, i, i, i, i, i, vp]
         L.mfl_conv2d_wgrad_workspace_bytes.restype = C.c_size_t
         L.mfl_conv2d_wgrad_workspace_bytes.argtypes = [i, i, i, i]
         _BOUND = True
@@ -59,8 +65,10 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int) -> tor
     w = w.contiguous(memory_format=torch.channels_last)
     oh, ow = (h + 2 * pad - r) // stride + 1, (wd + 2 * pad - s) // stride + 1
     y = torch.empty((n, k, oh, ow), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
-    rc = _bind().mfl_conv2d_fprop_bf16(y.data_ptr(), x.data_ptr(), w.data_ptr(), n, h, wd, c, k, r, s, stride, pad,
-                                       _lib.stream_ptr())
+    stream = torch.cuda.current_stream(x.device)
+    ws = _workspace(x.device, 0, stream)
+    rc = _bind().mfl_conv2d_fprop_bf16_ws(y.data_ptr(), x.data_ptr(), w.data_ptr(), ws.data_ptr(), ws.numel() * 4, n, h, wd,
+                                          c, k, r, s, stride, pad, stream.cuda_stream)
     _lib.check(rc, "mfl_conv2d_fprop_bf16")
     return y
 
@@ -112,12 +120,15 @@ def conv2d_dgrad(gy: torch.Tensor, w: torch.Tensor, x_shape, stride: int, pad: i
     gy = gy.contiguous(memory_format=torch.channels_last)
     w = w.contiguous(memory_format=torch.channels_last)
     gx = torch.empty((n, c, h, wd), dtype=torch.bfloat16, device=gy.device, memory_format=torch.channels_last)
-    rc = _bind().mfl_conv2d_dgrad_bf16(gx.data_ptr(), gy.data_ptr(), w.data_ptr(), n, h, wd, c, k, r, s, stride, pad,
-                                       _lib.stream_ptr())
+    stream = torch.cuda.current_stream(gy.device)
+    ws = _workspace(gy.device, 0, stream)
+    rc = _bind().mfl_conv2d_dgrad_bf16_ws(gx.data_ptr(), gy.data_ptr(), w.data_ptr(), ws.data_ptr(), ws.numel() * 4, n, h,
+                                          wd, c, k, r, s, stride, pad, stream.cuda_stream)
     _lib.check(rc, "mfl_conv2d_dgrad_bf16", launches=stride * stride)
     return gx
 
 
+USE_HALO = True   # route 3x3 / stride-1 layers with <= 128 reduction channels to the weight-stationary kernel (K15)
 _WS = {}   # (device, stream id) -> zeroed fp32 split-K workspace, handed back zeroed by every call
 
 
@@ -126,7 +137,7 @@ def _workspace(device, nbytes: int, stream) -> torch.Tensor:
     ws = _WS.get(key)
     if ws is None or ws.numel() * 4 < nbytes:
         with torch.cuda.stream(stream):
-            ws = torch.zeros(max(nbytes // 4, 1 << 20), dtype=torch.float32, device=device)
+            ws = torch.zeros(max(nbytes // 4, 4 << 20), dtype=torch.float32, device=device)  # >= 16 MiB
         _WS[key] = ws
     return ws
 
@@ -151,11 +162,90 @@ def conv2d_wgrad(gy: torch.Tensor, x: torch.Tensor, w_shape, stride: int, pad: i
     return out
 
 
+def stem_supported(x: torch.Tensor, w: torch.Tensor, stride, padding) -> bool:
+    """The network stem: 3x3 / stride 1 / padding 1 over an image with at most 4 channels (K11s)."""
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 4
+            and tuple(w.shape[2:]) == (3, 3) and tuple(stride) == (1, 1) and tuple(padding) == (1, 1)
+            and _lib.available() and bool(_bind().mfl_conv_stem_supported(x.shape[1], w.shape[0])))
+
+
+class _StemFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w):
+        n, c, h, wd = x.shape
+        k = w.shape[0]
+        x = x.contiguous(memory_format=torch.channels_last)
+        wc = w.contiguous(memory_format=torch.channels_last)
+        ctx.save_for_backward(x, w)
+        y = torch.empty((n, k, h, wd), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+        rc = _bind().mfl_conv_stem_fprop_bf16(y.data_ptr(), x.data_ptr(), wc.data_ptr(), n, h, wd, c, k, _lib.stream_ptr())
+        _lib.check(rc, "mfl_conv_stem_fprop_bf16")
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        n, c, h, wd = x.shape
+        k = w.shape[0]
+        gy = gy.contiguous(memory_format=torch.channels_last)
+        gx = None
+        if ctx.needs_input_grad[0]:  # an image that wants a gradient: rare, leave it to the library
+            gx = torch.ops.aten.convolution_backward(gy, x, w, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1,
+                                                     [True, False, False])[0]
+        if not ctx.needs_input_grad[1]:
+            return gx, None
+        L = _bind()
+
+        def run(out, accumulate):
+            stream = torch.cuda.current_stream(x.device)
+            ws = _workspace(x.device, 0, stream)
+            rc = L.mfl_conv_stem_wgrad_bf16(out.data_ptr(), gy.data_ptr(), x.data_ptr(), ws.data_ptr(), n, h, wd, c, k,
+                                            int(accumulate), stream.cuda_stream)
+            _lib.check(rc, "mfl_conv_stem_wgrad_bf16", launches=2)
+
+        direct = OVERLAP_WGRAD and w.grad is not None and w.grad.dtype == torch.bfloat16 and \
+            w.grad.is_contiguous(memory_format=torch.channels_last)
+        if direct:
+            main = torch.cuda.current_stream(x.device)
+            side = _SIDE.stream(x.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                run(w.grad, True)
+            _SIDE.pending.append((gy, x))
+            _SIDE.dirty.add(x.device)
+            return gx, None
+        gw = torch.empty(w.shape, dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+        run(gw, False)
+        return gx, gw
+
+
+def conv3x3_dgrad(gy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """K15 in data-gradient mode: dX of ``conv3x3(x, w)`` from gy [N,K,H,W]; w is the FORWARD filter [K,C,3,3]."""
+    n, k, h, wd = gy.shape
+    c = w.shape[1]
+    gy = gy.contiguous(memory_format=torch.channels_last)
+    w = w.contiguous(memory_format=torch.channels_last)
+    gx = torch.empty((n, c, h, wd), dtype=torch.bfloat16, device=gy.device, memory_format=torch.channels_last)
+    rc = _bind().mfl_conv3x3_dgrad_bf16(gx.data_ptr(), gy.data_ptr(), w.data_ptr(), n, h, wd, c, k, _lib.stream_ptr())
+    _lib.check(rc, "mfl_conv3x3_dgrad_bf16")
+    return gx
+
+
+def _halo_ok(n, c_red, h, wd, k_out, r, s, stride, pad) -> bool:
+    """Shapes where the weight-stationary halo kernel (K15) is the faster formulation: 3x3 / stride 1 / padding 1 with
+    at most 128 reduction channels (all taps of 64 output channels stay resident in shared memory)."""
+    return (r == 3 and s == 3 and stride == 1 and pad == 1 and
+            bool(_bind().mfl_conv3x3_supported(n, h, wd, c_red, k_out)))
+
+
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, stride, pad):
         ctx.save_for_backward(x, w)
         ctx.stride, ctx.pad = stride, pad
+        n, c, h, wd = x.shape
+        if USE_HALO and _halo_ok(n, c, h, wd, w.shape[0], w.shape[2], w.shape[3], stride, pad):
+            return conv3x3(x, w)
         return conv2d_fprop(x, w, stride, pad)
 
     @staticmethod
@@ -181,6 +271,10 @@ class _Conv2dFn(torch.autograd.Function):
             else:
                 gw = conv2d_wgrad(gy, x, w.shape, stride, pad)
             need_w = False
+        if need_x and USE_HALO and _halo_ok(x.shape[0], w.shape[0], x.shape[2], x.shape[3], w.shape[1], w.shape[2],
+                                            w.shape[3], stride, pad):
+            gx = conv3x3_dgrad(gy, w)
+            need_x = False
         if need_x and dgrad_supported(x.shape, w.shape, stride, pad):
             gx = conv2d_dgrad(gy, w, x.shape, stride, pad)
             need_x = False
@@ -196,6 +290,10 @@ def conv2d(x: torch.Tensor, w: torch.Tensor, bias=None, stride=(1, 1), padding=(
     """Drop-in for ``F.conv2d`` that uses the tcgen05 implicit-GEMM kernel when the operands allow it."""
     stride = (stride, stride) if isinstance(stride, int) else tuple(stride)
     padding = (padding, padding) if isinstance(padding, int) else tuple(padding)
+    if isinstance(padding, tuple) and groups == 1 and stem_supported(x, w, stride, padding) and \
+            (dilation == 1 or tuple(dilation) == (1, 1)):
+        y = _StemFn.apply(x, w)
+        return y if bias is None else y + bias.view(1, -1, 1, 1)
     if isinstance(padding, tuple) and supported(x, w, stride, padding, dilation if not isinstance(dilation, int)
                                                 else (dilation, dilation), groups):
         y = _Conv2dFn.apply(x, w, stride[0], padding[0])

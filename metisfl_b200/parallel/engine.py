@@ -28,6 +28,7 @@ from metisfl_b200.ops import aggregation as agg_ops
 from metisfl_b200.ops.optim import OptimHyper
 from metisfl_b200.parallel.arena import ArenaLayout, ModelArena
 from metisfl_b200.parallel.fabric import Fabric
+from metisfl_b200.utils.tracing import DeviceTimer, nvtx_range
 
 
 def staleness_factor(kind: str, staleness: float, a: float = 0.5, b: float = 4.0) -> float:
@@ -77,12 +78,16 @@ class EngineConfig:
     nvls: Optional[bool] = None          # NVSwitch in-switch reduction + multicast stores; None: when world >= 4 (measured: 1.83 vs 2.10 ms
                                          # at 8 GPUs for 355 M bf16 parameters, but 1.83 vs 1.16 ms at 2 GPUs)
     overlap_wgrad: bool = True           # convolution weight gradients on a side stream (ops/conv.py), CUDA only
+    own_conv: bool = False               # every convolution (forward, data and weight gradient) on the hand-written
+                                         # kernels (K11 / K11s / K15) instead of cuDNN; bf16 on CUDA only
     use_b200_linear: bool = True         # nn.Linear forward/backward on the tcgen05 GEMM (K10) when bf16 on CUDA
     seed: int = 1234
     ring: Optional[int] = None           # publish slots per learner (the device lineage): FedRec keeps the previous
                                          # contribution, so 2; every other rule 1
     staging_slots: int = 0               # extra slots per rank for models of off-box learners (unpacked by K12)
     executor_rank: int = 0               # asynchronous rules: the GPU that owns the fp32 rolling state and folds
+    trace: bool = False                  # CUDA-event phase timers (train / aggregate / fold) + NVTX ranges; read them
+                                         # with ``engine.phase_times()``
     fold_blocks: int = 64                # CTAs of one asynchronous fold (it shares the executor's GPU with training)
     standalone: bool = False             # ignore an initialised torch.distributed job: this engine is its own world
     direct_install: Optional[bool] = None  # train in place in the community buffer (one learner per GPU, synchronous
@@ -106,7 +111,10 @@ class FederationEngine:
         module = model_factory()
         if cfg.channels_last and self.device.type == "cuda":
             module = module.to(memory_format=torch.channels_last)
-        if cfg.overlap_wgrad and self.device.type == "cuda":
+        if cfg.own_conv and self.device.type == "cuda" and cfg.model_dtype == torch.bfloat16:
+            from metisfl_b200.ops import conv as _conv
+            _conv.use_b200_conv(module)
+        elif cfg.overlap_wgrad and self.device.type == "cuda":
             from metisfl_b200.ops import conv as _conv
             _conv.use_overlapped_wgrad(module)
         if cfg.use_b200_linear and self.device.type == "cuda" and cfg.model_dtype == torch.bfloat16:
@@ -164,6 +172,7 @@ class FederationEngine:
         self._remote_tasks = {}
         self._copy_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._pinned_loss = None
+        self.timer = DeviceTimer(self.device) if cfg.trace else None
         self._init_async_state()
         self.fabric.host_barrier()
 
@@ -220,8 +229,22 @@ class FederationEngine:
         return float(w[learner])
 
     # ------------------------------------------------------------------------------------------
+    def _phase(self, name: str):
+        """NVTX range + (with ``EngineConfig.trace``) a CUDA-event timer around one phase of the round."""
+        return self.timer.phase(name) if self.timer is not None else nvtx_range(name)
+
+    def phase_times(self, reset: bool = True) -> Dict[str, float]:
+        """Device milliseconds per phase since the last call (``EngineConfig.trace``): the numbers that go into
+        ``FederatedTaskRuntimeMetadata`` on the service path, taken with CUDA events instead of host clocks."""
+        return self.timer.report(reset) if self.timer is not None else {}
+
     def train_learner(self, j: int, batches: Sequence, publish_scale: Optional[float] = None,
                       min_version: Optional[int] = None, cancel=None):
+        with self._phase("train_learner"):
+            return self._train_learner(j, batches, publish_scale, min_version, cancel)
+
+    def _train_learner(self, j: int, batches: Sequence, publish_scale: Optional[float] = None,
+                       min_version: Optional[int] = None, cancel=None):
         """Run one learning task for local learner ``j``; returns the device loss of the last step.
         ``publish_scale`` defaults to the learner's aggregation weight in NVLS mode and to 1 otherwise.
 
@@ -282,6 +305,11 @@ class FederationEngine:
     # ------------------------------------------------------------------------------------------
     def aggregate_sync(self, participants: Optional[Sequence[int]] = None, weights: Optional[Sequence[float]] = None,
                        sources: Optional[Sequence] = None, accumulate: bool = False):
+        with self._phase("aggregate"):
+            return self._aggregate_sync(participants, weights, sources, accumulate)
+
+    def _aggregate_sync(self, participants: Optional[Sequence[int]] = None, weights: Optional[Sequence[float]] = None,
+                        sources: Optional[Sequence] = None, accumulate: bool = False):
         """FedAvg / FedStride over all (or the given) learners: ONE fused launch per GPU.
 
         ``weights`` overrides the scaling factors computed here (the controller computes them on the service

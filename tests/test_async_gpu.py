@@ -135,3 +135,15 @@ def test_async_federation_on_one_gpu_matches_the_cpu_engine(rule):
         outs[dev] = {k: v.float().cpu() for k, v in e.community_state_dict().items()}
     for k in outs["cpu"]:
         torch.testing.assert_close(outs[DEV][k], outs["cpu"][k], atol=2e-4, rtol=2e-3)
+
+
+def test_engine_phase_timers_are_device_timed():
+    """``EngineConfig.trace``: CUDA-event phase timers (utils/tracing.py) around training and aggregation."""
+    e = FederationEngine(FashionMnistMLP, EngineConfig(trace=True, use_cuda_graph=False), device=DEV)
+    x = torch.randn(32, 1, 28, 28).pin_memory()
+    y = torch.randint(0, 10, (32,)).pin_memory()
+    for _ in range(2):
+        e.run_round([[(x, y)] * 2])
+    t = e.phase_times()
+    assert set(t) == {"train_learner", "aggregate"} and all(0.0 < v < 5e3 for v in t.values()), t
+    assert e.phase_times() == {}

@@ -71,6 +71,43 @@ def test_conv_dgrad_and_wgrad_kernels_match_reference(n, c, h, w, k, r, stride, 
     assert (acc.float() - want).norm() / want.norm() < 1e-2
 
 
+@pytest.mark.parametrize("n,c,h,w,k", [(8, 64, 32, 32, 64), (4, 128, 16, 16, 128), (4, 64, 16, 16, 128), (3, 128, 10, 6, 64)])
+def test_halo_kernel_data_gradient_matches_reference(n, c, h, w, k):
+    """K15 in data-gradient mode: forward filters read MN-major with mirrored taps (no transformed copy)."""
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(c + k + h)
+    wt = (torch.randn(k, c, 3, 3, generator=g) / (c * 9) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(n, k, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    xr = torch.zeros(n, c, h, w, device="cuda", requires_grad=True)
+    F.conv2d(xr, wt.float(), None, 1, 1).backward(gy.float())
+    gx = conv.conv3x3_dgrad(gy, wt)
+    err = (gx.float() - xr.grad).norm() / xr.grad.norm()
+    assert err < 1e-2, float(err)
+
+
+@pytest.mark.parametrize("n,c,h,w,k", [(16, 3, 32, 32, 64), (5, 1, 28, 28, 32), (3, 4, 9, 7, 128)])
+def test_stem_convolution_matches_reference(n, c, h, w, k):
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(c + k)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, 3, 3, generator=g) / (c * 9) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last).requires_grad_()
+    assert conv.stem_supported(x, wt, (1, 1), (1, 1))
+    y = conv.conv2d(x, wt, None, 1, 1)
+    wr = wt.detach().float().requires_grad_()
+    yr = F.conv2d(x.float(), wr, None, 1, 1)
+    torch.testing.assert_close(y.float(), yr, atol=2e-2, rtol=2e-2)
+    gy = torch.randn(yr.shape, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    for _ in range(2):  # twice: the scratch comes back zeroed
+        wt.grad = None
+        conv.conv2d(x, wt, None, 1, 1).backward(gy)
+        conv.join()
+    yr.backward(gy.float())
+    err = (wt.grad.float() - wr.grad).norm() / wr.grad.norm()
+    assert err < 1e-2, float(err)
+
+
 def test_resnet18_with_b200_conv_tracks_cudnn():
     from metisfl_b200.models.zoo import ResNet18
     from metisfl_b200.ops import conv
