@@ -525,12 +525,25 @@ __global__ void splitk_finalize_kernel(float* __restrict__ ws, __nv_bfloat16* __
                                        int64_t ld, int accumulate);
 // Split the reduction of a convolution whose output has too few tiles to fill the machine (the 8x8 and 4x4 layers
 // of ResNet-18 give 32-64 tiles for 148 SMs): each (tile, split) work item adds its fp32 partial into `ws`.
+// Output-tile width for a convolution: the widest N tile that still gives (almost) every SM a tile.  A 128 x 256 tile
+// is the most efficient instruction shape, but the 8x8 / 4x4 layers of ResNet-18 have only 64 / 16 row tiles, and a CTA
+// that owns a whole 256-wide tile then runs its 36-72 k-blocks alone while half the machine idles.
+static int pick_bn(int m, int n) {
+  const int tiles_m = (m + kBlockM - 1) / kBlockM;
+  for (int bn : {256, 128}) {
+    if (n < bn && !(bn == 128 && n > 64)) continue;
+    if (tiles_m * ((n + bn - 1) / bn) * 5 >= sm_count() * 4) return bn;
+  }
+  return n > 64 ? 128 : 64;
+}
+
 static void plan_splits(Epilogue& ep, int bn, const float* ws, size_t ws_bytes) {
   const int tiles = ((ep.N + bn - 1) / bn) * ((ep.M + kBlockM - 1) / kBlockM);
   const int num_kb = (ep.K + kBlockK - 1) / kBlockK;
   ep.splits = 1;
   ep.kb_per_split = num_kb;
-  if (!ws || (size_t)ep.M * ep.N * sizeof(float) > ws_bytes || tiles * 5 >= sm_count() * 4 || ep.N % 8 != 0) return;
+  // the fp32 reduce-add pass and the finalize launch cost ~10 us: only worth it when under half of the SMs have a tile
+  if (!ws || (size_t)ep.M * ep.N * sizeof(float) > ws_bytes || tiles * 2 > sm_count() || ep.N % 8 != 0) return;
   int splits = std::min(num_kb / 4, (sm_count() + tiles - 1) / tiles);
   if (splits < 2) return;
   ep.kb_per_split = (num_kb + splits - 1) / splits;
@@ -570,7 +583,7 @@ extern "C" int mfl_conv2d_fprop_bf16_ws(void* y, const void* x, const void* w, f
     MFL_ARG(res == CUDA_SUCCESS, "conv2d: cuTensorMapEncodeIm2col failed with CUresult %d", (int)res);
   }
   const int m = n * oh * ow, kk = r * s * c;
-  const int bn = k > 128 ? 256 : (k > 64 ? 128 : 64);
+  const int bn = pick_bn(m, k);
   if (int rc = make_map(&tb, w, k, kk, kk, bn)) return rc;
   Epilogue ep{y, nullptr, k, m, k, kk, 0, 0, 0, 1, 1, oh, ow, stride, pad, s, c / 64};
   plan_splits(ep, bn, ws, ws_bytes);
@@ -657,6 +670,17 @@ static bool pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 }}  // namespace mfl::gemm
 
+// ws (fp32 [rows, cols]) -> out (bf16, row pitch ld; out += ws when accumulate), ws re-zeroed; cols % 8 == 0
+extern "C" int mfl_splitk_finalize(float* ws, void* out_bf16, int rows, int cols, int64_t ld, int accumulate, void* stream) {
+  using namespace mfl::gemm;
+  MFL_ARG(ws && out_bf16 && rows > 0 && cols > 0 && cols % 8 == 0 && ld % 8 == 0, "splitk_finalize: bad arguments");
+  const int64_t vecs = (int64_t)rows * cols / 8;
+  const int blocks = (int)std::min<int64_t>((vecs + 255) / 256, (int64_t)sm_count() * 4);
+  splitk_finalize_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(ws, static_cast<__nv_bfloat16*>(out_bf16), rows, cols, ld,
+                                                                  accumulate);
+  return check(cudaGetLastError(), "splitk_finalize_kernel launch");
+}
+
 extern "C" size_t mfl_conv2d_wgrad_workspace_bytes(int c, int k, int r, int s) { return (size_t)k * r * s * c * sizeof(float); }
 
 // dW[K,R,S,C] (+)= sum over output pixels of dY[p, k] * X[p + (r, s), c].  ws: zero-initialised fp32 scratch of
@@ -716,7 +740,7 @@ extern "C" int mfl_conv2d_dgrad_bf16_ws(void* dx, const void* dy, const void* w,
   const int rsc = r * s * c;
   CUtensorMap ta, tb, tc;
   if (int rc = make_map_mn(&tb, w, rsc, k, rsc)) return rc;   // B: W [K, RSC]: rows = reduction k, columns contiguous
-  const int bn = c > 128 ? 256 : (c > 64 ? 128 : 64);
+  const int bn = pick_bn(n * (h / stride) * (wd / stride), c);
   if (stride == 2) {
     MFL_ARG(h % 2 == 0 && wd % 2 == 0 && h / 2 == oh && wd / 2 == ow && pow2(oh) && pow2(ow) && c % 64 == 0,
             "conv2d dgrad: stride 2 needs even H, W with H/2, W/2 powers of two and C %% 64 == 0");

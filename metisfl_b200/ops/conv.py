@@ -37,6 +37,8 @@ def _bind():
         L.mfl_conv3x3_supported.argtypes = [i, i, i, i, i]
         L.mfl_conv3x3_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
         L.mfl_conv3x3_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
+        L.mfl_conv3x3_wgrad_supported.argtypes = [i, i, i, i, i]
+        L.mfl_conv3x3_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, vp]
         L.mfl_conv_stem_supported.argtypes = [i, i]
         L.mfl_conv_stem_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
         L.mfl_conv_stem_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, vp]
@@ -156,6 +158,12 @@ def conv2d_wgrad(gy: torch.Tensor, x: torch.Tensor, w_shape, stride: int, pad: i
     L = _bind()
     stream = torch.cuda.current_stream(x.device)
     ws = _workspace(x.device, L.mfl_conv2d_wgrad_workspace_bytes(c, k, r, s), stream)
+    if USE_HALO and r == 3 and s == 3 and stride == 1 and pad == 1 and L.mfl_conv3x3_wgrad_supported(n, h, wd, c, k):
+        # K15w: one halo tile per filter row, the three taps of the row in one N = 192 instruction
+        rc = L.mfl_conv3x3_wgrad_bf16(out.data_ptr(), gy.data_ptr(), x.data_ptr(), ws.data_ptr(), n, h, wd, c, k,
+                                      int(accumulate), stream.cuda_stream)
+        _lib.check(rc, "mfl_conv3x3_wgrad_bf16", launches=2)
+        return out
     rc = L.mfl_conv2d_wgrad_bf16(out.data_ptr(), gy.data_ptr(), x.data_ptr(), ws.data_ptr(), n, h, wd, c, k, r, s, stride,
                                  pad, int(accumulate), stream.cuda_stream)
     _lib.check(rc, "mfl_conv2d_wgrad_bf16", launches=2)

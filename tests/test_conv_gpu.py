@@ -86,6 +86,22 @@ def test_halo_kernel_data_gradient_matches_reference(n, c, h, w, k):
     assert err < 1e-2, float(err)
 
 
+@pytest.mark.parametrize("n,c,h,w,k", [(5, 64, 9, 7, 72), (3, 128, 5, 20, 200), (13, 64, 4, 4, 64), (2, 64, 33, 32, 64),
+                                       (7, 192, 8, 8, 256)])
+def test_halo_weight_gradient_ragged_shapes(n, c, h, w, k):
+    """K15w on shapes that do not divide evenly: ragged row chunks, partial image groups, K not a multiple of 128."""
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(n + c + h + w + k)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(n, k, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wr = torch.zeros(k, c, 3, 3, device="cuda", requires_grad=True)
+    F.conv2d(x.float(), wr, None, 1, 1).backward(gy.float())
+    for _ in range(2):
+        gw = conv.conv2d_wgrad(gy, x, (k, c, 3, 3), 1, 1)
+        err = (gw.float() - wr.grad).norm() / wr.grad.norm()
+        assert err < 1e-2, float(err)
+
+
 @pytest.mark.parametrize("n,c,h,w,k", [(16, 3, 32, 32, 64), (5, 1, 28, 28, 32), (3, 4, 9, 7, 128)])
 def test_stem_convolution_matches_reference(n, c, h, w, k):
     from metisfl_b200.ops import conv
