@@ -37,11 +37,16 @@ for (c, h, k, r, st, p) in [(64, 32, 64, 3, 1, 1), (64, 32, 128, 3, 2, 1), (128,
     t_ours = timeit(lambda: conv.conv2d_fprop(x, w, st, p))
     t_halo = timeit(lambda: conv.conv3x3(x, w)) if (r == 3 and st == 1 and p == 1 and conv.conv3x3_supported(x, w)) else None
     t_cudnn = timeit(lambda: F.conv2d(x, w, None, st, p))
+    tt_f = tt_d = None
+    if r == 3 and st == 1:
+        tt_f = timeit(lambda: conv.conv3x3_t(x, w))
     oh = (h + 2 * p - r) // st + 1
     gy = torch.randn(n, k, oh, oh, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     cb = lambda mask: torch.ops.aten.convolution_backward(gy, x, w, None, [st, st], [p, p], [1, 1], False, [0, 0], 1, mask)
     t_dgrad = timeit(lambda: conv.conv2d_dgrad(gy, w, x.shape, st, p)) if conv.dgrad_supported(x.shape, w.shape, st, p) else None
     t_dgrad_cudnn = timeit(lambda: cb([True, False, False]))
+    if r == 3 and st == 1:
+        tt_d = timeit(lambda: conv.conv3x3_t_dgrad(gy, w))
     t_wgrad = timeit(lambda: conv.conv2d_wgrad(gy, x, w.shape, st, p))
     t_wgrad_cudnn = timeit(lambda: cb([False, True, False]))
     fl = 2.0 * n * oh * oh * k * c * r * r
@@ -50,6 +55,7 @@ for (c, h, k, r, st, p) in [(64, 32, 64, 3, 1, 1), (64, 32, 128, 3, 2, 1), (128,
                  "ours_tflops": fl / t_ours / 1e9, "cudnn_tflops": fl / t_cudnn / 1e9,
                  "dgrad_us": t_dgrad * 1e3 if t_dgrad else None, "dgrad_cudnn_us": t_dgrad_cudnn * 1e3,
                  "wgrad_us": t_wgrad * 1e3, "wgrad_cudnn_us": t_wgrad_cudnn * 1e3,
+                 "k15t_fprop_us": tt_f * 1e3 if tt_f else None, "k15t_dgrad_us": tt_d * 1e3 if tt_d else None,
                  "fprop_vs_cudnn": t_cudnn / t_ours, "dgrad_vs_cudnn": t_dgrad_cudnn / t_dgrad if t_dgrad else None,
                  "wgrad_vs_cudnn": t_wgrad_cudnn / t_wgrad})
 print(json.dumps({"bench": "conv_bench", "batch": 128, "results": rows}))

@@ -39,6 +39,9 @@ def _bind():
         L.mfl_conv3x3_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
         L.mfl_conv3x3_wgrad_supported.argtypes = [i, i, i, i, i]
         L.mfl_conv3x3_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, vp]
+        L.mfl_conv3x3_t_supported.argtypes = [i, i, i, i, i]
+        L.mfl_conv3x3_t_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
+        L.mfl_conv3x3_t_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
         L.mfl_conv_stem_supported.argtypes = [i, i]
         L.mfl_conv_stem_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
         L.mfl_conv_stem_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, vp]
@@ -130,6 +133,8 @@ def conv2d_dgrad(gy: torch.Tensor, w: torch.Tensor, x_shape, stride: int, pad: i
     return gx
 
 
+USE_T = True      # 3x3 / stride-1 layers on the pixels-as-N kernel (K15t) where the image is wide enough
+T_MIN_WIDTH = 8   # below this the zero-padded pixel grid wastes too much of every tile (4x4 images: 16 of 36 columns)
 USE_HALO = True   # route 3x3 / stride-1 layers with <= 128 reduction channels to the weight-stationary kernel (K15)
 _WS = {}   # (device, stream id) -> zeroed fp32 split-K workspace, handed back zeroed by every call
 
@@ -239,6 +244,35 @@ def conv3x3_dgrad(gy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     return gx
 
 
+def conv3x3_t(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """K15t forward: y = conv2d(x, w, stride 1, padding 1) with the pixels as the MMA's N dimension."""
+    n, c, h, wd = x.shape
+    k = w.shape[0]
+    x = x.contiguous(memory_format=torch.channels_last)
+    w = w.contiguous(memory_format=torch.channels_last)
+    y = torch.empty((n, k, h, wd), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    rc = _bind().mfl_conv3x3_t_fprop_bf16(y.data_ptr(), x.data_ptr(), w.data_ptr(), n, h, wd, c, k, _lib.stream_ptr())
+    _lib.check(rc, "mfl_conv3x3_t_fprop_bf16")
+    return y
+
+
+def conv3x3_t_dgrad(gy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """K15t data gradient: dX from gy [N,K,H,W] and the FORWARD filter w [K,C,3,3] (read MN-major, taps mirrored)."""
+    n, k, h, wd = gy.shape
+    c = w.shape[1]
+    gy = gy.contiguous(memory_format=torch.channels_last)
+    w = w.contiguous(memory_format=torch.channels_last)
+    gx = torch.empty((n, c, h, wd), dtype=torch.bfloat16, device=gy.device, memory_format=torch.channels_last)
+    rc = _bind().mfl_conv3x3_t_dgrad_bf16(gx.data_ptr(), gy.data_ptr(), w.data_ptr(), n, h, wd, c, k, _lib.stream_ptr())
+    _lib.check(rc, "mfl_conv3x3_t_dgrad_bf16")
+    return gx
+
+
+def _t_ok(n, c_red, h, wd, c_out, r, s, stride, pad, dgrad: bool) -> bool:
+    return (USE_T and r == 3 and s == 3 and stride == 1 and pad == 1 and (not dgrad or c_out % 64 == 0)
+            and wd >= T_MIN_WIDTH and bool(_bind().mfl_conv3x3_t_supported(n, h, wd, c_red, c_out)))
+
+
 def _halo_ok(n, c_red, h, wd, k_out, r, s, stride, pad) -> bool:
     """Shapes where the weight-stationary halo kernel (K15) is the faster formulation: 3x3 / stride 1 / padding 1 with
     at most 128 reduction channels (all taps of 64 output channels stay resident in shared memory)."""
@@ -252,6 +286,8 @@ class _Conv2dFn(torch.autograd.Function):
         ctx.save_for_backward(x, w)
         ctx.stride, ctx.pad = stride, pad
         n, c, h, wd = x.shape
+        if _t_ok(n, c, h, wd, w.shape[0], w.shape[2], w.shape[3], stride, pad, False):
+            return conv3x3_t(x, w)
         if USE_HALO and _halo_ok(n, c, h, wd, w.shape[0], w.shape[2], w.shape[3], stride, pad):
             return conv3x3(x, w)
         return conv2d_fprop(x, w, stride, pad)
@@ -279,6 +315,10 @@ class _Conv2dFn(torch.autograd.Function):
             else:
                 gw = conv2d_wgrad(gy, x, w.shape, stride, pad)
             need_w = False
+        if need_x and _t_ok(x.shape[0], w.shape[0], x.shape[2], x.shape[3], w.shape[1], w.shape[2], w.shape[3], stride,
+                            pad, True):
+            gx = conv3x3_t_dgrad(gy, w)
+            need_x = False
         if need_x and USE_HALO and _halo_ok(x.shape[0], w.shape[0], x.shape[2], x.shape[3], w.shape[1], w.shape[2],
                                             w.shape[3], stride, pad):
             gx = conv3x3_dgrad(gy, w)

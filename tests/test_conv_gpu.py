@@ -86,6 +86,30 @@ def test_halo_kernel_data_gradient_matches_reference(n, c, h, w, k):
     assert err < 1e-2, float(err)
 
 
+@pytest.mark.parametrize("n,c,h,w,k", [(8, 64, 32, 32, 64), (4, 128, 16, 16, 128), (4, 256, 8, 8, 256), (6, 512, 4, 4, 512),
+                                       (3, 64, 9, 7, 72), (2, 128, 33, 30, 192), (5, 192, 6, 12, 64)])
+def test_pixels_as_n_kernel_forward_and_data_gradient(n, c, h, w, k):
+    """K15t: halo tile as the B operand, weights streamed as A, transposed epilogue; forward and (where the channel
+    counts allow) data gradient against fp32 references."""
+    from metisfl_b200.ops import conv
+    g = torch.Generator().manual_seed(n * 7 + c + h + w + k)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, 3, 3, generator=g) / (c * 9) ** 0.5).to(torch.bfloat16).cuda() \
+        .contiguous(memory_format=torch.channels_last)
+    xr = x.float().requires_grad_()
+    yr = F.conv2d(xr, wt.float(), None, 1, 1)
+    for _ in range(2):
+        y = conv.conv3x3_t(x, wt)
+        err = (y.float() - yr).norm() / yr.norm()
+        assert err < 1e-2, float(err)
+    if k % 64 == 0 and c % 64 == 0:
+        gy = torch.randn(n, k, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+        yr.backward(gy.float())
+        gx = conv.conv3x3_t_dgrad(gy, wt)
+        err = (gx.float() - xr.grad).norm() / xr.grad.norm()
+        assert err < 1e-2, float(err)
+
+
 @pytest.mark.parametrize("n,c,h,w,k", [(5, 64, 9, 7, 72), (3, 128, 5, 20, 200), (13, 64, 4, 4, 64), (2, 64, 33, 32, 64),
                                        (7, 192, 8, 8, 256)])
 def test_halo_weight_gradient_ragged_shapes(n, c, h, w, k):
