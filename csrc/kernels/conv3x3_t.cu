@@ -25,7 +25,8 @@
 //     pixel; junk columns (w >= W) and rows past the image are simply not stored.
 //
 //   warp 0 / lane 0 : TMA producer (halo ring + weight ring)        warp 1 : MMA issuer (one elected lane)
-//   warp 2          : TMEM allocator                                warps 4-7 : epilogue
+//   warp 2          : TMEM allocator                                warps 4-11 : epilogue (two warps per TMEM lane
+//                                                                   quarter, each takes every other 32-column chunk)
 // Reference counterpart: the framework convolutions under model.fit (keras_model_ops.py:156).
 #include <cuda.h>
 
@@ -39,7 +40,7 @@ namespace conv3t {
 
 using namespace mfl::gemm;
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;                // warps 0-2: producer / MMA / TMEM; 3 idle; 4-11: epilogue (2 per lane quarter)
 constexpr int kAStages = 6;                 // weight tiles in flight (16 KB each)
 constexpr int kABytes16 = 128 * 64 * 2;     // one weight tile: 128 out-channels x 64 reduction channels
 constexpr int kMaxBStages = 4;
@@ -83,6 +84,12 @@ conv3x3_t_kernel(const __grid_constant__ CUtensorMap tmap_act, const __grid_cons
   uint64_t* tmem_full = b_empty + kMaxBStages;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  // output offset (in pixels) of every padded pixel of a tile, -1 for the junk columns; rows are checked per tile
+  int* pix_off = reinterpret_cast<int*>(tmem_ptr_smem + 4);          // [256]
+  for (int q = threadIdx.x; q < 256; q += kThreads) {
+    const int trow = q / p.Wp, wcol = q - trow * p.Wp;
+    pix_off[q] = (q < p.NN && wcol < p.W && trow < p.TH) ? ((trow << 16) | wcol) : -1;
+  }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_items = p.num_ptiles * p.mtiles;   // item = pixel tile * mtiles + out-channel tile
@@ -92,7 +99,7 @@ conv3x3_t_kernel(const __grid_constant__ CUtensorMap tmap_act, const __grid_cons
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
     for (int s = 0; s < kAStages; ++s) { mbar_init(a_full + s, 1); mbar_init(a_empty + s, 1); }
     for (int s = 0; s < p.b_stages; ++s) { mbar_init(b_full + s, 1); mbar_init(b_empty + s, 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(tmem_full + b, 1); mbar_init(tmem_empty + b, 128); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tmem_full + b, 1); mbar_init(tmem_empty + b, 256); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   } else if (warp == 2) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(512) : "memory");
@@ -168,7 +175,7 @@ conv3x3_t_kernel(const __grid_constant__ CUtensorMap tmap_act, const __grid_cons
       __syncwarp();
     }
   } else if (warp >= 4) {  // ===== epilogue: D^T[channel lanes, pixel columns] -> NHWC =====
-    const int wq = warp & 3;
+    const int wq = warp & 3, half = (warp - 4) >> 2;
     uint32_t t = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++t) {
       const int pt = item / p.mtiles, mt = item - pt * p.mtiles;
@@ -177,29 +184,27 @@ conv3x3_t_kernel(const __grid_constant__ CUtensorMap tmap_act, const __grid_cons
       mbar_wait(tmem_full + buf, use & 1);
       tcgen05_fence_after();
       const int ch_warp = mt * 128 + wq * 32;          // first channel of this warp's lane quarter
-      const bool warp_live = ch_warp < p.Cout;         // warp-uniform
       // after the pair swap an even lane stores (its channel, its neighbour's) for the even pixel, an odd lane the
       // same pair for the odd pixel
       const int ch_pair = ch_warp + (lane & ~1);
-      __nv_bfloat16* out_img = p.y + (size_t)img * p.H * p.W * p.Cout;
+      const bool live = ch_pair < p.Cout;
+      const int rows_ok = min(p.TH, p.H - h0);         // ragged last tile of an image
+      __nv_bfloat16* out_tile = p.y + ((size_t)img * p.H + h0) * p.W * p.Cout + ch_pair;
+      const int odd = lane & 1;
 #pragma unroll 1
-      for (int c0 = 0; c0 < p.NN; c0 += 32) {
+      for (int c0 = half * 32; c0 < p.NN; c0 += 64) {
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * 256 + (uint32_t)c0, v);
-        if (!warp_live) continue;
+        if (ch_warp >= p.Cout) continue;               // warp-uniform: rows of zero-filled weights
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
-          // lane keeps the pixel of its own parity and gets the neighbour's value for that pixel
-          const uint32_t mine = (lane & 1) ? v[j + 1] : v[j];
-          const uint32_t give = (lane & 1) ? v[j] : v[j + 1];
-          const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
-          const int q = c0 + j + (lane & 1);            // padded pixel index inside the tile
-          const int trow = q / p.Wp, wcol = q - trow * p.Wp;
-          const int hh = h0 + trow;
-          if (q < p.NN && wcol < p.W && trow < p.TH && hh < p.H && ch_pair < p.Cout) {
-            const float lo = __uint_as_float((lane & 1) ? got : mine), hi = __uint_as_float((lane & 1) ? mine : got);
-            __nv_bfloat162 pk = __floats2bfloat162_rn(lo, hi);
-            *reinterpret_cast<__nv_bfloat162*>(out_img + ((size_t)hh * p.W + wcol) * p.Cout + ch_pair) = pk;
+          // a lane keeps the pixel of its own parity and gets its neighbour's value for that pixel
+          const uint32_t mine = odd ? v[j + 1] : v[j];
+          const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? v[j] : v[j + 1], 1);
+          const int po = pix_off[c0 + j + odd];
+          if (po >= 0 && (po >> 16) < rows_ok && live) {
+            const __nv_bfloat162 pk = __floats2bfloat162_rn(__uint_as_float(odd ? got : mine), __uint_as_float(odd ? mine : got));
+            *reinterpret_cast<__nv_bfloat162*>(out_tile + ((size_t)(po >> 16) * p.W + (po & 0xffff)) * p.Cout) = pk;
           }
         }
       }
@@ -250,7 +255,7 @@ static bool plan(Params& p, int n, int h, int wd, int cred, int cout) {
   // the last tap of the last (junk) columns reads up to NN + 2 * Wp + 2 rows
   const int need_rows = std::max((p.TH + 2) * p.Wp, p.NN + 2 * p.Wp + 2);
   p.halo_bytes = (need_rows * 128 + 1023) / 1024 * 1024;
-  const size_t fixed = 1024 + (size_t)kAStages * kABytes16 + 512;
+  const size_t fixed = 1024 + (size_t)kAStages * kABytes16 + 512 + 1024;
   p.b_stages = (int)std::min<size_t>(kMaxBStages, (227 * 1024 - fixed) / p.halo_bytes);
   if (p.b_stages < 2) return false;
   p.tiles_per_img = (h + p.TH - 1) / p.TH;
@@ -295,7 +300,7 @@ static int launch(void* y, const void* act, const void* w, int n, int h, int wd,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     MFL_ARG(r == CUDA_SUCCESS, "conv3x3: filter tensor map failed with CUresult %d", (int)r);
   }
-  const size_t smem = 1024 + (size_t)kAStages * kABytes16 + (size_t)p.b_stages * p.halo_bytes + 512;
+  const size_t smem = 1024 + (size_t)kAStages * kABytes16 + (size_t)p.b_stages * p.halo_bytes + 512 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     MFL_CUDA(cudaFuncSetAttribute(conv3x3_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
