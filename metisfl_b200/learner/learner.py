@@ -138,9 +138,12 @@ class Learner(object):
     def _model_ops_factory(self, nn_engine=None):
         if self._model_ops is None:
             engine = (nn_engine or self._nn_engine or "pytorch").lower()
+            if engine in ("keras", "tensorflow", "tf"):  # needs TensorFlow at load time (SavedModel directory)
+                from metisfl_b200.models.keras.keras_model_ops import KerasModelOps
+                self._model_ops = KerasModelOps(self._model_dir, he_scheme=self._he_scheme_factory())
+                return self._model_ops
             if engine not in ("pytorch", "torch"):
-                raise RuntimeError("Only the PyTorch engine is available in this build (got '{}'); the "
-                                   "reference's Keras backend needs TensorFlow.".format(engine))
+                raise RuntimeError("Unknown neural engine '{}' (pytorch | keras | echo).".format(engine))
             from metisfl_b200.models.torch_model_ops import TorchModelOps
             self._model_ops = TorchModelOps(self._model_dir, he_scheme=self._he_scheme_factory(), device=self._device)
         return self._model_ops
