@@ -18,6 +18,7 @@ under ``model.fit`` (``keras_model_ops.py:156``).
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.nn as nn
@@ -134,7 +135,7 @@ def conv2d_dgrad(gy: torch.Tensor, w: torch.Tensor, x_shape, stride: int, pad: i
 
 
 USE_T = True      # 3x3 / stride-1 layers on the pixels-as-N kernel (K15t) where the image is wide enough
-T_MIN_WIDTH = 8   # below this the zero-padded pixel grid wastes too much of every tile (4x4 images: 16 of 36 columns)
+T_MIN_WIDTH = 16  # below this the zero-padded pixel grid wastes too much of every tile (4x4 images: 16 of 36 columns)
 USE_HALO = True   # route 3x3 / stride-1 layers with <= 128 reduction channels to the weight-stationary kernel (K15)
 _WS = {}   # (device, stream id) -> zeroed fp32 split-K workspace, handed back zeroed by every call
 
@@ -269,8 +270,11 @@ def conv3x3_t_dgrad(gy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
 
 
 def _t_ok(n, c_red, h, wd, c_out, r, s, stride, pad, dgrad: bool) -> bool:
+    # measured (profiles/README.md): K15t wins among the own kernels for 128-channel layers on 16x16 images; 64-channel
+    # layers stay on K15 (their 1024 small tiles are bound by K15t's transposed epilogue), 8x8 and 4x4 images on K11
     return (USE_T and r == 3 and s == 3 and stride == 1 and pad == 1 and (not dgrad or c_out % 64 == 0)
-            and wd >= T_MIN_WIDTH and bool(_bind().mfl_conv3x3_t_supported(n, h, wd, c_red, c_out)))
+            and wd >= T_MIN_WIDTH and c_red >= 128 and c_out >= 128
+            and bool(_bind().mfl_conv3x3_t_supported(n, h, wd, c_red, c_out)))
 
 
 def _halo_ok(n, c_red, h, wd, k_out, r, s, stride, pad) -> bool:
@@ -410,22 +414,66 @@ class _OverlapConvFn(torch.autograd.Function):
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         gw = None
         direct = need_w and OVERLAP_WGRAD and w.grad is not None and w.grad.dtype == w.dtype
+        own_w = direct and HYBRID and _own_wgrad_wins(x, w, stride, padding, dilation, groups) and \
+            w.grad.is_contiguous(memory_format=torch.channels_last)
         if direct:
             main = torch.cuda.current_stream(x.device)
             side = _SIDE.stream(x.device)
             side.wait_stream(main)                       # gy (and x) are ready on the main stream
             with torch.cuda.stream(side):
-                g = torch.ops.aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0], groups,
-                                                        [False, True, False])[1]
-                w.grad.add_(g)
+                if own_w:   # hand-written weight gradient, accumulated straight into the flat gradient arena
+                    conv2d_wgrad(gy.contiguous(memory_format=torch.channels_last), x, w.shape, stride[0], padding[0],
+                                 out=w.grad, accumulate=True)
+                    g = None
+                else:
+                    g = torch.ops.aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0],
+                                                            groups, [False, True, False])[1]
+                    w.grad.add_(g)
             _SIDE.pending.append((gy, x, g))             # keep the operands alive until join()
             _SIDE.dirty.add(x.device)
             need_w = False
         gx = None
+        if need_x and HYBRID and _own_dgrad_wins(x, w, stride, padding, dilation, groups):
+            gx = conv2d_dgrad(gy, w, x.shape, stride[0], padding[0])
+            need_x = False
         if need_x or need_w:
             gx, gw, _ = torch.ops.aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0],
                                                             groups, [need_x, need_w, False])
         return gx, gw, None, None, None, None
+
+
+# Per-shape dispatch of the cuDNN-based default path: where a hand-written gradient kernel measured faster than cuDNN on
+# the ResNet-18 shapes (bench/conv_bench.py, profiles/README.md) it takes that gradient; the rest stays on the library.
+HYBRID = os.environ.get("MFL_CONV_HYBRID", "1") != "0"
+
+
+def _bf16_nhwc(x, w, dilation, groups) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and groups == 1
+            and tuple(dilation) == (1, 1) and _lib.available())
+
+
+def _own_dgrad_wins(x, w, stride, padding, dilation, groups) -> bool:
+    """Stride-2 data gradients (one launch over the four parity classes) from 128 input channels up, and every 1x1
+    stride-2 shortcut: 18.9 vs 59.4 us, 21.9 vs 31.1 us, 17.4 vs 21.2 us against cuDNN."""
+    if not _bf16_nhwc(x, w, dilation, groups) or tuple(stride) != (2, 2) or stride[0] != stride[1]:
+        return False
+    k, c, r, s = w.shape
+    if not dgrad_supported(x.shape, w.shape, 2, padding[0]) or padding[0] != padding[1]:
+        return False
+    return (r == 1 and s == 1) or (r == 3 and s == 3 and c >= 128)
+
+
+def _own_wgrad_wins(x, w, stride, padding, dilation, groups) -> bool:
+    """K15w on 3x3 stride-1 layers with images of 16x16 and more (29.6 vs 32.8 us, 23.5 vs 28.3 us), and the 1x1
+    shortcuts (17.4 vs 22.5 us)."""
+    if not _bf16_nhwc(x, w, dilation, groups) or x.shape[1] % 64 != 0 or w.shape[0] % 8 != 0:
+        return False
+    k, c, r, s = w.shape
+    if padding[0] != padding[1] or stride[0] != stride[1]:
+        return False
+    if r == 3 and s == 3 and stride[0] == 1 and padding[0] == 1:
+        return x.shape[3] >= 16 and bool(_bind().mfl_conv3x3_wgrad_supported(x.shape[0], x.shape[2], x.shape[3], c, k))
+    return r == 1 and s == 1 and padding[0] == 0
 
 
 class OverlappedConv2d(nn.Conv2d):

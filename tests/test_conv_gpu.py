@@ -169,6 +169,33 @@ def test_resnet18_with_b200_conv_tracks_cudnn():
     assert torch.nn.functional.cosine_similarity(gr.flatten(), go.flatten(), dim=0) > 0.98
 
 
+def test_hybrid_dispatch_gradients_match_the_library_path():
+    """The default path takes the hand-written gradient kernels where they measured faster (stride-2 / 1x1 data
+    gradients, K15w weight gradients): a whole ResNet-18 backward must give the same flat gradient arena."""
+    from metisfl_b200.models.zoo import ResNet18
+    from metisfl_b200.ops import conv
+    from metisfl_b200.parallel.arena import ModelArena
+    x = torch.randn(32, 3, 32, 32, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 10, (32,), device="cuda")
+    grads = []
+    for hybrid in (False, True):
+        torch.manual_seed(0)
+        m = ResNet18().to(memory_format=torch.channels_last)
+        conv.use_overlapped_wgrad(m)
+        arena = ModelArena(m, "cuda", torch.bfloat16)
+        old = conv.HYBRID
+        conv.HYBRID = hybrid
+        try:
+            F.cross_entropy(m(x).float(), y).backward()
+            conv.join()
+        finally:
+            conv.HYBRID = old
+        torch.cuda.synchronize()
+        grads.append(arena.grad[0].float().clone())
+    err = (grads[0] - grads[1]).norm() / grads[0].norm()
+    assert err < 2e-2, float(err)
+
+
 def test_overlapped_wgrad_matches_autograd_eager_and_in_a_graph():
     """Weight gradients issued on the side stream (and accumulated into pre-allocated flat grads) equal autograd's."""
     import torch.nn as nn
