@@ -226,6 +226,11 @@ extern "C" int mfl_quantify_noalloc(const void* data, int dtype, const uint64_t*
                                     unsigned long long* counts, void* stream) {
   MFL_ARG(data && offsets && counts, "quantify_noalloc: data, offsets and counts are required");
   MFL_ARG(n_vars >= 1, "quantify_noalloc: n_vars must be >= 1");
+  // Today the scratch need does not depend on the call (one fixed-size record per CTA of a fixed-size grid: 9472 of the
+  // 16384 bytes), so this refusal cannot trigger yet; it is here so that a later change of the grid or the record
+  // size turns into a clear error for oversized calls instead of a write past the array.
+  static_assert(sizeof(QPartial) * kQBlocks <= MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES,
+                "the built-in scratch array no longer holds one record per CTA");
   const size_t need = mfl_quantify_scratch_bytes(n_vars);
   MFL_ARG(need <= (size_t)MFL_QUANTIFY_NOALLOC_SCRATCH_BYTES,
           "quantify_noalloc: this call needs %zu bytes of scratch but the built-in array holds %d; "

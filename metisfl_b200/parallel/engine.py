@@ -62,7 +62,10 @@ class EngineConfig:
     learners_per_gpu: int = 1
     model_dtype: torch.dtype = torch.bfloat16
     optimizer: OptimHyper = field(default_factory=lambda: OptimHyper("MomentumSGD", lr=0.05, momentum=0.9))
-    rule: str = "FedAvg"                 # FedAvg | FedStride | FedRec | FedAsync
+    rule: str = "FedAvg"                 # FedAvg | FedStride | FedRec | FedAsync | PWA (CKKS secure FedAvg, needs crypto_dir)
+    crypto_dir: Optional[str] = None     # PWA: directory with cryptocontext.txt / key-public.txt / key-private.txt
+    he_batch_size: int = 4096
+    he_scaling_factor_bits: int = 52
     scaling: str = "NumTrainingExamples"
     stride_length: int = 0
     num_train_examples: int = 6400       # per learner (can be overridden per learner)
@@ -124,7 +127,7 @@ class FederationEngine:
         nb = self.layout.total_bytes
         # symmetric buffers: community model + k publish slots per rank
         want_mc = (cfg.nvls is True or (cfg.nvls is None and self.world >= 4)) and self.world > 1 and self.k <= 8
-        sync_rule = cfg.rule in ("FedAvg", "FedStride")
+        sync_rule = cfg.rule in ("FedAvg", "FedStride", "PWA")
         self.async_rule = not sync_rule
         self.ring = int(cfg.ring or (2 if cfg.rule == "FedRec" else 1))
         self.n_slots = self.k * self.ring + int(cfg.staging_slots)
@@ -174,6 +177,12 @@ class FederationEngine:
         self._pinned_loss = None
         self.timer = DeviceTimer(self.device) if cfg.trace else None
         self._init_async_state()
+        self.secure = None
+        if cfg.rule == "PWA":
+            assert self.k == 1 and cfg.crypto_dir, "PWA: one learner per GPU and EngineConfig.crypto_dir (key files)"
+            assert self.device.type == "cuda", "the PWA engine rule runs the CKKS kernels: CUDA only (host path: fhe.CKKS)"
+            from metisfl_b200.parallel.secure import SecureAggregator
+            self.secure = SecureAggregator(self, cfg.crypto_dir, cfg.he_batch_size, cfg.he_scaling_factor_bits)
         self.fabric.host_barrier()
 
     # ------------------------------------------------------------------------------------------
@@ -635,7 +644,10 @@ class FederationEngine:
         Returns the per-learner last-step losses (host floats) and, if requested, the community
         model's evaluation on ``evaluate_batch`` - both read back through pinned memory.
         """
-        assert self.cfg.rule in ("FedAvg", "FedStride"), "run_round drives the synchronous rules"
+        assert self.cfg.rule in ("FedAvg", "FedStride", "PWA"), "run_round drives the synchronous rules"
+        if self.secure is not None:   # encrypted FedAvg: encrypt -> fused ciphertext reduction over NVLink -> decrypt
+            self.secure.round(batches_per_learner[0])
+            return {"loss": [], "eval": None, "phase_ms": self.secure.phase_ms(reset=False)}
         losses = []
         for j in range(self.k):
             losses.append(self.train_learner(j, batches_per_learner[j]))
