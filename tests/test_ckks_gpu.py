@@ -89,3 +89,25 @@ def test_fhe_class_uses_gpu_for_large_tensors(ctx):
     a, b = auto.encrypt(x), auto.encrypt(-x)
     avg = auto.compute_weighted_average([a, b], [0.75, 0.25])
     np.testing.assert_allclose(auto.decrypt(avg, x.size), 0.5 * x, atol=1e-7)
+
+
+def test_engine_rule_pwa_round_with_key_files(tmp_path):
+    """``EngineConfig(rule="PWA")``: keys from files, encrypt -> fused ciphertext reduction -> decrypt, device-timed
+    phases; at world 1 the decrypted community model must equal the learner's own published model."""
+    import torch
+    from metisfl_b200.models.zoo import FashionMnistMLP
+    from metisfl_b200.parallel.engine import EngineConfig, FederationEngine
+    from metisfl_b200.parallel.secure import SecureAggregator
+    files = SecureAggregator.generate_keys(str(tmp_path / "keys"))
+    assert set(files) >= {"crypto_context_file", "public_key_file", "private_key_file"}
+    eng = FederationEngine(FashionMnistMLP, EngineConfig(rule="PWA", crypto_dir=str(tmp_path / "keys"),
+                                                         use_cuda_graph=False), device="cuda:0")
+    x = torch.randn(32, 1, 28, 28).to(torch.bfloat16).cuda()
+    y = torch.randint(0, 10, (32,)).cuda()
+    eng.secure.round([(x, y)] * 2, check=True)
+    assert eng.secure.last_error < 1e-6, eng.secure.last_error
+    out = eng.run_round([[(x, y)]])
+    assert set(out["phase_ms"]) >= {"train", "encode_encrypt", "reduce_over_nvlink", "decrypt_decode"}
+    assert all(v > 0 for v in out["phase_ms"].values())
+    slot = eng.slot_views[0][0].float()
+    torch.testing.assert_close(eng.arena.seg[0].float(), slot, atol=1e-2, rtol=1e-2)
