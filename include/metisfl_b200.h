@@ -213,6 +213,50 @@ int mfl_conv2d_fprop_bf16(void* y, const void* x, const void* w, int n, int h, i
 int mfl_conv3x3_supported(int n, int h, int wd, int c, int k);
 int mfl_conv3x3_bf16(void* y, const void* x, const void* w, float* stats, int n, int h, int wd, int c, int k,
                      void* stream);
+/* K15 as a data gradient: dx[n,h,w,c] from dy[n,h,w,k] and the FORWARD filters w[k,3,3,c] (the kernel reads them
+ * transposed and flipped in place; no repacked copy). */
+int mfl_conv3x3_dgrad_bf16(void* dx, const void* dy, const void* w, int n, int h, int wd, int c, int k, void* stream);
+
+/* ---- K11 gradients (csrc/kernels/gemm_tcgen05.cu).  Same NHWC bf16 tensors as the forward call.
+ * _ws variants take an fp32 scratch (any size; used for split-K when the output has few tiles: partial tiles are
+ * added into it with TMA reduce-add and mfl_splitk_finalize casts to bf16).  Without scratch no split-K is used.
+ *  - dgrad: dx[n,h,w,c] = sum over taps of dy . w; stride 1 and 2; ONE launch walks the stride^2 parity classes of
+ *    input pixels, each with its own tap subset, and stores through a 5-D strided TMA map.
+ *  - wgrad: dw[k,r,s,c] (+)= dy^T . im2col(x), split over output pixels across the whole grid; ws must hold
+ *    mfl_conv2d_wgrad_workspace_bytes(c,k,r,s) bytes and be ZERO on entry (the call leaves it zero again). */
+int mfl_conv2d_fprop_bf16_ws(void* y, const void* x, const void* w, float* ws, size_t ws_bytes, int n, int h, int wd,
+                             int c, int k, int r, int s, int stride, int pad, void* stream);
+int mfl_conv2d_dgrad_bf16(void* dx, const void* dy, const void* w, int n, int h, int wd, int c, int k, int r, int s,
+                          int stride, int pad, void* stream);
+int mfl_conv2d_dgrad_bf16_ws(void* dx, const void* dy, const void* w, float* ws, size_t ws_bytes, int n, int h, int wd,
+                             int c, int k, int r, int s, int stride, int pad, void* stream);
+size_t mfl_conv2d_wgrad_workspace_bytes(int c, int k, int r, int s);
+int mfl_conv2d_wgrad_bf16(void* dw, const void* dy, const void* x, float* ws, int n, int h, int wd, int c, int k, int r,
+                          int s, int stride, int pad, int accumulate, void* stream);
+int mfl_splitk_finalize(float* ws, void* out_bf16, int rows, int cols, int64_t ld, int accumulate, void* stream);
+
+/* ---- K15w: 3x3 / stride-1 / pad-1 weight gradient from halo tiles (csrc/kernels/conv3x3_wgrad.cu): one x halo tile
+ * and one dy tile per chunk of output pixels; the three taps of a filter row are ONE N=192 tcgen05 instruction whose
+ * B descriptor walks overlapping 64-column blocks.  Same workspace contract as mfl_conv2d_wgrad_bf16. */
+int mfl_conv3x3_wgrad_supported(int n, int h, int wd, int c, int k);
+int mfl_conv3x3_wgrad_bf16(void* dw, const void* dy, const void* x, float* ws, int n, int h, int wd, int c, int k,
+                           int accumulate, void* stream);
+
+/* ---- K15t: 3x3 / stride-1 / pad-1 convolution with PIXELS as the tensor-core N dimension
+ * (csrc/kernels/conv3x3_t.cu): filters stream as the M operand, the halo tile is the N operand, the epilogue
+ * transposes back to NHWC.  Measured best of the hand-written kernels for 128-channel layers on 16x16 images (the
+ * Python dispatch routes >= 128 channels, width >= 16 here).  fprop and dgrad (forward filters, read transposed +
+ * flipped in place). */
+int mfl_conv3x3_t_supported(int n, int h, int wd, int c_reduce, int c_out);
+int mfl_conv3x3_t_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, void* stream);
+int mfl_conv3x3_t_dgrad_bf16(void* dx, const void* dy, const void* w, int n, int h, int wd, int c, int k, void* stream);
+
+/* ---- K11s: the network stem (csrc/kernels/conv_stem.cu): 3x3 / stride 1 / pad 1 with c <= 4 input channels, where
+ * an implicit GEMM would pad the reduction 16x.  Direct convolution, filters in registers / shared memory. */
+int mfl_conv_stem_supported(int c, int k);
+int mfl_conv_stem_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, void* stream);
+int mfl_conv_stem_wgrad_bf16(void* dw, const void* dy, const void* x, float* ws, int n, int h, int wd, int c, int k,
+                             int accumulate, void* stream);
 
 /* ---- K16: fused softmax cross-entropy for a language-model head (csrc/kernels/cross_entropy.cu): per-row loss and
  * d(loss)/d(logits) in one pass pair over bf16 logits, no fp32 copy.  logits [rows, vocab] bf16 with row pitch ld,
