@@ -47,7 +47,54 @@ def parse():
     ap.add_argument("--own-conv", action="store_true", help="convolutions on the hand-written kernels instead of cuDNN")
     ap.add_argument("--no-stock", action="store_true", help="skip the stock PyTorch/cuDNN + NCCL arm (vs_baseline)")
     ap.add_argument("--no-service", action="store_true", help="skip the DriverSession/gRPC sub-record (1 GPU only)")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5],
+                    help="BASELINE.json north-star config: 2 = the headline (default), 3 = asynchronous ResNet-18 with "
+                         "8 heterogeneous learners per GPU, 4 = ResNet-18 + CKKS secure aggregation, 5 = GPT-2 medium "
+                         "with 128 streamed learners per GPU")
     return ap.parse_args()
+
+
+def run_other_config(args):
+    """Configs #3 / #4 / #5 live in ``examples/``; this runs the script in-process on every rank (same launch
+    contract as the headline), samples clocks around it and re-emits rank 0's result in the bench.py line format."""
+    import contextlib
+    import io
+    import runpy
+    here = os.path.dirname(os.path.abspath(__file__))
+    script, argv, metric, pick = {
+        3: ("resnet_async.py", ["--rule", "FedAsync", "--updates", str(max(32, args.steps * 8))],
+            "community_updates_per_sec (asynchronous FedAsync, 8 heterogeneous learners per GPU)",
+            lambda r: (r["updates_per_s"], "updates/s", r["ms_per_update"], "weak")),
+        4: ("resnet_secure.py", ["--rounds", str(args.steps)],
+            "secure_round_time_s (ResNet-18, CKKS encrypt -> fused ciphertext reduce over NVLink -> decrypt)",
+            lambda r: (r["round_time_s"], "s", r["round_time_s"] * 1e3, "weak")),
+        5: ("gpt2_many_learners.py", ["--rounds", "1"],
+            "aggregated_params_per_sec (GPT-2 medium, 128 streamed learners per GPU)",
+            lambda r: (r["aggregated_params_per_s"], "params/s", r["round_time_s"] * 1e3, "weak")),
+    }[args.config]
+    rank = int(os.environ.get("RANK", "0"))
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0"))) if rank == 0 else None
+    sys.path.insert(0, os.path.join(here, "examples"))
+    old_argv, buf = sys.argv, io.StringIO()
+    sys.argv = [script] + argv
+    try:
+        with contextlib.redirect_stdout(buf):
+            runpy.run_path(os.path.join(here, "examples", script), run_name="__main__")
+    finally:
+        sys.argv = old_argv
+    clocks = sampler.stop() if sampler else None
+    if rank != 0:
+        return 0
+    lines = [l for l in buf.getvalue().splitlines() if l.startswith("{")]
+    res = json.loads(lines[-1])
+    value, unit, ms, scaling = pick(res)
+    print(json.dumps({"metric": metric, "value": value, "unit": unit, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+                      "steps": args.steps, "warmup": 1, "ms_per_step": ms, "higher_is_better": args.config != 4,
+                      "scaling": scaling, "vs_baseline": None, "dtype": "bf16",
+                      "data": "synthetic (random batches of the named shape, random-init weights)", "impl": "ours",
+                      "config": {"north_star_config": args.config, "script": "examples/" + script, **res},
+                      "clocks": clocks, "e2e": None, "gpu_launches": None}))
+    return 0
 
 
 class ClockSampler:
@@ -100,6 +147,8 @@ def main():
     if args.impl == "reference":
         print(json.dumps({"impl": "reference", "unavailable": REF_WHY}))
         return 0
+    if args.config != 2:
+        return run_other_config(args)
 
     import torch
     import torch.distributed as dist
@@ -302,6 +351,25 @@ def main():
     h2d = k * S * (x0.numel() * x0.element_size() + (y0.numel() * y0.element_size() if y0 is not x0 else 0))
     d2h = 4 * k
     peak_mb = torch.cuda.max_memory_allocated(device) / 2**20
+    agg_mode = "nvls" if eng.nvls else ("p2p" if world > 1 else "local")
+    # ---- the same round through DriverSession -> controller gRPC -> learner (the reference user's call sequence) ----
+    service = None
+    if world == 1 and not args.no_service and args.model == "resnet18":
+        eng.close()
+        eng = None
+        try:
+            sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "bench"))
+            import contextlib
+            import io
+            from service_bench import service_rounds
+            with contextlib.redirect_stdout(io.StringIO()):
+                service = service_rounds(True, rounds=max(8, min(args.steps, 20)), warmup=4, local_steps=S, batch=B,
+                                         cuda_device=local_rank)
+            if service.get("ms_per_round"):
+                service["value"] = n_params / (service["ms_per_round"] * 1e-3)
+                service["unit"] = "params/s"
+        except Exception as e:  # the headline must not die with the side measurement
+            service = {"error": repr(e)[:300]}
     if rank == 0:
         print(json.dumps({
             "metric": "aggregated_params_per_sec (federation round: local training + fused FedAvg)",
@@ -315,7 +383,10 @@ def main():
                        "batch_per_learner": B, "seq_len": args.seq_len if args.model.startswith("gpt2") else None,
                        "parallelism": f"fed-dp{world}", "optimizer": "MomentumSGD(fused K2)",
                        "cuda_graph": not args.no_graph,
-                       "convolutions": "own tcgen05 kernels (K11/K11s/K15)" if args.own_conv else "cuDNN",
+                       "convolutions": "own tcgen05 kernels for every convolution (K11/K11s/K15/K15t/K15w)" if args.own_conv
+                                       else ("per-shape dispatch: own tcgen05 gradients where measured faster "
+                                             "(stride-2 / 1x1 dgrad, K15w + 1x1 wgrad), cuDNN elsewhere"
+                                             if os.environ.get("MFL_CONV_HYBRID", "1") != "0" else "cuDNN"),
                        "l2": f"no flush: per-round working set (peak {peak_mb:.0f} MiB allocated) exceeds the 126 MB L2"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "params/s", "ms_per_step": e2e_ms,
@@ -329,15 +400,17 @@ def main():
                              "ms_per_round_cuda_graph": stock_graph_ms or None},
             "aggregation": {"k1_fused_ms": k1_ms, "nccl_scale_allreduce_ms": nccl_ms,
                             "k1_vs_nccl": nccl_ms / k1_ms if k1_ms > 0 else None,
-                            "mode": "nvls" if eng.nvls else ("p2p" if world > 1 else "local"),
+                            "mode": agg_mode,
                             "roofline_ms": roof_ms, "fraction_of_roofline": roof_ms / k1_ms if k1_ms > 0 else None,
                             "roofline_def": "bytes that must cross NVLink per GPU and direction / 770 GB/s measured "
                                             "(world 1: slot reads + community write / measured HBM copy)"},
             "community_check": check,
+            "e2e_service": service,
             "gpu_launches": launches, "gpu_launches_per_round": launches / args.steps,
             "last_loss": last["loss"] if last else None,
         }))
-    eng.close()
+    if eng is not None:
+        eng.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
