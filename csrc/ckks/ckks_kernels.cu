@@ -100,27 +100,38 @@ __global__ void __launch_bounds__(kNttThreads, 1) ntt_rows_kernel(const __grid_c
   }
 }
 
-// ---- counter-based RNG (Philox4x32-10) --------------------------------------------------------
-struct Philox {
-  uint32_t key[2];
-  __device__ static void round(uint32_t* c, const uint32_t* k) {
-    const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
-    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
-    const uint32_t n0 = hi1 ^ c[1] ^ k[0], n2 = hi0 ^ c[3] ^ k[1];
-    c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+// ---- counter-based CSPRNG: ChaCha20 block function (RFC 8439 state layout, 64-bit block counter) -------------------
+// One 256-bit key per encrypt call (fresh from the OS on the host side).  A block is addressed by
+// (counter = ciphertext index << 16 | block-in-polynomial, stream id): stream 0 = ternary u, 1 = e0, 2 = e1, so no
+// block is ever used for two purposes and every limb row of a ciphertext regenerates the SAME u / e0 / e1.
+struct ChaChaKey { uint32_t k[8]; };
+struct ChaCha20 {
+  ChaChaKey key;
+  __device__ __forceinline__ static void qr(uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+    a += b; d ^= a; d = __funnelshift_l(d, d, 16);
+    c += d; b ^= c; b = __funnelshift_l(b, b, 12);
+    a += b; d ^= a; d = __funnelshift_l(d, d, 8);
+    c += d; b ^= c; b = __funnelshift_l(b, b, 7);
   }
-  __device__ void operator()(uint64_t counter, uint32_t stream_id, uint32_t* out) const {
-    uint32_t c[4] = {(uint32_t)counter, (uint32_t)(counter >> 32), stream_id, 0x9E3779B9u};
-    uint32_t k[2] = {key[0], key[1]};
+  __device__ __forceinline__ void block(uint64_t counter, uint32_t stream_id, uint32_t* out) const {
+    const uint32_t in[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u,
+                             key.k[0], key.k[1], key.k[2], key.k[3], key.k[4], key.k[5], key.k[6], key.k[7],
+                             (uint32_t)counter, (uint32_t)(counter >> 32), stream_id, 0u};
+    uint32_t x[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = in[i];
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
-      round(c, k);
-      k[0] += 0x9E3779B9u;
-      k[1] += 0xBB67AE85u;
+      qr(x[0], x[4], x[8], x[12]); qr(x[1], x[5], x[9], x[13]); qr(x[2], x[6], x[10], x[14]); qr(x[3], x[7], x[11], x[15]);
+      qr(x[0], x[5], x[10], x[15]); qr(x[1], x[6], x[11], x[12]); qr(x[2], x[7], x[8], x[13]); qr(x[3], x[4], x[9], x[14]);
     }
-    out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) out[i] = x[i] + in[i];
   }
 };
+
+// uniform {-1, 0, 1} from one 32-bit word by rejection-free multiply-shift (bias 2^-32, below the scheme's noise budget)
+__device__ __forceinline__ int ternary_from_bits(uint32_t a) { return (int)__umulhi(a, 3u) - 1; }
 
 __device__ __forceinline__ int gaussian_from_bits(uint32_t a, uint32_t b, float sigma) {
   const float u1 = (a + 1.0f) * 2.3283064e-10f;  // (0, 1]
@@ -256,12 +267,13 @@ __global__ void __launch_bounds__(512) decode_kernel(const __grid_constant__ Ctx
 // ---- K7: encrypt / decrypt ---------------------------------------------------------------------
 __global__ void __launch_bounds__(kNttThreads, 1) encrypt_kernel(const __grid_constant__ Ctx cx, const double* __restrict__ coeffs,
                                                                  uint32_t slots, const uint64_t* __restrict__ pk,
-                                                                 const uint64_t* __restrict__ pks, uint64_t seed,
+                                                                 const uint64_t* __restrict__ pks,
+                                                                 const __grid_constant__ ChaChaKey key,
                                                                  uint64_t* ct_out, uint32_t n_ct) {
   extern __shared__ __align__(16) uint64_t sm[];
   const int L = cx.c.n_limbs, log_n = cx.c.log_n;
   const uint32_t N = 1u << log_n, gap = (N / 2) / slots;
-  const Philox rng{{(uint32_t)seed, (uint32_t)(seed >> 32)}};
+  const ChaCha20 rng{key};
   constexpr float kSigma = 3.2f;
   for (uint32_t row = blockIdx.x; row < n_ct * (uint32_t)L; row += gridDim.x) {
     const uint32_t ct = row / L, l = row % L;
@@ -273,11 +285,16 @@ __global__ void __launch_bounds__(kNttThreads, 1) encrypt_kernel(const __grid_co
     const uint64_t *pk0 = pk + (size_t)l * N, *pk1 = pk + (size_t)(L + l) * N;
     const uint64_t *pk0s = pks + (size_t)l * N, *pk1s = pks + (size_t)(L + l) * N;
     const double* m = coeffs + (size_t)ct * 2 * slots;
-    uint32_t r[4];
-    // pass 1: u (ternary, the same polynomial for every limb of this ciphertext)
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) {
-      rng((uint64_t)ct * N + i, 0, r);
-      sm[i] = signed_to_mod((int)(r[0] % 3) - 1, q);
+    uint32_t r[16];
+    // Word j of block b lands on coefficient j * (N / words-per-block-used) + b: consecutive threads (consecutive b)
+    // write consecutive shared-memory words, and the map (b, j) -> coefficient is a bijection.
+    const uint32_t nb16 = N / 16, nb8 = N / 8;
+    const uint64_t ctr0 = (uint64_t)ct << 16;
+    // pass 1: u (ternary, the same polynomial for every limb of this ciphertext), 16 coefficients per block
+    for (uint32_t b = threadIdx.x; b < nb16; b += blockDim.x) {
+      rng.block(ctr0 | b, 0, r);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) sm[j * nb16 + b] = signed_to_mod(ternary_from_bits(r[j]), q);
     }
     __syncthreads();
     ntt_forward_smem(sm, w, wp, q, log_n);
@@ -288,20 +305,25 @@ __global__ void __launch_bounds__(kNttThreads, 1) encrypt_kernel(const __grid_co
     }
     __syncthreads();
     // pass 2: c0 += NTT(m + e0)
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) {
-      rng((uint64_t)ct * N + i, 0, r);
-      uint64_t t = signed_to_mod(gaussian_from_bits(r[1], r[2], kSigma), q);
-      if (i % gap == 0) t = d_add(t, double_to_mod(m[i / gap], q, two40), q);
-      sm[i] = t;
+    for (uint32_t b = threadIdx.x; b < nb8; b += blockDim.x) {
+      rng.block(ctr0 | b, 1, r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t i = j * nb8 + b;
+        uint64_t t = signed_to_mod(gaussian_from_bits(r[2 * j], r[2 * j + 1], kSigma), q);
+        if (i % gap == 0) t = d_add(t, double_to_mod(m[i / gap], q, two40), q);
+        sm[i] = t;
+      }
     }
     __syncthreads();
     ntt_forward_smem(sm, w, wp, q, log_n);
     for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) c0[i] = d_add(c0[i], sm[i], q);
     __syncthreads();
     // pass 3: c1 += NTT(e1)
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) {
-      rng((uint64_t)ct * N + i, 1, r);
-      sm[i] = signed_to_mod(gaussian_from_bits(r[0], r[1], kSigma), q);
+    for (uint32_t b = threadIdx.x; b < nb8; b += blockDim.x) {
+      rng.block(ctr0 | b, 2, r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sm[j * nb8 + b] = signed_to_mod(gaussian_from_bits(r[2 * j], r[2 * j + 1], kSigma), q);
     }
     __syncthreads();
     ntt_forward_smem(sm, w, wp, q, log_n);
@@ -477,14 +499,19 @@ extern "C" int mfl_ckks_encode(const mfl_ckks_ctx* ctx, const double* values, si
 }
 
 extern "C" int mfl_ckks_encrypt(const mfl_ckks_ctx* ctx, const double* coeffs, uint32_t n_ct, uint32_t slots,
-                                const uint64_t* pk, const uint64_t* pk_shoup, uint64_t seed, uint64_t* ct_out, void* stream) {
+                                const uint64_t* pk, const uint64_t* pk_shoup, const uint32_t* key256, uint64_t* ct_out,
+                                void* stream) {
   if (int rc = check_ctx(ctx)) return rc;
+  MFL_ARG(key256 != nullptr, "ckks_encrypt: a 256-bit key (8 host words from the OS entropy source) is required");
+  MFL_ARG(ctx->log_n >= 4 && ctx->log_n <= 19, "ckks_encrypt: ring dimension 2^%d outside the block addressing", ctx->log_n);
   if (n_ct == 0) return 0;
+  ChaChaKey key;
+  for (int i = 0; i < 8; ++i) key.k[i] = key256[i];
   const size_t smem = sizeof(uint64_t) << ctx->log_n;
   if (int rc = allow_smem(encrypt_kernel, smem)) return rc;
   Ctx cx{*ctx};
   const int blocks = (int)std::min<size_t>((size_t)n_ct * ctx->n_limbs, (size_t)sm_count());
-  encrypt_kernel<<<blocks, kNttThreads, smem, (cudaStream_t)stream>>>(cx, coeffs, slots, pk, pk_shoup, seed, ct_out, n_ct);
+  encrypt_kernel<<<blocks, kNttThreads, smem, (cudaStream_t)stream>>>(cx, coeffs, slots, pk, pk_shoup, key, ct_out, n_ct);
   return check(cudaGetLastError(), "encrypt_kernel launch");
 }
 

@@ -330,9 +330,12 @@ int mfl_ckks_ntt(const mfl_ckks_ctx* ctx, uint64_t* rows, size_t n_rows, int inv
 int mfl_ckks_encode(const mfl_ckks_ctx* ctx, const double* values, size_t n_values, uint32_t slots, double scale,
                     const double* ksi_pows /* (2N+1) x {cos,sin} */, const uint32_t* rot_group, double* coeffs,
                     void* stream);
-/* K7: RLWE public-key encryption of encoded coefficients; pk = [2][limb][N] with Shoup companions. */
+/* K7: RLWE public-key encryption of encoded coefficients; pk = [2][limb][N] with Shoup companions.  key256: eight
+ * HOST words = a fresh 256-bit key from the OS entropy source for every call; the kernel expands it with the ChaCha20
+ * block function (one stream each for the ternary mask u and the two error polynomials). */
 int mfl_ckks_encrypt(const mfl_ckks_ctx* ctx, const double* coeffs, uint32_t n_ct, uint32_t slots,
-                     const uint64_t* pk, const uint64_t* pk_shoup, uint64_t seed, uint64_t* ct_out, void* stream);
+                     const uint64_t* pk, const uint64_t* pk_shoup, const uint32_t* key256, uint64_t* ct_out,
+                     void* stream);
 /* K7: c0 + c1*s per limb, inverse NTT -> residues[ct][limb][N] (coefficient form). */
 int mfl_ckks_decrypt(const mfl_ckks_ctx* ctx, const uint64_t* ct, uint32_t n_ct, const uint64_t* sk,
                      const uint64_t* sk_shoup, uint64_t* residues, void* stream);

@@ -39,7 +39,7 @@ def _bind():
     P = C.POINTER
     L.mfl_ckks_ntt.argtypes = [P(_Ctx), vp, sz, i, vp]
     L.mfl_ckks_encode.argtypes = [P(_Ctx), vp, sz, u32, d, vp, vp, vp, vp]
-    L.mfl_ckks_encrypt.argtypes = [P(_Ctx), vp, u32, u32, vp, vp, u64, vp, vp]
+    L.mfl_ckks_encrypt.argtypes = [P(_Ctx), vp, u32, u32, vp, vp, P(u32), vp, vp]
     L.mfl_ckks_decrypt.argtypes = [P(_Ctx), vp, u32, vp, vp, vp, vp]
     L.mfl_ckks_decode.argtypes = [P(_Ctx), vp, u32, u32, d, P(u64), vp, vp, vp, sz, vp]
     L.mfl_ckks_weighted_sum.argtypes = [P(_Ctx), P(vp), P(u64), P(u64), i, sz, vp, vp]
@@ -164,10 +164,11 @@ class GpuCKKS:
         _lib.check(self.L.mfl_ckks_encode(C.byref(self.ctx), v.data_ptr(), n, self.slots, self.scale,
                                           self.ksi.data_ptr(), self.rot.data_ptr(), coeffs.data_ptr(), st),
                    "mfl_ckks_encode")
-        if not seed:
-            seed = int.from_bytes(os.urandom(8), "little") | 1
+        # 256-bit ChaCha20 key per call: OS entropy, or (tests only) a fixed expansion of ``seed`` for reproducibility
+        raw = os.urandom(32) if not seed else int(seed).to_bytes(32, "little", signed=False)
+        key = (C.c_uint32 * 8).from_buffer_copy(raw)
         _lib.check(self.L.mfl_ckks_encrypt(C.byref(self.ctx), coeffs.data_ptr(), n_ct, self.slots, self.pk.data_ptr(),
-                                           self.pk_shoup.data_ptr(), seed, out.data_ptr(), st), "mfl_ckks_encrypt")
+                                           self.pk_shoup.data_ptr(), key, out.data_ptr(), st), "mfl_ckks_encrypt")
         return out
 
     def decrypt_device(self, ct_words: torch.Tensor, n_values: int, scale: float = None, n_limbs: int = None):
