@@ -40,11 +40,20 @@ def main():
         a = torch.randn(m, k, device="cuda").to(torch.bfloat16)
         b = torch.randn(n, k, device="cuda").to(torch.bfloat16)
         out = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
-        t_ours = timeit(lambda: gemm.gemm_nt(a, b, out=out))
+        gemm.set_pair_mode(-1)
+        t_ours = timeit(lambda: gemm.gemm_nt(a, b, out=out))        # default dispatch
+        gemm.set_pair_mode(0)
+        t_single = timeit(lambda: gemm.gemm_nt(a, b, out=out))      # single-CTA kernel (cta_group::1)
+        gemm.set_pair_mode(1)
+        t_pair = timeit(lambda: gemm.gemm_nt(a, b, out=out))        # CTA-pair kernel where legal (cta_group::2)
+        gemm.set_pair_mode(-1)
         t_cublas = timeit(lambda: torch.matmul(a, b.t(), out=out))
         fl = 2.0 * m * n * k
         rows.append({"m": m, "n": n, "k": k, "ours_ms": t_ours, "cublas_ms": t_cublas,
+                     "single_cta_ms": t_single, "cta_pair_ms": t_pair,
                      "ours_tflops": fl / t_ours / 1e9, "cublas_tflops": fl / t_cublas / 1e9,
+                     "single_cta_tflops": fl / t_single / 1e9, "cta_pair_tflops": fl / t_pair / 1e9,
+                     "ours_over_cublas": t_cublas / t_ours,
                      "ours_fraction_of_measured_peak": fl / t_ours / 1e9 / peak})
     print(json.dumps({"bench": "gemm_bench", "measured_bf16_peak_tflops": peak, "results": rows}))
 

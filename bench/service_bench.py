@@ -84,7 +84,8 @@ def service_rounds(device_fabric=True, rounds=12, warmup=4, local_steps=4, batch
     factory, shape = (zoo.ResNet18, (3, 32, 32)) if model == "resnet18" else (zoo.FashionMnistMLP, (1, 28, 28))
     n = batch * local_steps   # one epoch = local_steps batches
     with tempfile.TemporaryDirectory() as tmp:
-        os.environ["METISFL_SNAPSHOT_DIR"] = os.path.join(tmp, "snap")
+        # no snapshot directory: with one, the controller pulls the community model's bytes off the device every round
+        os.environ.pop("METISFL_SNAPSHOT_DIR", None)
         torch.manual_seed(0)
         s = DriverSession(FederationEnvironment(d), factory(), _recipe(n, 1, shape), None, _recipe(batch, 3, shape),
                           working_dir=os.path.join(tmp, "w"), launcher="inprocess", banner=False,

@@ -26,6 +26,7 @@
 
 #include "common.cuh"
 #include "tcgen05_common.cuh"
+#include "gemm_2sm.cuh"
 
 namespace mfl {
 namespace gemm {
@@ -90,15 +91,6 @@ __device__ __forceinline__ void tma_store_5d(const CUtensorMap* map, const void*
                                              int c4) {
   asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
                ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4) : "memory");
-}
-
-template <int ACT> __device__ __forceinline__ float apply_act(float x) {
-  if constexpr (ACT == 1) return fmaxf(x, 0.f);
-  if constexpr (ACT == 2) {
-    const float u = 0.7978845608f * (x + 0.044715f * x * x * x);
-    return 0.5f * x * (1.f + tanhf(u));
-  }
-  return x;
 }
 
 template <int BN, int ACT, bool C_FP32>
@@ -475,6 +467,88 @@ static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int6
                           int64_t ldb, int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act,
                           void* stream);
 
+namespace mfl { namespace gemm {
+// ---- CTA-pair variant (gemm_2sm.cuh) ----------------------------------------------------------------------------
+// How many 2-CTA clusters of this kernel the device runs at once (GPCs with an odd SM count leave an SM unpaired).
+template <typename K> static int max_pair_clusters(K kern, size_t smem) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * (unsigned)(sm_count() / 2));
+  cfg.blockDim = dim3(gemm2::kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    n = sm_count() / 2;
+  }
+  return std::min(n, sm_count() / 2);
+}
+
+static int g_pair_mode = [] { const char* e = getenv("MFL_GEMM_2SM"); return e ? atoi(e) : -1; }();
+
+static int pair_cluster_estimate() { return std::max(1, sm_count() / 2); }
+
+// Tile width of the pair kernel for this problem, or 0 to stay on the single-CTA kernel.  MFL_GEMM_2SM=0 disables,
+// =1 forces it wherever it is legal.  Cost model: waves over the resident clusters x (tile width + a fixed per-tile
+// cost); BN = 192 exists for shapes like N = 3072 whose 256-wide tiling ends in a nearly empty wave.
+static int pair_tile_width(int m, int n, int k, bool b_mn) {
+  const int mode = g_pair_mode;
+  if (mode == 0) return 0;
+  if (m < 2 * kBlockM || n < 128 || k < kBlockK) return 0;
+  const int clusters = pair_cluster_estimate();
+  const int tiles_m = (m + 2 * kBlockM - 1) / (2 * kBlockM);
+  if (mode != 1 && tiles_m * ((n + 127) / 128) < clusters / 2) return 0;  // too small to fill the machine in pairs
+  int best = 0;
+  long best_cost = 0;
+  for (int bn : {256, 192, 128}) {
+    if (bn == 192 && b_mn) continue;  // an MN-major B half is made of 64-column boxes
+    if (n < bn && bn != 128) continue;
+    const long tiles = (long)tiles_m * ((n + bn - 1) / bn);
+    const long cost = ((tiles + clusters - 1) / clusters) * (bn + 32);
+    if (!best || cost < best_cost) { best = bn; best_cost = cost; }
+  }
+  return best;
+}
+
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const gemm2::Params& pp,
+                            int bn, int act, bool c32, cudaStream_t st) {
+  const int tiles = ((pp.N + bn - 1) / bn) * ((pp.M + 2 * kBlockM - 1) / (2 * kBlockM));
+  int rc = 0;
+#define MFL_GEMM2_LAUNCH(BN_, ACT_, F32_)                                                                           \
+  do {                                                                                                              \
+    auto kern = gemm2::gemm2sm_kernel<BN_, ACT_, F32_>;                                                             \
+    static int clusters = 0;                                                                                        \
+    rc = check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,                              \
+                                    (int)gemm2::Cfg<BN_>::kSmemBytes), "cudaFuncSetAttribute(gemm2 smem)");         \
+    if (!rc && !clusters) clusters = max_pair_clusters(kern, gemm2::Cfg<BN_>::kSmemBytes);                          \
+    if (!rc) kern<<<2 * std::min(tiles, clusters), gemm2::kThreads, gemm2::Cfg<BN_>::kSmemBytes, st>>>(ta, tb, tc, pp); \
+  } while (0)
+#define MFL_GEMM2_ACT(BN_, F32_)                                        \
+  do {                                                                  \
+    if (act == 0) MFL_GEMM2_LAUNCH(BN_, 0, F32_);                       \
+    else if (act == 1) MFL_GEMM2_LAUNCH(BN_, 1, F32_);                  \
+    else MFL_GEMM2_LAUNCH(BN_, 2, F32_);                                \
+  } while (0)
+  if (bn == 256) { if (c32) MFL_GEMM2_ACT(256, true); else MFL_GEMM2_ACT(256, false); }
+  else if (bn == 192) { if (c32) MFL_GEMM2_ACT(192, true); else MFL_GEMM2_ACT(192, false); }
+  else { if (c32) MFL_GEMM2_ACT(128, true); else MFL_GEMM2_ACT(128, false); }
+#undef MFL_GEMM2_ACT
+#undef MFL_GEMM2_LAUNCH
+  if (rc) return rc;
+  return check(cudaGetLastError(), "gemm2sm_kernel launch");
+}
+}}  // namespace mfl::gemm
+
+// -1 automatic (default, or MFL_GEMM_2SM from the environment), 0 never use the CTA-pair kernel, 1 wherever it is legal
+extern "C" int mfl_gemm_set_pair_mode(int mode) {
+  const int old = mfl::gemm::g_pair_mode;
+  mfl::gemm::g_pair_mode = mode < 0 ? -1 : (mode ? 1 : 0);
+  return old;
+}
+
 extern "C" int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, const void* b, int64_t ldb,
                              const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream) {
   return gemm_bf16_impl(c, c_dtype, ldc, a, lda, 0, b, ldb, 0, bias, bias_dtype, m, n, k, act, stream);
@@ -501,6 +575,19 @@ static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int6
           "gemm: A and B need 16-byte aligned bases and row pitches that are multiples of 8 elements (TMA)");
   MFL_ARG(act >= 0 && act <= 2, "gemm: unknown activation %d", act);
   CUtensorMap ta, tb, tc;
+  if (const int pbn = pair_tile_width(m, n, k, b_mn != 0)) {  // CTA pairs (tcgen05.mma.cta_group::2)
+    if (int rc = a_mn ? make_map_mn(&ta, a, m, k, lda) : make_map(&ta, a, m, k, lda, kBlockM)) return rc;
+    if (int rc = b_mn ? make_map_mn(&tb, b, n, k, ldb) : make_map(&tb, b, n, k, ldb, pbn / 2)) return rc;
+    const bool c32p = c_dtype == MFL_FLOAT32;
+    const bool tma_store_p = ((uintptr_t)c & 15) == 0 && (ldc * (c32p ? 4 : 2)) % 16 == 0;
+    if (tma_store_p) {
+      if (int rc = make_map(&tc, c, m, n, ldc, 32, c32p)) return rc;
+    } else {
+      tc = ta;
+    }
+    gemm2::Params pp{c, bias, ldc, m, n, k, bias_dtype == MFL_FLOAT32, tma_store_p, a_mn ? 1 : 0, b_mn ? 1 : 0};
+    return launch_gemm_pair(ta, tb, tc, pp, pbn, act, c32p, (cudaStream_t)stream);
+  }
   const int bn = n > 128 ? 256 : (n > 64 ? 128 : 64);
   if (int rc = a_mn ? make_map_mn(&ta, a, m, k, lda) : make_map(&ta, a, m, k, lda, kBlockM)) return rc;
   if (int rc = b_mn ? make_map_mn(&tb, b, n, k, ldb) : make_map(&tb, b, n, k, ldb, bn)) return rc;

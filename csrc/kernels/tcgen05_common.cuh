@@ -126,5 +126,15 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void*
                ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
 }
 
+// epilogue activations: 0 none, 1 relu, 2 gelu (tanh form)
+template <int ACT> __device__ __forceinline__ float apply_act(float x) {
+  if constexpr (ACT == 1) return fmaxf(x, 0.f);
+  if constexpr (ACT == 2) {
+    const float u = 0.7978845608f * (x + 0.044715f * x * x * x);
+    return 0.5f * x * (1.f + tanhf(u));
+  }
+  return x;
+}
+
 }  // namespace gemm
 }  // namespace mfl

@@ -196,6 +196,10 @@ int mfl_gemm_bf16(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda,
  * and the instruction descriptor transposes in the tensor core. */
 int mfl_gemm_bf16_ex(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb,
                      int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act, void* stream);
+/* Large problems (m >= 256, enough 256 x BN tiles to occupy the SM pairs) run on a CTA-PAIR kernel
+ * (csrc/kernels/gemm_2sm.cuh): tcgen05.mma.cta_group::2, M = 256 per instruction, each CTA stages its half of B.
+ * mode: -1 automatic (default; env MFL_GEMM_2SM), 0 never, 1 wherever legal.  Returns the previous mode. */
+int mfl_gemm_set_pair_mode(int mode);
 
 /* ---- K11: implicit-GEMM convolution forward on the same tcgen05 pipeline; the A operand is gathered by
  * im2col-mode TMA (cuTensorMapEncodeIm2col), never materialised.  NHWC bf16: x[n,h,w,c], w[k,r,s,c],

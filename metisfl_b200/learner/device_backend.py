@@ -129,6 +129,11 @@ class DeviceBackend:
         self._comm_lock = threading.Lock()   # community buffer: aggregation writes, evaluation / install read
         self._installed_bytes_iteration = None
         self._known_version = 0
+        self._ds_cache = {}       # pinned host copies + gather buffers of the array datasets (models/torch_model_ops._Batches)
+        self._eval_cache = {}     # (id(dataset), batch size) -> device-resident evaluation batches
+        self._eval_cache_bytes = 0
+        self._eval_graphs = {}    # batch signature -> captured forward + metric accumulation
+        self._eval_acc = torch.zeros(2, dtype=torch.float32, device=self.device)   # [sum of loss * n, correct]
 
     # -- membership -----------------------------------------------------------------------------------------------
     def membership_pb(self):
@@ -167,7 +172,7 @@ class DeviceBackend:
         batch_size = hyperparameters_pb.batch_size or 32
         total_steps = max(1, int(learning_task_pb.num_local_updates))
         src = _Batches(train_dataset, batch_size, shuffle=True, pin=self.device.type == "cuda",
-                       seed=learning_task_pb.global_iteration)
+                       seed=learning_task_pb.global_iteration, cache=self._ds_cache)
         spe = max(1, src.steps_per_epoch)
         batches = []
         while len(batches) < total_steps:
@@ -186,6 +191,8 @@ class DeviceBackend:
                                  min_version=int(ref.version) if (ref is not None and eng.async_rule) else None,
                                  cancel=cancel_event)
         if loss is None and (cancel_event is not None and cancel_event.is_set()):
+            if cuda:   # copies out of the pinned gather buffer may still be in flight; the next task rewrites it
+                torch.cuda.current_stream(self.device).synchronize()
             return None
         if cuda:
             t1.record()
@@ -233,29 +240,92 @@ class DeviceBackend:
             if ds is None or not ds.get_size():
                 out[code] = {}
                 continue
-            loss_sum = torch.zeros((), device=self.device)
-            correct = torch.zeros((), device=self.device)
+            self._eval_acc.zero_()
             seen, classification = 0, False
-            for x, y in _Batches(ds, batch_size or 100, shuffle=False, pin=self.device.type == "cuda"):
-                x = x.to(self.device, non_blocking=True)
-                y = y.to(self.device, non_blocking=True)
-                if x.is_floating_point():
-                    x = x.to(self.eval_arena.model_dtype)
-                    if x.dim() == 4 and self.device.type == "cuda":
-                        x = x.contiguous(memory_format=torch.channels_last)
-                logits = module(x)
-                loss_sum += self.loss_fn(logits, y).float() * x.shape[0]
-                if logits.dim() == 2 and not y.is_floating_point():
-                    classification = True
-                    correct += (logits.argmax(dim=-1) == y).sum()
+            for x, y in self._eval_batches(ds, batch_size or 100):
+                classification = self._eval_step(module, x, y) or classification
                 seen += x.shape[0]
-            res = {"loss": float(loss_sum) / max(1, seen)}
+            acc = self._eval_acc.tolist()   # the one host read-back per split
+            res = {"loss": acc[0] / max(1, seen)}
             if classification:
-                res["accuracy"] = float(correct) / max(1, seen)
+                res["accuracy"] = acc[1] / max(1, seen)
             if metrics:
                 res = {k: v for k, v in res.items() if k in metrics or k == "loss"} or res
             out[code] = res
         return out
+
+    EVAL_CACHE_LIMIT_BYTES = 8 << 30   # evaluation splits up to this total stay resident in HBM between rounds
+
+    def _eval_batches(self, ds, batch_size):
+        """Evaluation batches on the device, in the model's dtype / memory format.  The splits of a learner do not
+        change between rounds (``learner.py`` loads them once), so they are uploaded once and kept."""
+        key = (id(ds), batch_size)
+        hit = self._eval_cache.get(key)
+        if hit is not None:
+            return hit[1]
+        cuda = self.device.type == "cuda"
+        batches, nbytes = [], 0
+        for x, y in _Batches(ds, batch_size, shuffle=False, pin=cuda, cache=self._ds_cache):
+            x = x.to(self.device, non_blocking=True)
+            y = y.to(self.device, non_blocking=True)
+            if x.is_floating_point():
+                x = x.to(self.eval_arena.model_dtype)
+                if x.dim() == 4 and cuda:
+                    x = x.contiguous(memory_format=torch.channels_last)
+            batches.append((x, y))
+            nbytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+        if cuda and self._eval_cache_bytes + nbytes <= self.EVAL_CACHE_LIMIT_BYTES:
+            self._eval_cache[key] = (ds, batches)   # holding ``ds`` keeps id(ds) from being reused
+            self._eval_cache_bytes += nbytes
+        return batches
+
+    def _eval_body(self, module, x, y) -> bool:
+        logits = module(x)
+        self._eval_acc[0] += self.loss_fn(logits, y).float() * x.shape[0]
+        if logits.dim() == 2 and not y.is_floating_point():
+            self._eval_acc[1] += (logits.argmax(dim=-1) == y).sum()
+            return True
+        return False
+
+    def _eval_step(self, module, x, y) -> bool:
+        """One evaluation batch: forward + loss / accuracy accumulation on the device.  On CUDA the step is captured
+        once per batch signature and replayed (a ResNet-18 forward is ~60 launches; eagerly the host is the bottleneck
+        and it competes with the training thread for the interpreter)."""
+        if self.device.type != "cuda":
+            return self._eval_body(module, x, y)
+        key = (tuple(x.shape), x.dtype, tuple(y.shape), y.dtype)
+        ent = self._eval_graphs.get(key)
+        if ent is None:
+            ent = {"graph": None}
+            try:
+                sx, sy = torch.empty_like(x), torch.empty_like(y)
+                sx.copy_(x)
+                sy.copy_(y)
+                saved = self._eval_acc.clone()   # warm-up passes add to the accumulator: put it back afterwards
+                cur = torch.cuda.current_stream(self.device)
+                side = torch.cuda.Stream(device=self.device)
+                side.wait_stream(cur)
+                with torch.cuda.stream(side):
+                    for _ in range(2):   # lazy initialisations, cuDNN algorithm selection
+                        cls = self._eval_body(module, sx, sy)
+                cur.wait_stream(side)
+                g = torch.cuda.CUDAGraph()
+                # thread_local: the training thread keeps launching and allocating while this thread captures
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    self._eval_body(module, sx, sy)
+                self._eval_acc.copy_(saved)
+                ent = {"graph": g, "x": sx, "y": sy, "cls": cls}
+            except Exception as e:   # capture is an optimisation: fall back to eager evaluation for this signature
+                from metisfl_b200.utils.metis_logger import MetisLogger
+                MetisLogger.warning("evaluation graph capture failed (%r); evaluating eagerly", e)
+                torch.cuda.synchronize(self.device)
+            self._eval_graphs[key] = ent
+        if ent["graph"] is None:
+            return self._eval_body(module, x, y)
+        ent["x"].copy_(x, non_blocking=True)
+        ent["y"].copy_(y, non_blocking=True)
+        ent["graph"].replay()
+        return ent["cls"]
 
     # -- aggregation (commanded by the controller) ------------------------------------------------------------------
     @_on_device

@@ -75,10 +75,14 @@ def _as_tensor(a):
 
 
 class _Batches:
-    """Uniform batch iterator over (x, y) arrays/tensors or a DataLoader; pins host memory for CUDA."""
+    """Uniform batch iterator over (x, y) arrays/tensors or a DataLoader; pins host memory for CUDA.
 
-    def __init__(self, dataset: ModelDataset, batch_size: int, shuffle: bool, pin: bool, seed: int = 0):
+    ``cache`` (a dict owned by the caller, one per learner) keeps the pinned copy of an array dataset and a pinned
+    gather buffer across tasks, so a task costs one host-side gather instead of a fresh pin + pageable H2D copies."""
+
+    def __init__(self, dataset: ModelDataset, batch_size: int, shuffle: bool, pin: bool, seed: int = 0, cache=None):
         self.loader = None
+        self.gather = None
         x = dataset.get_x()
         if isinstance(x, torch.utils.data.DataLoader):
             self.loader = x
@@ -89,12 +93,24 @@ class _Batches:
             self.n = len(x)
             self.batch_size = batch_size
         else:
-            self.x, self.y = _as_tensor(x), _as_tensor(dataset.get_y())
-            if self.y is not None and self.y.dtype in (torch.int32, torch.int16, torch.uint8, torch.int8):
-                self.y = self.y.long()
-            if pin and torch.cuda.is_available():
-                self.x = self.x.pin_memory()
-                self.y = self.y.pin_memory() if self.y is not None else None
+            pin = bool(pin and torch.cuda.is_available())
+            ent = cache.get((id(dataset), pin)) if cache is not None else None
+            if ent is None:
+                tx, ty = _as_tensor(x), _as_tensor(dataset.get_y())
+                if ty is not None and ty.dtype in (torch.int32, torch.int16, torch.uint8, torch.int8):
+                    ty = ty.long()
+                if pin:
+                    tx = tx.pin_memory()
+                    ty = ty.pin_memory() if ty is not None else None
+                ent = {"x": tx, "y": ty, "gx": None, "gy": None, "ref": dataset}  # ref keeps id(dataset) unique
+                if cache is not None:
+                    cache[(id(dataset), pin)] = ent
+            self.x, self.y = ent["x"], ent["y"]
+            if shuffle and pin and cache is not None:
+                if ent["gx"] is None:
+                    ent["gx"] = torch.empty_like(self.x).pin_memory()
+                    ent["gy"] = torch.empty_like(self.y).pin_memory() if self.y is not None else None
+                self.gather = (ent["gx"], ent["gy"])
             self.n = self.x.shape[0]
             self.batch_size = max(1, min(batch_size, self.n))
         self.shuffle = shuffle
@@ -110,7 +126,11 @@ class _Batches:
             return
         if self.shuffle:
             perm = torch.randperm(self.n, generator=self.gen)
-            x, y = self.x[perm], self.y[perm] if self.y is not None else None
+            if self.gather is not None:   # shuffled rows land in pinned memory: the H2D copies stay asynchronous
+                x = torch.index_select(self.x, 0, perm, out=self.gather[0])
+                y = torch.index_select(self.y, 0, perm, out=self.gather[1]) if self.y is not None else None
+            else:
+                x, y = self.x[perm], self.y[perm] if self.y is not None else None
         else:
             x, y = self.x, self.y
         for i in range(0, self.n, self.batch_size):

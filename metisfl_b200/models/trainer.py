@@ -102,7 +102,8 @@ class LocalTrainer:
                 g.zero_()
         self._graph = torch.cuda.CUDAGraph()
         launches0 = _lib.LAUNCHES
-        with torch.cuda.graph(self._graph):
+        # thread_local: a learner's evaluation thread may be launching / allocating on this device at the same time
+        with torch.cuda.graph(self._graph, capture_error_mode="thread_local"):
             self._static_loss = self._fwd_bwd(self._static_x, self._static_y)
         self.graph_launches = _lib.LAUNCHES - launches0  # library kernels (K10 / K14 ...) every replay launches
         # undo what warm-up and capture did to BatchNorm statistics etc.

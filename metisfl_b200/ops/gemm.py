@@ -28,10 +28,17 @@ def _bind():
         vp, i, i64 = C.c_void_p, C.c_int, C.c_int64
         L.mfl_gemm_bf16.argtypes = [vp, i, i64, vp, i64, vp, i64, vp, i, i, i, i, i, vp]
         L.mfl_gemm_bf16_ex.argtypes = [vp, i, i64, vp, i64, i, vp, i64, i, vp, i, i, i, i, i, vp]
+        L.mfl_gemm_set_pair_mode.argtypes = [i]
         L.mfl_colsum_slices.argtypes = [i]
         L.mfl_colsum_bf16.argtypes = [vp, vp, i64, i, i, vp]
         _BOUND = True
     return L
+
+
+def set_pair_mode(mode: int) -> int:
+    """CTA-pair kernel (``tcgen05.mma.cta_group::2``) selection: -1 automatic, 0 never, 1 wherever the shape allows.
+    Returns the previous mode."""
+    return _bind().mfl_gemm_set_pair_mode(int(mode))
 
 
 def supported(x: torch.Tensor, w: torch.Tensor) -> bool:

@@ -34,6 +34,47 @@ def test_gemm_matches_fp32_reference(m, n, k, act):
     torch.testing.assert_close(y32, _ref(a, b, None, None), atol=2e-3, rtol=2e-3)
 
 
+@pytest.fixture
+def pair_kernel():
+    from metisfl_b200.ops import gemm
+    old = gemm.set_pair_mode(1)
+    yield
+    gemm.set_pair_mode(old)
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 256, 64), (256, 128, 512), (512, 384, 1024), (300, 200, 72), (1000, 130, 40),
+                                   (2048, 3072, 1024), (4096, 1024, 4096), (640, 1000, 264)])
+@pytest.mark.parametrize("act", [None, "gelu"])
+def test_pair_kernel_matches_fp32_reference(pair_kernel, m, n, k, act):
+    """The CTA-pair kernel (cta_group::2, M = 256 per instruction) forced on: ragged M / N / K, all three tile widths
+    (256, 192 for N = 3072, 128), bias + activation, bf16 and fp32 output, and the same result as the single-CTA kernel."""
+    from metisfl_b200.ops import gemm
+    g = torch.Generator(device="cpu").manual_seed(m * 5 + n * 3 + k)
+    a = (torch.randn(m, k, generator=g) / k ** 0.5).to(torch.bfloat16).cuda()
+    b = torch.randn(n, k, generator=g).to(torch.bfloat16).cuda()
+    bias = torch.randn(n, generator=g).to(torch.bfloat16).cuda()
+    y = gemm.gemm_nt(a, b, bias, act)
+    torch.testing.assert_close(y.float(), _ref(a, b, bias, act), atol=3e-2, rtol=3e-2)
+    y32 = gemm.gemm_nt(a, b, None, None, out_dtype=torch.float32)
+    torch.testing.assert_close(y32, _ref(a, b, None, None), atol=2e-3, rtol=2e-3)
+    gemm.set_pair_mode(0)
+    y1 = gemm.gemm_nt(a, b, None, None, out_dtype=torch.float32)
+    gemm.set_pair_mode(1)
+    torch.testing.assert_close(y1, y32, atol=1e-4, rtol=1e-4)   # same reduction order per element
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 128, 64), (384, 320, 192), (4096, 1024, 1024), (1024, 3072, 1024)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+def test_pair_kernel_mn_major_operands(pair_kernel, m, n, k, a_mn, b_mn):
+    from metisfl_b200.ops import gemm
+    g = torch.Generator().manual_seed(m + n + k)
+    a = torch.randn(m, k, generator=g).to(torch.bfloat16).cuda()
+    b = torch.randn(n, k, generator=g).to(torch.bfloat16).cuda()
+    ref = a.float() @ b.float().t()
+    out = gemm.gemm_ex(a.t().contiguous() if a_mn else a, b.t().contiguous() if b_mn else b, a_mn, b_mn)
+    torch.testing.assert_close(out.float(), ref, atol=k ** 0.5 * 3e-2, rtol=2e-2)
+
+
 def test_gemm_fp32_bias_and_strided_inputs():
     from metisfl_b200.ops import gemm
     big = torch.randn(300, 512, device="cuda").to(torch.bfloat16)
