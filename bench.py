@@ -365,9 +365,16 @@ def main():
             with contextlib.redirect_stdout(io.StringIO()):
                 service = service_rounds(True, rounds=max(8, min(args.steps, 20)), warmup=4, local_steps=S, batch=B,
                                          cuda_device=local_rank)
+                host = service_rounds(False, rounds=6, warmup=2, local_steps=S, batch=B, cuda_device=local_rank)
             if service.get("ms_per_round"):
                 service["value"] = n_params / (service["ms_per_round"] * 1e-3)
                 service["unit"] = "params/s"
+            # the reference's architecture on this box: same learner, same GPU, but models travel as protobuf bytes
+            # through the controller and are averaged on the host
+            service["host_path_ms_per_round"] = host.get("ms_per_round")
+            service["host_path_controller_rx_model_bytes"] = host.get("controller_rx_model_bytes")
+            if service.get("ms_per_round") and host.get("ms_per_round"):
+                service["device_path_speedup_over_host_path"] = host["ms_per_round"] / service["ms_per_round"]
         except Exception as e:  # the headline must not die with the side measurement
             service = {"error": repr(e)[:300]}
     if rank == 0:

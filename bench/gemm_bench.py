@@ -26,7 +26,45 @@ def timeit(fn, iters=20, warmup=5):
     return tot / iters
 
 
+def gpt2_shapes(tokens=4096, d=1024, vocab=50304):
+    """Every GEMM of one GPT-2-medium training step (per layer x 24, head x 1): forward y = x W^T, data gradient
+    dx = dy W (B read MN-major), weight gradient dW = dy^T x (both operands MN-major)."""
+    out = []
+    for name, n_out, n_in, reps in (("qkv", 3 * d, d, 24), ("proj", d, d, 24), ("fc", 4 * d, d, 24), ("out", d, 4 * d, 24),
+                                    ("head", vocab, d, 1)):
+        out.append((name + ".fwd", tokens, n_out, n_in, False, False, reps))
+        out.append((name + ".dgrad", tokens, n_in, n_out, False, True, reps))
+        out.append((name + ".wgrad", n_out, n_in, tokens, True, True, reps))
+    return out
+
+
+def gpt2_main():
+    rows, tot = [], {"ours": 0.0, "cublas": 0.0, "single": 0.0}
+    for name, m, n, k, a_mn, b_mn, reps in gpt2_shapes():
+        a = torch.randn((k, m) if a_mn else (m, k), device="cuda").to(torch.bfloat16)
+        b = torch.randn((k, n) if b_mn else (n, k), device="cuda").to(torch.bfloat16)
+        ref_a = a.t() if a_mn else a
+        ref_b = b if b_mn else b.t()
+        gemm.set_pair_mode(-1)
+        t_ours = timeit(lambda: gemm.gemm_ex(a, b, a_mn, b_mn), iters=10, warmup=3)
+        gemm.set_pair_mode(0)
+        t_single = timeit(lambda: gemm.gemm_ex(a, b, a_mn, b_mn), iters=10, warmup=3)
+        gemm.set_pair_mode(-1)
+        t_cublas = timeit(lambda: torch.matmul(ref_a, ref_b), iters=10, warmup=3)
+        fl = 2.0 * m * n * k
+        rows.append({"gemm": name, "m": m, "n": n, "k": k, "a_mn": a_mn, "b_mn": b_mn, "per_step": reps,
+                     "ours_us": t_ours * 1e3, "single_cta_us": t_single * 1e3, "cublas_us": t_cublas * 1e3,
+                     "ours_tflops": fl / t_ours / 1e9, "cublas_tflops": fl / t_cublas / 1e9,
+                     "ours_over_cublas": t_cublas / t_ours})
+        tot["ours"] += t_ours * reps
+        tot["cublas"] += t_cublas * reps
+        tot["single"] += t_single * reps
+    print(json.dumps({"bench": "gemm_bench --gpt2", "step_gemm_ms": tot, "results": rows}))
+
+
 def main():
+    if "--gpt2" in sys.argv:
+        return gpt2_main()
     peak = 1642.2
     try:
         peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),

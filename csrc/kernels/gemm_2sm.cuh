@@ -14,7 +14,7 @@
 //   full[s]       even CTA only, count 1: the even CTA's producer arms it with the bytes of BOTH CTAs' stage
 //   empty[s]      both CTAs, count 1: tcgen05.commit multicast to the pair once the MMAs have read stage s
 //   tmem_full[b]  both CTAs, count 1: tcgen05.commit multicast when accumulator b is complete
-//   tmem_empty[b] even CTA only, count 256: every epilogue thread of the pair arrives (remote arrive for the odd CTA)
+//   tmem_empty[b] even CTA only, count 8: one lane of every epilogue warp of the pair arrives (remotely from the odd CTA)
 // Tiles are walked in bands of kGroupM tile rows so that the clusters running at the same time share A and B panels
 // in L2.
 #pragma once
@@ -99,7 +99,9 @@ __device__ __forceinline__ void umma2_commit_pair(uint64_t* bar) {
                ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+  // default semantics (no .release.cluster): the arrival orders nothing but itself; the data it stands for
+  // (tcgen05.ld results) was already waited for, and a cluster-scope release costs a MEMBAR.GPU per arriving thread
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
 }
 
 // work item -> tile coordinates: bands of kGroupM tile rows, walked row-fastest inside a band
@@ -146,7 +148,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(tmem_full_bar + b, 1);
-      mbar_init(tmem_empty_bar + b, 256);  // the epilogue threads of both CTAs
+      mbar_init(tmem_empty_bar + b, 8);  // one lane of each epilogue warp of both CTAs
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   } else if (warp == 2) {
@@ -305,7 +307,8 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
       }
       tcgen05_fence_before();
-      mbar_arrive_cluster(map_to_cta(smem_u32(tmem_empty_bar + buf), 0));  // this thread has drained the buffer
+      __syncwarp();  // every lane's tcgen05.ld of this buffer has completed (tcgen05.wait::ld inside tmem_ld_32x32)
+      if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(tmem_empty_bar + buf), 0));
     }
   }
   if (warp >= 4 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");

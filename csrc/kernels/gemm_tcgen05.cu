@@ -465,7 +465,7 @@ static int make_map_mn(CUtensorMap* map, const void* base, int mn, int kred, int
 
 static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b,
                           int64_t ldb, int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act,
-                          void* stream);
+                          void* stream, float* ws = nullptr, size_t ws_bytes = 0);
 
 namespace mfl { namespace gemm {
 // ---- CTA-pair variant (gemm_2sm.cuh) ----------------------------------------------------------------------------
@@ -487,6 +487,9 @@ template <typename K> static int max_pair_clusters(K kern, size_t smem) {
   return std::min(n, sm_count() / 2);
 }
 
+struct Epilogue;
+static void plan_splits(Epilogue& ep, int bn, const float* ws, size_t ws_bytes);
+static int finalize_splits(const Epilogue& ep, float* ws, void* out, int64_t ld, cudaStream_t st);
 static int g_pair_mode = [] { const char* e = getenv("MFL_GEMM_2SM"); return e ? atoi(e) : -1; }();
 
 static int pair_cluster_estimate() { return std::max(1, sm_count() / 2); }
@@ -564,9 +567,17 @@ extern "C" int mfl_gemm_bf16_ex(void* c, int c_dtype, int64_t ldc, const void* a
   return gemm_bf16_impl(c, c_dtype, ldc, a, lda, a_mn, b, ldb, b_mn, bias, bias_dtype, m, n, k, act, stream);
 }
 
+// Same product with an optional split of the reduction: ws is a ZERO-initialised fp32 scratch of at least m * n floats
+// (handed back zeroed).  It is used when the output has too few tiles to occupy the machine (the weight gradient of a
+// square Linear layer: 1024 x 1024 outputs, reduction over thousands of tokens), bf16 output, no bias / activation.
+extern "C" int mfl_gemm_bf16_ws(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b,
+                                int64_t ldb, int b_mn, int m, int n, int k, float* ws, size_t ws_bytes, void* stream) {
+  return gemm_bf16_impl(c, c_dtype, ldc, a, lda, a_mn, b, ldb, b_mn, nullptr, 0, m, n, k, 0, stream, ws, ws_bytes);
+}
+
 static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b,
                           int64_t ldb, int b_mn, const void* bias, int bias_dtype, int m, int n, int k, int act,
-                          void* stream) {
+                          void* stream, float* ws, size_t ws_bytes) {
   using namespace mfl::gemm;
   MFL_ARG(a && b && c && m > 0 && n > 0 && k > 0, "gemm: null operand or empty shape");
   MFL_ARG(c_dtype == MFL_BFLOAT16 || c_dtype == MFL_FLOAT32, "gemm: output must be BFLOAT16 or FLOAT32");
@@ -599,6 +610,15 @@ static int gemm_bf16_impl(void* c, int c_dtype, int64_t ldc, const void* a, int6
     tc = ta;  // unused by the kernel
   }
   Epilogue ep{c, bias, ldc, m, n, k, c32, bias_dtype == MFL_FLOAT32, act, tma_store, 0, 0, 0, 0, 0, 0, 0, a_mn ? 1 : 0, b_mn ? 1 : 0};
+  if (ws && !bias && act == 0 && !c32 && tma_store) {
+    plan_splits(ep, bn, ws, ws_bytes);
+    if (ep.splits > 1) {
+      ep.c = ws; ep.c_fp32 = 1; ep.ldc = n;
+      if (int rc = make_map(&tc, ws, m, n, n, 32, true)) return rc;
+      if (int rc = launch_gemm(ta, tb, tc, ep, bn, 0, true, (cudaStream_t)stream)) return rc;
+      return finalize_splits(ep, ws, c, ldc, (cudaStream_t)stream);
+    }
+  }
   return launch_gemm(ta, tb, tc, ep, bn, act, c32, (cudaStream_t)stream);
 }
 

@@ -200,6 +200,11 @@ int mfl_gemm_bf16_ex(void* c, int c_dtype, int64_t ldc, const void* a, int64_t l
  * (csrc/kernels/gemm_2sm.cuh): tcgen05.mma.cta_group::2, M = 256 per instruction, each CTA stages its half of B.
  * mode: -1 automatic (default; env MFL_GEMM_2SM), 0 never, 1 wherever legal.  Returns the previous mode. */
 int mfl_gemm_set_pair_mode(int mode);
+/* The same product with an optional split of the reduction over more SMs: ws = ZERO-initialised fp32 scratch of at
+ * least m * n floats (handed back zeroed).  Used when the output has few tiles and k is long (weight gradients of
+ * square Linear layers); bf16 output only.  Partial tiles are added into ws with TMA reduce-add stores. */
+int mfl_gemm_bf16_ws(void* c, int c_dtype, int64_t ldc, const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb,
+                     int b_mn, int m, int n, int k, float* ws, size_t ws_bytes, void* stream);
 
 /* ---- K11: implicit-GEMM convolution forward on the same tcgen05 pipeline; the A operand is gathered by
  * im2col-mode TMA (cuTensorMapEncodeIm2col), never materialised.  NHWC bf16: x[n,h,w,c], w[k,r,s,c],

@@ -17,6 +17,8 @@ import torch.nn.functional as F
 
 from metisfl_b200.ops import _lib
 
+SPLIT_K = True              # gemm_ex may hand the kernel a workspace for split-k (small outputs, long reductions)
+SPLIT_K_MAX_OUT = 1 << 21   # outputs up to 2 M elements (an 8 MiB fp32 workspace)
 ACTS = {None: 0, "none": 0, "relu": 1, "gelu": 2, "gelu_tanh": 2}
 _BOUND = False
 
@@ -29,6 +31,7 @@ def _bind():
         L.mfl_gemm_bf16.argtypes = [vp, i, i64, vp, i64, vp, i64, vp, i, i, i, i, i, vp]
         L.mfl_gemm_bf16_ex.argtypes = [vp, i, i64, vp, i64, i, vp, i64, i, vp, i, i, i, i, i, vp]
         L.mfl_gemm_set_pair_mode.argtypes = [i]
+        L.mfl_gemm_bf16_ws.argtypes = [vp, i, i64, vp, i64, i, vp, i64, i, i, i, i, vp, C.c_size_t, vp]
         L.mfl_colsum_slices.argtypes = [i]
         L.mfl_colsum_bf16.argtypes = [vp, vp, i64, i, i, vp]
         _BOUND = True
@@ -88,6 +91,15 @@ def gemm_ex(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = F
     n, k2 = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
     assert k == k2, (a.shape, b.shape, a_mn, b_mn)
     out = torch.empty(m, n, dtype=out_dtype, device=a.device)
+    if SPLIT_K and out_dtype == torch.bfloat16 and m * n <= SPLIT_K_MAX_OUT and k >= 8 * max(m, n, 512) // 4:
+        # few output tiles, long reduction (dW of a square layer): let the kernel split k over the idle SMs
+        from metisfl_b200.ops.conv import _workspace
+        ws = _workspace(a.device, m * n * 4, torch.cuda.current_stream(a.device))
+        rc = _bind().mfl_gemm_bf16_ws(out.data_ptr(), _lib.wire(out), out.stride(0), a.data_ptr(), a.stride(0),
+                                      int(a_mn), b.data_ptr(), b.stride(0), int(b_mn), m, n, k, ws.data_ptr(),
+                                      ws.numel() * 4, _lib.stream_ptr())
+        _lib.check(rc, "mfl_gemm_bf16_ws")
+        return out
     rc = _bind().mfl_gemm_bf16_ex(out.data_ptr(), _lib.wire(out), out.stride(0), a.data_ptr(), a.stride(0), int(a_mn),
                                   b.data_ptr(), b.stride(0), int(b_mn), None, 0, m, n, k, 0, _lib.stream_ptr())
     _lib.check(rc, "mfl_gemm_bf16_ex")

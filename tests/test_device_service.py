@@ -192,6 +192,41 @@ def test_resnet18_three_rounds_through_driver_session_on_the_device_path(tmp_pat
 
 
 @pytest.mark.gpu
+@pytest.mark.timeout(300)
+def test_captured_evaluation_matches_eager_evaluation(tmp_path):
+    """DeviceBackend.evaluate (device-cached batches, one captured forward + metric accumulation per batch signature)
+    returns the loss / accuracy an eager fp32 pass over the same community model gives - on the first call (capture)
+    and on the second (replay), including the ragged last batch."""
+    from metisfl_b200.learner.device_backend import DeviceBackend, FabricSpec
+    from metisfl_b200.models.torch_model_ops import save_torch_model
+    from metisfl_b200.models.zoo import ResNet18
+    torch.manual_seed(3)
+    model = ResNet18()
+    save_torch_model(model, str(tmp_path / "m"))
+    spec = FabricSpec.parse(FabricSpec(fabric_id="t", rank=0, world=1, init_method="", model_dtype="bf16").to_text())
+    be = DeviceBackend(str(tmp_path / "m"), "cuda:0", spec)
+    try:
+        ds = _resnet_recipe(300, 5)()   # 300 = 2 x 128 + 44: two batch signatures
+        from metisfl_b200.ops.pack import arena_to_model_pb
+        pb = arena_to_model_pb(be.engine.arena)   # the model as the driver would ship it (bytes): becomes the community
+        got1 = be.evaluate(pb, {"test": ds}, 128, None)["test"]
+        got2 = be.evaluate(pb, {"test": ds}, 128, None)["test"]
+        ref = model.cuda().eval()
+        x = torch.from_numpy(ds.get_x()).cuda()
+        y = torch.from_numpy(ds.get_y()).cuda()
+        with torch.no_grad():
+            logits = ref(x)
+            loss = torch.nn.functional.cross_entropy(logits, y).item()
+            acc = (logits.argmax(-1) == y).float().mean().item()
+        for got in (got1, got2):
+            assert abs(got["loss"] - loss) < 0.05 * max(1.0, abs(loss)), (got, loss)
+            assert abs(got["accuracy"] - acc) < 0.05, (got, acc)
+        assert abs(got1["loss"] - got2["loss"]) < 1e-6 and got1["accuracy"] == got2["accuracy"]
+    finally:
+        be.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.timeout(900)
 @pytest.mark.parametrize("world,rule,protocol", [(2, "FedAvg", None), (2, "FedAsync", "Asynchronous"),
                                                  (2, "FedRec", "Asynchronous"), (4, "FedAvg", None),

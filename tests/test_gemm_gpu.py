@@ -120,7 +120,8 @@ def test_mlp_trains_with_b200_linear():
         torch.testing.assert_close(p2.grad.float(), p1.grad.float(), atol=2e-2, rtol=1e-1), n1
 
 
-@pytest.mark.parametrize("m,n,k", [(256, 128, 64), (384, 320, 192), (4096, 1024, 1024), (200, 72, 136), (1024, 3072, 1024)])
+@pytest.mark.parametrize("m,n,k", [(256, 128, 64), (384, 320, 192), (4096, 1024, 1024), (200, 72, 136), (1024, 3072, 1024),
+                                   (1024, 1024, 4096), (512, 768, 8192)])   # the last two take the split-k path
 @pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
 def test_mn_major_operands_match_reference(m, n, k, a_mn, b_mn):
     """General-major GEMM: operands handed over as their transposes, transposed inside the tensor core."""
