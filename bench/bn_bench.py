@@ -58,11 +58,15 @@ for shape in shapes:
             if res is not None:
                 res.grad = None
 
-        t_fused = timeit(lambda: run(True), 3 if ONE else 20, 2 if ONE else 5)
+        fbn.set_cluster_mode(0)
+        t_fused = timeit(lambda: run(True), 3 if ONE else 20, 2 if ONE else 5)     # three launches per direction
+        fbn.set_cluster_mode(1)
+        t_cluster = timeit(lambda: run(True), 3 if ONE else 20, 2 if ONE else 5)   # one launch on thread-block clusters
+        fbn.set_cluster_mode(-1)
         t_aten = None if ONE else timeit(lambda: run(False))
         nbytes = x.numel() * 2
         moved = nbytes * (3 + 7 + (2 if use_res else 0))
-        rows.append({"shape": shape, "residual": use_res, "fused_us": t_fused, "aten_us": t_aten,
+        rows.append({"shape": shape, "residual": use_res, "fused_us": t_fused, "cluster_us": t_cluster, "aten_us": t_aten,
                      "algorithmic_GBps": moved / t_fused / 1e3})
 fbn.ENABLED = True
 print(json.dumps({"bench": "bn_bench", "results": rows}))

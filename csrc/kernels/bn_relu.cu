@@ -24,6 +24,8 @@
 // keras_model_ops.py:156); this is part of the "local training math" row of SURVEY section 2.4.
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace mfl {
@@ -585,7 +587,16 @@ static int coop_max_blocks(K kernel) {
 }  // namespace bn
 }  // namespace mfl
 
+#include "bn_cluster.cuh"
+
 using namespace mfl;
+
+// -1 automatic (default; MFL_BN_CLUSTER in the environment), 0 never use the cluster back-end, 1 wherever a plan exists
+extern "C" int mfl_bn_set_cluster_mode(int mode) {
+  const int old = bn::g_cluster_mode;
+  bn::g_cluster_mode = mode < 0 ? -1 : (mode ? 1 : 0);
+  return old;
+}
 
 extern "C" size_t mfl_bn_workspace_bytes(int m, int c) {
   if (m <= 0 || !bn::supported_channels(c)) return 0;
@@ -663,6 +674,13 @@ extern "C" int mfl_bn_fwd(void* y, const void* x, const void* residual, const fl
   float* coef = workspace + bn::workspace_floats(m, c) - 3 * (size_t)c;
   const bn::FwdFinal fin{gamma, beta, running_mean, running_var, num_batches_tracked, save_mean, save_invstd, coef,
                          eps, momentum};
+  bn::ClPlan cp;
+  if (training && !barrier && bn::make_cluster_plan(m, c, 1, &cp)) {  // one launch on thread-block clusters
+    if (relu && rb) return bn::launch_cluster(bn::cluster_fwd_kernel<true, true>, cp, st, xb, rb, yb, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+    if (relu) return bn::launch_cluster(bn::cluster_fwd_kernel<true, false>, cp, st, xb, rb, yb, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+    if (rb) return bn::launch_cluster(bn::cluster_fwd_kernel<false, true>, cp, st, xb, rb, yb, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+    return bn::launch_cluster(bn::cluster_fwd_kernel<false, false>, cp, st, xb, rb, yb, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+  }
   if (training && barrier) {  // one cooperative launch
     if (relu && rb) return launch_coop_fwd<true, true>(xb, rb, yb, workspace, m, c, barrier, fin, st);
     if (relu) return launch_coop_fwd<true, false>(xb, rb, yb, workspace, m, c, barrier, fin, st);
@@ -703,6 +721,16 @@ extern "C" int mfl_bn_bwd(void* dx, void* dres, float* dgamma, float* dbeta, int
   auto* drb = static_cast<__nv_bfloat16*>(dres);
   float* coef = workspace + bn::workspace_floats(m, c) - 3 * (size_t)c;
   const bn::BwdFinal fin{gamma, save_invstd, dgamma, dbeta, accumulate, coef};
+  bn::ClPlan cp;
+  if (!barrier && bn::make_cluster_plan(m, c, 2, &cp)) {  // one launch on thread-block clusters
+    if (relu && drb)
+      return bn::launch_cluster(bn::cluster_bwd_kernel<true, true>, cp, st, xb, db, yb, dxb, drb, save_mean, save_invstd, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+    if (relu)
+      return bn::launch_cluster(bn::cluster_bwd_kernel<true, false>, cp, st, xb, db, yb, dxb, drb, save_mean, save_invstd, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+    if (drb)
+      return bn::launch_cluster(bn::cluster_bwd_kernel<false, true>, cp, st, xb, db, yb, dxb, drb, save_mean, save_invstd, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+    return bn::launch_cluster(bn::cluster_bwd_kernel<false, false>, cp, st, xb, db, yb, dxb, drb, save_mean, save_invstd, m, c, cp.slice, cp.rows_per_cta, cp.keep, fin);
+  }
   if (barrier) {  // one cooperative launch
     if (relu && drb)
       return launch_coop_bwd<true, true>(xb, db, yb, dxb, drb, save_mean, save_invstd, workspace, m, c, barrier, fin, st);

@@ -28,10 +28,17 @@ def _bind():
         vp, i, f, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
         L.mfl_bn_workspace_bytes.restype = sz
         L.mfl_bn_workspace_bytes.argtypes = [i, i]
+        L.mfl_bn_set_cluster_mode.argtypes = [i]
         L.mfl_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp, i, i, f, f, i, i, vp]
         L.mfl_bn_bwd.argtypes = [vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, sz, vp, i, i, i, vp]
         _BOUND = True
     return L
+
+
+def set_cluster_mode(mode: int) -> int:
+    """Back-end C of K14 (one launch per direction on thread-block clusters, ``csrc/kernels/bn_cluster.cuh``):
+    -1 automatic (layers up to ~4.5 M elements), 0 never, 1 wherever a plan exists.  Returns the previous mode."""
+    return _bind().mfl_bn_set_cluster_mode(int(mode))
 
 
 def _ptr(t):

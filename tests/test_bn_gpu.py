@@ -8,18 +8,21 @@ pytestmark = pytest.mark.gpu
 
 
 
-@pytest.fixture(params=["cooperative", "three_launches"], autouse=True)
+@pytest.fixture(params=["cooperative", "three_launches", "clusters"], autouse=True)
 def finalize_mode(request):
-    """Both back-ends: one cooperative launch with grid barriers, and the three-launch sequence."""
+    """All back-ends: one cooperative launch with grid barriers, the three-launch sequence, and one launch on
+    thread-block clusters (channel slices, partial sums combined through distributed shared memory)."""
     from metisfl_b200.ops import bn as fbn
     old = fbn.FUSED_FINALIZE
     fbn.FUSED_FINALIZE = request.param == "cooperative"
+    old_cluster = fbn.set_cluster_mode(1 if request.param == "clusters" else 0)
     yield
     fbn.FUSED_FINALIZE = old
+    fbn.set_cluster_mode(old_cluster)
 
 
 SHAPES = [(128, 64, 32, 32), (32, 128, 16, 16), (7, 256, 5, 3), (16, 512, 4, 4), (3, 8, 9, 11), (2, 2048, 2, 2),
-          (2, 64, 1, 1), (5, 32, 17, 13)]
+          (2, 64, 1, 1), (5, 32, 17, 13), (128, 128, 16, 16), (128, 256, 8, 8), (128, 512, 4, 4), (64, 16, 24, 24)]
 
 
 def _inputs(shape, seed, device="cuda"):
