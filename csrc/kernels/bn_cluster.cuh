@@ -324,6 +324,37 @@ static size_t g_cluster_auto_max_elems = [] {
   return e ? (size_t)atoll(e) : (size_t)2200000;   // measured crossover (bn_bench): 128x512x4x4 and 128x256x8x8 win
 }();
 
+// 16-CTA clusters are a non-portable size: they need an opt-in per kernel and a GPC with 16 free SMs
+static int g_cluster_max_ranks = [] { const char* e = getenv("MFL_BN_CLUSTER_RANKS"); return e ? atoi(e) : 16; }();
+
+// Can this device co-schedule a 16-CTA cluster of these kernels at all?  Asked once, with the largest shared-memory
+// request and the backward kernel (the heavier of the two).
+static bool cluster16_fits() {
+  static int fits = -1;
+  if (fits < 0) {
+    auto kernel = cluster_bwd_kernel<true, true>;
+    fits = 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kClSmemLimit) == cudaSuccess &&
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(16, 8);
+      cfg.blockDim = dim3(kClThreads);
+      cfg.dynamicSmemBytes = kClSmemLimit;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 16;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) == cudaSuccess && n > 0) fits = 1;
+    }
+    cudaGetLastError();
+  }
+  return fits == 1;
+}
+
 static bool make_cluster_plan(int m, int c, int slabs, ClPlan* p) {
   if (g_cluster_mode == 0 || c < 16) return false;
   if (g_cluster_mode < 0 && (size_t)m * c > g_cluster_auto_max_elems) return false;
@@ -332,7 +363,8 @@ static bool make_cluster_plan(int m, int c, int slabs, ClPlan* p) {
   // widen the slice while there are still enough (slice, rank) CTAs to cover the machine with 8-CTA clusters
   while (S < kClMaxSlice && S * 2 <= c && (c / (S * 2)) * 8 >= target) S *= 2;
   int R = 1;
-  while (R < 8 && (c / S) * R < target && (m + 2 * R - 1) / (2 * R) >= 64) R *= 2;
+  const int max_r = (g_cluster_max_ranks > 8 && cluster16_fits()) ? 16 : std::min(g_cluster_max_ranks, 8);
+  while (R < max_r && (c / S) * R < target && (m + 2 * R - 1) / (2 * R) >= 64) R *= 2;
   p->slice = S;
   p->n_slices = c / S;
   p->ranks = R;
@@ -349,6 +381,7 @@ static bool make_cluster_plan(int m, int c, int slabs, ClPlan* p) {
 template <typename K, typename... Args>
 static int launch_cluster(K kernel, const ClPlan& p, cudaStream_t st, Args... args) {
   MFL_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kClSmemLimit));
+  if (p.ranks > 8) MFL_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(p.ranks, p.n_slices);
   cfg.blockDim = dim3(kClThreads);
