@@ -100,7 +100,7 @@ def run_other_config(args):
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,utilization.gpu")
 
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
@@ -122,7 +122,7 @@ class ClockSampler:
             self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
+        sm, mx, reasons, busy = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f:
             parts = [c.strip() for c in line.split(",")]
@@ -132,13 +132,20 @@ class ClockSampler:
                 sm.append(float(parts[1])); mx.append(float(parts[2]))
             except ValueError:
                 continue
+            try:
+                busy.append(float(parts[9]) >= 10.0 if len(parts) > 9 else True)
+            except ValueError:
+                busy.append(True)
             for n, v in zip(names, parts[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         os.unlink(self.f.name)
         if sm:
-            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                   "samples": len(sm)}
+            # "under load": samples taken while the GPU reported work (a sampler that brackets a whole script also
+            # sees its idle set-up phases at the idle clock)
+            loaded = [v for v, b in zip(sm, busy) if b] or sm
+            out = {"sm_mhz": statistics.median(loaded), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                   "samples": len(sm), "samples_under_load": len(loaded)}
         return out
 
 
