@@ -362,10 +362,49 @@ struct WsArgs {
   int n_src, n_limbs, log_n;
 };
 
+// One ciphertext model per GPU (2, 4 or 8 sources): all sixteen 16-byte loads of 16 / NS element pairs are issued before
+// the first modular multiply, so a thread keeps 256 B in flight over NVLink instead of 64 B (the 4-load batches of the
+// general loop spent most of a round trip with nothing outstanding: 0.40 of the link roofline at 8 GPUs).
+template <bool PEER, int NS>
+__device__ __forceinline__ void ws_range_batched(const WsArgs& a, size_t begin, size_t end, uint64_t* const* outs,
+                                                 int n_out) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x * 2;
+  constexpr int P = 16 / NS;
+  for (size_t base = begin + ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; base < end; base += stride * P) {
+    uint4 v[P][NS];
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const size_t i = base + p * stride;
+#pragma unroll
+      for (int j = 0; j < NS; ++j)
+        v[p][j] = i < end ? (PEER ? ld_peer(a.src[j] + i) : ld_stream(a.src[j] + i)) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const size_t i = base + p * stride;
+      if (i >= end) break;
+      const int limb = (int)((i >> a.log_n) % a.n_limbs);
+      const uint64_t q = a.q[limb];
+      uint64_t acc0 = 0, acc1 = 0;
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {
+        const uint64_t x0 = ((uint64_t)v[p][j].y << 32) | v[p][j].x, x1 = ((uint64_t)v[p][j].w << 32) | v[p][j].z;
+        acc0 = d_add(acc0, d_mul_shoup(x0, a.w[j][limb], a.wp[j][limb], q), q);
+        acc1 = d_add(acc1, d_mul_shoup(x1, a.w[j][limb], a.wp[j][limb], q), q);
+      }
+      const uint4 o = make_uint4((uint32_t)acc0, (uint32_t)(acc0 >> 32), (uint32_t)acc1, (uint32_t)(acc1 >> 32));
+      for (int t = 0; t < n_out; ++t) st_stream(outs[t] + i, o);
+    }
+  }
+}
+
 // out[i] = sum_l src_l[i] * w_l[limb(i)] mod q[limb(i)] for words i in [begin, end), 2 words / thread-step
 template <bool PEER>
 __device__ __forceinline__ void ws_range(const WsArgs& a, size_t begin, size_t end, uint64_t* const* outs, int n_out) {
   const size_t stride = (size_t)gridDim.x * blockDim.x * 2;
+  if (a.n_src == 8) return ws_range_batched<PEER, 8>(a, begin, end, outs, n_out);
+  if (a.n_src == 4) return ws_range_batched<PEER, 4>(a, begin, end, outs, n_out);
+  if (a.n_src == 2) return ws_range_batched<PEER, 2>(a, begin, end, outs, n_out);
   for (size_t i = begin + ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; i < end; i += stride) {
     const int limb = (int)((i >> a.log_n) % a.n_limbs);  // both words of the pair share a row (N is even)
     const uint64_t q = a.q[limb];

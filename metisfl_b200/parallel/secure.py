@@ -66,8 +66,11 @@ class SecureAggregator:
     def ciphertext_bytes(self) -> int:
         return self.words * 8
 
-    def round(self, batches: Sequence, weights: Optional[Sequence[float]] = None, check: bool = False):
-        """One secure federation round for the learner of this rank (one learner per GPU)."""
+    def round(self, batches: Sequence, weights: Optional[Sequence[float]] = None, check: bool = False,
+              sync_phases: bool = False):
+        """One secure federation round for the learner of this rank (one learner per GPU).  ``sync_phases`` lines the
+        ranks up (host barrier, outside the timers) before the cross-GPU reduction, so that its timer measures the
+        kernel and not the slowest rank's encryption."""
         import torch.distributed as dist
         e, g = self.e, self.g
         w = list(weights) if weights is not None else [1.0 / e.world] * e.world
@@ -76,6 +79,9 @@ class SecureAggregator:
         x = e.slot_views[0][0]
         with self.timer.phase("encode_encrypt"):
             g.encrypt_device(x, out=self.ct_slot.local.view(torch.int64)[:self.words])  # randomness: os.urandom per call
+        if sync_phases and e.world > 1:
+            torch.cuda.synchronize(e.device)
+            dist.barrier()
         with self.timer.phase("reduce_over_nvlink"):
             g.fused_weighted_sum(self.ct_slot.ptrs, w, self.words, self.ct_out.ptrs, e.pads.ptrs, e.rank, e.world,
                                  n_blocks=148)

@@ -80,6 +80,25 @@ def test_fused_weighted_sum_single_rank(ctx):
     assert torch.equal(out, local)
 
 
+def test_eight_source_weighted_sum_matches_decrypted_average(ctx):
+    """Eight ciphertext models (the 8-GPU shape: all sixteen loads of two element pairs in flight per thread): the local
+    and the fused kernel agree bit for bit, and the decrypted result is the plaintext weighted average."""
+    host, g = ctx
+    from metisfl_b200.ops import _lib
+    rng = np.random.default_rng(11)
+    xs = [rng.normal(size=9000) for _ in range(8)]
+    w = [0.05, 0.1, 0.15, 0.2, 0.2, 0.15, 0.1, 0.05]
+    cts = [g.encrypt_device(torch.from_numpy(x).cuda()) for x in xs]   # fresh OS randomness per ciphertext
+    local = g.weighted_sum_device(cts, w)
+    out = torch.zeros_like(local)
+    pads = torch.zeros(_lib.lib().mfl_signal_pad_bytes(148), dtype=torch.uint8, device="cuda")
+    g.fused_weighted_sum([c.data_ptr() for c in cts], w, local.numel(), [out.data_ptr()], [pads.data_ptr()], 0, 1)
+    torch.cuda.synchronize()
+    assert torch.equal(out, local)
+    dec = g.decrypt_device(out, 9000, scale=g.scale * g.scale).cpu().numpy()
+    np.testing.assert_allclose(dec, sum(wi * x for wi, x in zip(w, xs)), atol=1e-7)
+
+
 def test_fhe_class_uses_gpu_for_large_tensors(ctx):
     host, _ = ctx
     auto = fhe.CKKS(4096, 52, backend="cuda")
