@@ -19,13 +19,15 @@
 namespace mfl {
 namespace bn {
 
-constexpr int kClThreads = 256;
+constexpr int kClThreads = 512;         // largest CTA (the plan picks 256 or 512 threads by rows per CTA)
+constexpr int kClUnrollFwd = 8;         // one input stream per row in forward
+constexpr int kClUnrollBwd = 4;         // three input streams per row in backward
 constexpr int kClWarps = kClThreads / 32;
 constexpr int kClMaxSlice = 64;          // channels per cluster (tpr <= 8 threads per row)
 constexpr size_t kClSmemLimit = 200 * 1024;
 
 struct ClPlan {
-  int slice, n_slices, ranks, rows_per_cta, keep;
+  int slice, n_slices, ranks, rows_per_cta, keep, threads;
   size_t smem;
 };
 
@@ -39,9 +41,16 @@ __device__ __forceinline__ uint32_t cl_size() {
   asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
   return r;
 }
-// per-thread forms (no .aligned): they sit right behind loops that only part of a warp runs
-__device__ __forceinline__ void cl_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
-__device__ __forceinline__ void cl_wait() { asm volatile("barrier.cluster.wait.acquire;" ::: "memory"); }
+// warp-level (.aligned) forms behind an explicit reconvergence: they follow loops that only part of a warp runs, and
+// per-thread arrivals of 2-8 K threads per cluster cost microseconds
+__device__ __forceinline__ void cl_arrive() {
+  __syncwarp();
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cl_wait() {
+  __syncwarp();
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ float cl_ld_remote(const float* local_smem_ptr, uint32_t rank) {
   uint32_t addr;
   float v;
@@ -68,18 +77,17 @@ __device__ __forceinline__ void cl_fold_cta(float* wred, float* part, const floa
     for (int k = 0; k < 16; ++k) wred[(warp * kClMaxSlice / 8 + lane) * 16 + k] = v[k];
   }
   __syncthreads();
-  for (int o = threadIdx.x; o < 2 * S; o += kClThreads) {
+  for (int o = threadIdx.x; o < 2 * S; o += blockDim.x) {
     const int s = o / S, c = o - s * S;
     float acc = 0.f;
-#pragma unroll
-    for (int w = 0; w < kClWarps; ++w) acc += wred[(w * kClMaxSlice / 8 + (c >> 3)) * 16 + s * 8 + (c & 7)];
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) acc += wred[(w * kClMaxSlice / 8 + (c >> 3)) * 16 + s * 8 + (c & 7)];
     part[o] = acc;
   }
 }
 
 // tot[o] = sum over the cluster's CTAs (rank order) of part[o]; call between cl_arrive/cl_wait pairs as below
 __device__ __forceinline__ void cl_total(float* tot, const float* part, int S, uint32_t R) {
-  for (int o = threadIdx.x; o < 2 * S; o += kClThreads) {
+  for (int o = threadIdx.x; o < 2 * S; o += blockDim.x) {
     float v[8];   // all remote loads in flight before the first add (one DSMEM latency, not R)
 #pragma unroll
     for (uint32_t j = 0; j < 8; ++j) v[j] = j < R ? cl_ld_remote(part + o, j) : 0.f;
@@ -117,7 +125,7 @@ __global__ void __launch_bounds__(kClThreads) cluster_fwd_kernel(const __nv_bflo
   extern __shared__ __align__(16) uint8_t cl_smem_raw[];
   const ClSmem sm = cl_carve(cl_smem_raw);
   const uint32_t rank = cl_rank(), R = cl_size();
-  const int tpr = S >> 3, rpi = kClThreads / tpr;
+  const int tpr = S >> 3, rpi = (int)blockDim.x / tpr;
   const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
   const int c0 = blockIdx.y * S;
   const size_t col = (size_t)c0 + tx * 8;
@@ -125,12 +133,12 @@ __global__ void __launch_bounds__(kClThreads) cluster_fwd_kernel(const __nv_bflo
   float s0[8], s1[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) s0[k] = s1[k] = 0.f;
-  for (int r = r0 + ty; r < r1; r += kUnroll * rpi) {
-    uint4 v[kUnroll];
+  for (int r = r0 + ty; r < r1; r += kClUnrollFwd * rpi) {
+    uint4 v[kClUnrollFwd];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) v[u] = ld_row(x + (size_t)(r + u * rpi) * C + col, r + u * rpi < r1);
+    for (int u = 0; u < kClUnrollFwd; ++u) v[u] = ld_row(x + (size_t)(r + u * rpi) * C + col, r + u * rpi < r1);
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kClUnrollFwd; ++u) {
       if (keep && r + u * rpi < r1) sm.slab[(size_t)(r + u * rpi - r0) * tpr + tx] = v[u];
       float f[8];
       V::unpack(v[u], f);
@@ -169,17 +177,17 @@ __global__ void __launch_bounds__(kClThreads) cluster_fwd_kernel(const __nv_bflo
   float sc[8], sh[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) { sc[k] = sm.coef[tx * 8 + k]; sh[k] = sm.coef[S + tx * 8 + k]; }
-  for (int r = r0 + ty; r < r1; r += kUnroll * rpi) {
-    uint4 vx[kUnroll], vr[kUnroll];
+  for (int r = r0 + ty; r < r1; r += kClUnrollFwd * rpi) {
+    uint4 vx[kClUnrollFwd], vr[kClUnrollFwd];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kClUnrollFwd; ++u) {
       const bool ok = r + u * rpi < r1;
       const size_t off = (size_t)(r + u * rpi) * C + col;
       vx[u] = !ok ? make_uint4(0, 0, 0, 0) : (keep ? sm.slab[(size_t)(r + u * rpi - r0) * tpr + tx] : ld_stream(x + off));
       vr[u] = RES ? ld_row(res + off, ok) : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kClUnrollFwd; ++u) {
       if (r + u * rpi < r1) {
         float f[8], fr[8];
         V::unpack(vx[u], f);
@@ -209,14 +217,14 @@ __global__ void __launch_bounds__(kClThreads) cluster_bwd_kernel(const __nv_bflo
   extern __shared__ __align__(16) uint8_t cl_smem_raw[];
   const ClSmem sm = cl_carve(cl_smem_raw);
   const uint32_t rank = cl_rank(), R = cl_size();
-  const int tpr = S >> 3, rpi = kClThreads / tpr;
+  const int tpr = S >> 3, rpi = (int)blockDim.x / tpr;
   const int tx = threadIdx.x % tpr, ty = threadIdx.x / tpr;
   const int c0 = blockIdx.y * S;
   const size_t col = (size_t)c0 + tx * 8;
   const int r0 = (int)rank * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
   uint4* slab_x = sm.slab;
   uint4* slab_g = sm.slab + (size_t)rows_per_cta * tpr;
-  constexpr int U = kUnrollBwd;
+  constexpr int U = kClUnrollBwd;
   float mu[8], is[8], s0[8], s1[8];
   load8(mean + col, mu);
   load8(invstd + col, is);
@@ -368,7 +376,9 @@ static bool make_cluster_plan(int m, int c, int slabs, ClPlan* p) {
   p->slice = S;
   p->n_slices = c / S;
   p->ranks = R;
-  const int rpi = kClThreads / (S / 8);
+  // 512 threads (more loads in flight) once a CTA has at least eight row vectors per thread at that size
+  p->threads = ((m + R - 1) / R) * (S / 8) >= 8 * 512 ? 512 : 256;
+  const int rpi = p->threads / (S / 8);
   int rows = (m + R - 1) / R;
   rows = (rows + rpi - 1) / rpi * rpi;
   p->rows_per_cta = rows;
@@ -384,7 +394,7 @@ static int launch_cluster(K kernel, const ClPlan& p, cudaStream_t st, Args... ar
   if (p.ranks > 8) MFL_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(p.ranks, p.n_slices);
-  cfg.blockDim = dim3(kClThreads);
+  cfg.blockDim = dim3(p.threads);
   cfg.dynamicSmemBytes = p.smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
