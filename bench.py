@@ -346,12 +346,14 @@ def main():
     stock_best_ms = min([v for v in (stock_eager_ms, stock_graph_ms) if v > 0], default=0.0)
     vs_baseline = (stock_best_ms / dev_ms) if stock_best_ms > 0 else None   # = value / stock value (same numerator)
     link_gbs = 770.0  # measured peer-copy bandwidth per direction (B200_PROFILING.md)
-    # roofline of the aggregation alone: one model's worth of bytes has to leave and enter every GPU over NVLink
-    # ((world-1)/world of it with peer loads/stores, 1/world + 1/world per direction with the in-switch reduction);
-    # at world 1 it is an HBM copy of the slots
+    # roofline of the aggregation alone = INBOUND NVLink bytes per GPU / measured link bandwidth.  Peer loads / stores:
+    # this GPU reads its shard from world-1 peers and receives world-1 result shards = 2 (world-1)/world of a model.
+    # In-switch reduction: the reduced shard (1/world) plus the multicast all-gather (a whole model, own shard
+    # included).  At world 1 it is an HBM copy of the slots.
     seg_bytes = sum(sg.nbytes for sg in eng.layout.segments)
     if world > 1:
-        roof_ms = seg_bytes * (world - 1) / world / (link_gbs * 1e9) * 1e3
+        inbound = seg_bytes * (1.0 / world + 1.0) if eng.nvls else seg_bytes * 2.0 * (world - 1) / world
+        roof_ms = inbound / (link_gbs * 1e9) * 1e3
     else:
         roof_ms = seg_bytes * (k + 1) / (6553.9e9) * 1e3
     x0, y0 = pool[0][0]
@@ -416,7 +418,8 @@ def main():
                             "k1_vs_nccl": nccl_ms / k1_ms if k1_ms > 0 else None,
                             "mode": agg_mode,
                             "roofline_ms": roof_ms, "fraction_of_roofline": roof_ms / k1_ms if k1_ms > 0 else None,
-                            "roofline_def": "bytes that must cross NVLink per GPU and direction / 770 GB/s measured "
+                            "roofline_def": "inbound NVLink bytes per GPU (shard reads + result shards; in-switch "
+                                            "reduction: reduced shard + multicast all-gather) / 770 GB/s measured "
                                             "(world 1: slot reads + community write / measured HBM copy)"},
             "community_check": check,
             "e2e_service": service,

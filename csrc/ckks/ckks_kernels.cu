@@ -18,6 +18,7 @@
 
 #include "ckks/ckks_common.h"
 #include "kernels/common.cuh"
+#include "kernels/tcgen05_common.cuh"   // mbarrier helpers
 
 namespace mfl {
 namespace ckksdev {
@@ -362,12 +363,23 @@ struct WsArgs {
   int n_src, n_limbs, log_n;
 };
 
+// One multicast store lands in every GPU's output buffer (NVSwitch replicates it): 1/world of the outbound NVLink
+// traffic of world separate peer stores.  `mc` is the multicast address of the symmetric output buffers.
+__device__ __forceinline__ void ws_store(uint64_t* const* outs, int n_out, uint64_t* mc, size_t i, const uint4& o) {
+  if (mc) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(mc + i), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+  } else {
+    for (int t = 0; t < n_out; ++t) st_stream(outs[t] + i, o);
+  }
+}
+
 // One ciphertext model per GPU (2, 4 or 8 sources): all sixteen 16-byte loads of 16 / NS element pairs are issued before
 // the first modular multiply, so a thread keeps 256 B in flight over NVLink instead of 64 B (the 4-load batches of the
 // general loop spent most of a round trip with nothing outstanding: 0.40 of the link roofline at 8 GPUs).
 template <bool PEER, int NS>
 __device__ __forceinline__ void ws_range_batched(const WsArgs& a, size_t begin, size_t end, uint64_t* const* outs,
-                                                 int n_out) {
+                                                 int n_out, uint64_t* mc) {
   const size_t stride = (size_t)gridDim.x * blockDim.x * 2;
   constexpr int P = 16 / NS;
   for (size_t base = begin + ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; base < end; base += stride * P) {
@@ -393,18 +405,19 @@ __device__ __forceinline__ void ws_range_batched(const WsArgs& a, size_t begin, 
         acc1 = d_add(acc1, d_mul_shoup(x1, a.w[j][limb], a.wp[j][limb], q), q);
       }
       const uint4 o = make_uint4((uint32_t)acc0, (uint32_t)(acc0 >> 32), (uint32_t)acc1, (uint32_t)(acc1 >> 32));
-      for (int t = 0; t < n_out; ++t) st_stream(outs[t] + i, o);
+      ws_store(outs, n_out, mc, i, o);
     }
   }
 }
 
 // out[i] = sum_l src_l[i] * w_l[limb(i)] mod q[limb(i)] for words i in [begin, end), 2 words / thread-step
 template <bool PEER>
-__device__ __forceinline__ void ws_range(const WsArgs& a, size_t begin, size_t end, uint64_t* const* outs, int n_out) {
+__device__ __forceinline__ void ws_range(const WsArgs& a, size_t begin, size_t end, uint64_t* const* outs, int n_out,
+                                         uint64_t* mc = nullptr) {
   const size_t stride = (size_t)gridDim.x * blockDim.x * 2;
-  if (a.n_src == 8) return ws_range_batched<PEER, 8>(a, begin, end, outs, n_out);
-  if (a.n_src == 4) return ws_range_batched<PEER, 4>(a, begin, end, outs, n_out);
-  if (a.n_src == 2) return ws_range_batched<PEER, 2>(a, begin, end, outs, n_out);
+  if (a.n_src == 8) return ws_range_batched<PEER, 8>(a, begin, end, outs, n_out, mc);
+  if (a.n_src == 4) return ws_range_batched<PEER, 4>(a, begin, end, outs, n_out, mc);
+  if (a.n_src == 2) return ws_range_batched<PEER, 2>(a, begin, end, outs, n_out, mc);
   for (size_t i = begin + ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2; i < end; i += stride) {
     const int limb = (int)((i >> a.log_n) % a.n_limbs);  // both words of the pair share a row (N is even)
     const uint64_t q = a.q[limb];
@@ -428,7 +441,7 @@ __device__ __forceinline__ void ws_range(const WsArgs& a, size_t begin, size_t e
       acc1 = d_add(acc1, d_mul_shoup(x1, a.w[l][limb], a.wp[l][limb], q), q);
     }
     const uint4 o = make_uint4((uint32_t)acc0, (uint32_t)(acc0 >> 32), (uint32_t)acc1, (uint32_t)(acc1 >> 32));
-    for (int t = 0; t < n_out; ++t) st_stream(outs[t] + i, o);
+    ws_store(outs, n_out, mc, i, o);
   }
 }
 
@@ -441,16 +454,96 @@ struct FusedWsArgs {
   WsArgs ws;
   uint64_t* out[MFL_MAX_PEERS];
   uint32_t* pads[MFL_MAX_PEERS];
+  uint64_t* mc_out;   // multicast address of the output buffers, or NULL (peer stores)
   int rank, world;
   size_t words;
 };
+
+// ---- K8 fed by bulk copies --------------------------------------------------------------------------------------
+// 16-byte peer loads issued by threads top out near 300 GB/s per GPU over NVLink here (2 and 8 GPUs alike): the link
+// wants few, large requests.  This variant moves the operands with cp.async.bulk (no multicast: each copy reads one
+// GPU's memory into this CTA's shared memory): one producer lane streams 4 KB pieces of every source's shard into a
+// ring of stages (up to 192 KB in flight per SM), 256 consumer threads take one 16-byte element pair of every source
+// per stage from shared memory, multiply-accumulate modulo q and store the result once (multimem.st) or to every peer.
+constexpr int kWsChunkWords = 512;                 // 4 KB of one source per stage: 256 threads x 16 B
+constexpr int kWsConsumers = 256;
+constexpr int kWsThreads = kWsConsumers + 32;      // + the producer warp
+constexpr int kWsMaxSrc = 8;
+constexpr size_t kWsSmemBudget = 196 * 1024;
+
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(gemm::smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(gemm::smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(kWsThreads, 1) ckks_fused_weighted_sum_bulk_kernel(const __grid_constant__ FusedWsArgs fa,
+                                                                                     int stages) {
+  extern __shared__ __align__(128) uint8_t ws_smem[];
+  using namespace gemm;
+  const int ns = fa.ws.n_src;
+  const uint32_t stage_bytes = (uint32_t)ns * kWsChunkWords * 8;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ws_smem + (size_t)stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + stages;
+  const int slot0 = (0 * gridDim.x + blockIdx.x) * MFL_MAX_PEERS, slot1 = (1 * gridDim.x + blockIdx.x) * MFL_MAX_PEERS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, kWsConsumers / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  peer_barrier(fa.pads, fa.rank, fa.world, slot0, true);   // every rank's ciphertexts are complete (also a CTA barrier)
+  // shards in whole chunks (a chunk never straddles a limb row: rows are 2^log_n words, chunks 2^9)
+  const size_t chunks = fa.words / kWsChunkWords, per = (chunks + fa.world - 1) / fa.world;
+  const size_t c_begin = min(chunks, per * fa.rank), c_end = min(chunks, per * (fa.rank + 1));
+  if (warp == kWsConsumers / 32) {
+    if (lane == 0) {  // ===== producer =====
+      uint32_t it = 0;
+      for (size_t c = c_begin + blockIdx.x; c < c_end; c += gridDim.x, ++it) {
+        const int s = it % stages;
+        mbar_wait(empty_bar + s, ((it / stages) & 1) ^ 1);
+        mbar_expect_tx(full_bar + s, stage_bytes);
+        uint8_t* dst = ws_smem + (size_t)s * stage_bytes;
+        for (int j = 0; j < ns; ++j)
+          bulk_load(dst + (size_t)j * kWsChunkWords * 8, fa.ws.src[j] + c * kWsChunkWords, kWsChunkWords * 8, full_bar + s);
+      }
+    }
+  } else {  // ===== consumers =====
+    uint32_t it = 0;
+    for (size_t c = c_begin + blockIdx.x; c < c_end; c += gridDim.x, ++it) {
+      const int s = it % stages;
+      const size_t i = c * kWsChunkWords + (size_t)threadIdx.x * 2;
+      const int limb = (int)(((c * kWsChunkWords) >> fa.ws.log_n) % fa.ws.n_limbs);
+      const uint64_t q = fa.ws.q[limb];
+      mbar_wait(full_bar + s, (it / stages) & 1);
+      const uint4* src = reinterpret_cast<const uint4*>(ws_smem + (size_t)s * stage_bytes) + threadIdx.x;
+      uint64_t acc0 = 0, acc1 = 0;
+#pragma unroll
+      for (int j = 0; j < kWsMaxSrc; ++j) {
+        if (j < ns) {
+          const uint4 v = src[(size_t)j * (kWsChunkWords / 2)];
+          const uint64_t x0 = ((uint64_t)v.y << 32) | v.x, x1 = ((uint64_t)v.w << 32) | v.z;
+          acc0 = d_add(acc0, d_mul_shoup(x0, fa.ws.w[j][limb], fa.ws.wp[j][limb], q), q);
+          acc1 = d_add(acc1, d_mul_shoup(x1, fa.ws.w[j][limb], fa.ws.wp[j][limb], q), q);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar + s);   // this warp has read its part of the stage
+      const uint4 o = make_uint4((uint32_t)acc0, (uint32_t)(acc0 >> 32), (uint32_t)acc1, (uint32_t)(acc1 >> 32));
+      ws_store(fa.out, fa.world, fa.mc_out, i, o);
+    }
+  }
+  // words past the last whole chunk (none for ring dimensions >= 512) would be handled here
+  peer_barrier(fa.pads, fa.rank, fa.world, slot1, true);   // every shard has landed everywhere
+}
 
 __global__ void __launch_bounds__(512, 1) ckks_fused_weighted_sum_kernel(const __grid_constant__ FusedWsArgs fa) {
   const int slot0 = (0 * gridDim.x + blockIdx.x) * MFL_MAX_PEERS, slot1 = (1 * gridDim.x + blockIdx.x) * MFL_MAX_PEERS;
   peer_barrier(fa.pads, fa.rank, fa.world, slot0, true);   // every rank's ciphertexts are complete
   const size_t pairs = fa.words / 2, per = (pairs + fa.world - 1) / fa.world;
   const size_t begin = min(pairs, per * fa.rank) * 2, end = min(pairs, per * (fa.rank + 1)) * 2;
-  ws_range<true>(fa.ws, begin, end, fa.out, fa.world);
+  ws_range<true>(fa.ws, begin, end, fa.out, fa.world, fa.mc_out);
   peer_barrier(fa.pads, fa.rank, fa.world, slot1, true);   // every shard has landed everywhere
 }
 
@@ -591,18 +684,37 @@ extern "C" int mfl_ckks_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* co
   return check(cudaGetLastError(), "ckks_weighted_sum_kernel launch");
 }
 
-extern "C" int mfl_ckks_fused_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
-                                           const uint64_t* w_shoup, int n_src, size_t words, uint64_t* const* outs,
-                                           uint32_t* const* signal_pads, int rank, int world, int n_blocks, void* stream) {
+extern "C" int mfl_ckks_fused_weighted_sum_mc(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
+                                              const uint64_t* w_shoup, int n_src, size_t words, uint64_t* const* outs,
+                                              uint64_t* mc_out, uint32_t* const* signal_pads, int rank, int world,
+                                              int n_blocks, void* stream) {
   if (int rc = check_ctx(ctx)) return rc;
   MFL_ARG(world >= 1 && world <= MFL_MAX_PEERS && rank >= 0 && rank < world, "ckks fused: bad rank/world %d/%d", rank, world);
   MFL_ARG(n_blocks >= 1 && n_blocks <= sm_count(), "ckks fused: n_blocks=%d must be in [1, #SMs]", n_blocks);
+  MFL_ARG((reinterpret_cast<uintptr_t>(mc_out) & 15) == 0, "ckks fused: the multicast output address is not 16-byte aligned");
   FusedWsArgs fa;
   if (int rc = fill_ws(fa.ws, ctx, cts, w, w_shoup, n_src)) return rc;
   for (int t = 0; t < world; ++t) { fa.out[t] = outs[t]; fa.pads[t] = signal_pads[t]; }
+  fa.mc_out = mc_out;
   fa.rank = rank; fa.world = world; fa.words = words;
+  static const int bulk_mode = [] { const char* e = getenv("MFL_CKKS_BULK"); return e ? atoi(e) : 1; }();
+  if (bulk_mode && world > 1 && n_src <= kWsMaxSrc && words % kWsChunkWords == 0 && ctx->log_n >= 9) {
+    const size_t stage_bytes = (size_t)n_src * kWsChunkWords * 8;
+    const int stages = (int)std::min<size_t>(16, (kWsSmemBudget - 512) / stage_bytes);
+    const size_t smem = (size_t)stages * stage_bytes + 2 * (size_t)stages * sizeof(uint64_t);
+    if (int rc = allow_smem(ckks_fused_weighted_sum_bulk_kernel, smem)) return rc;
+    ckks_fused_weighted_sum_bulk_kernel<<<n_blocks, kWsThreads, smem, (cudaStream_t)stream>>>(fa, stages);
+    return check(cudaGetLastError(), "ckks_fused_weighted_sum_bulk_kernel launch");
+  }
   ckks_fused_weighted_sum_kernel<<<n_blocks, 512, 0, (cudaStream_t)stream>>>(fa);
   return check(cudaGetLastError(), "ckks_fused_weighted_sum_kernel launch");
+}
+
+extern "C" int mfl_ckks_fused_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
+                                           const uint64_t* w_shoup, int n_src, size_t words, uint64_t* const* outs,
+                                           uint32_t* const* signal_pads, int rank, int world, int n_blocks, void* stream) {
+  return mfl_ckks_fused_weighted_sum_mc(ctx, cts, w, w_shoup, n_src, words, outs, nullptr, signal_pads, rank, world,
+                                        n_blocks, stream);
 }
 
 extern "C" int mfl_ckks_rescale(const mfl_ckks_ctx* ctx, const uint64_t* ct_in, uint32_t n_ct, const uint64_t* qlast_inv,

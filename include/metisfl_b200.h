@@ -361,6 +361,12 @@ int mfl_ckks_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, c
 int mfl_ckks_fused_weighted_sum(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
                                 const uint64_t* w_shoup, int n_src, size_t words, uint64_t* const* outs,
                                 uint32_t* const* signal_pads, int rank, int world, int n_blocks, void* stream);
+/* The same with the result stored through mc_out, the MULTICAST address of the symmetric output buffers (one
+ * multimem.st per 16 bytes lands in every GPU instead of `world` peer stores); mc_out == NULL is the call above. */
+int mfl_ckks_fused_weighted_sum_mc(const mfl_ckks_ctx* ctx, const uint64_t* const* cts, const uint64_t* w,
+                                   const uint64_t* w_shoup, int n_src, size_t words, uint64_t* const* outs,
+                                   uint64_t* mc_out, uint32_t* const* signal_pads, int rank, int world, int n_blocks,
+                                   void* stream);
 /* K9: rescale - drop the last limb: out_l = (c_l - [c_last]_{q_l}) * q_last^-1 mod q_l.
  * qlast_inv / qlast_inv_shoup: host arrays per remaining limb. */
 int mfl_ckks_rescale(const mfl_ckks_ctx* ctx, const uint64_t* ct_in, uint32_t n_ct, const uint64_t* qlast_inv,

@@ -44,6 +44,7 @@ def _bind():
     L.mfl_ckks_decode.argtypes = [P(_Ctx), vp, u32, u32, d, P(u64), vp, vp, vp, sz, vp]
     L.mfl_ckks_weighted_sum.argtypes = [P(_Ctx), P(vp), P(u64), P(u64), i, sz, vp, vp]
     L.mfl_ckks_fused_weighted_sum.argtypes = [P(_Ctx), P(vp), P(u64), P(u64), i, sz, P(vp), P(vp), i, i, i, vp]
+    L.mfl_ckks_fused_weighted_sum_mc.argtypes = [P(_Ctx), P(vp), P(u64), P(u64), i, sz, P(vp), vp, P(vp), i, i, i, vp]
     L.mfl_ckks_rescale.argtypes = [P(_Ctx), vp, u32, P(u64), P(u64), vp, vp]
     _BOUND = True
     return L
@@ -208,13 +209,14 @@ class GpuCKKS:
 
     def fused_weighted_sum(self, src_ptrs: Sequence[int], weights: Sequence[float], words: int,
                            out_ptrs: Sequence[int], pad_ptrs: Sequence[int], rank: int, world: int,
-                           n_blocks: int = 148, scale: float = None):
-        """Every rank calls this with the same arguments: encrypted FedAvg over NVLink peer memory."""
+                           n_blocks: int = 148, scale: float = None, mc_out: int = 0):
+        """Every rank calls this with the same arguments: encrypted FedAvg over NVLink peer memory.  ``mc_out`` = the
+        multicast address of the output buffers (``SymmetricBuffer.mc_ptr``): results go out as one ``multimem.st``."""
         w, wp = scalar_weights(weights, scale or self.scale, self.moduli)
-        _lib.check(self.L.mfl_ckks_fused_weighted_sum(
+        _lib.check(self.L.mfl_ckks_fused_weighted_sum_mc(
             C.byref(self.ctx), _lib.voidp_array(src_ptrs), w, wp, len(src_ptrs), int(words),
-            _lib.voidp_array(out_ptrs), _lib.voidp_array(pad_ptrs), rank, world, n_blocks, _lib.stream_ptr()),
-            "mfl_ckks_fused_weighted_sum")
+            _lib.voidp_array(out_ptrs), int(mc_out) or None, _lib.voidp_array(pad_ptrs), rank, world, n_blocks,
+            _lib.stream_ptr()), "mfl_ckks_fused_weighted_sum_mc")
 
     def rescale_device(self, ct_words: torch.Tensor, n_ct: int, n_limbs: int = None):
         n_limbs = n_limbs or self.n_limbs
