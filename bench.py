@@ -107,7 +107,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "20", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             pass
 
@@ -415,7 +415,7 @@ def main():
                              "ms_per_round_eager": stock_eager_ms or None,
                              "ms_per_round_cuda_graph": stock_graph_ms or None},
             "aggregation": {"k1_fused_ms": k1_ms, "nccl_scale_allreduce_ms": nccl_ms,
-                            "k1_vs_nccl": nccl_ms / k1_ms if k1_ms > 0 else None,
+                            "k1_vs_nccl": nccl_ms / k1_ms if (k1_ms > 0 and world > 1) else None,  # world 1: no collective to compare with
                             "mode": agg_mode,
                             "roofline_ms": roof_ms, "fraction_of_roofline": roof_ms / k1_ms if k1_ms > 0 else None,
                             "roofline_def": "inbound NVLink bytes per GPU (shard reads + result shards; in-switch "
