@@ -93,8 +93,7 @@ class SecureAggregator:
             avg = g.decrypt_device(self.ct_out.local.view(torch.int64)[:self.words], self.n, scale=g.scale * g.scale)
         with self.timer.phase("install"):
             e.arena.seg[0].copy_(avg.to(e.arena.seg[0].dtype))
-            if e.direct_install or True:
-                e.arena.sync_master_from_model()
+            e.arena.sync_master_from_model()   # the fp32 master weights restart from the decrypted average
             if not e.direct_install:
                 e.community_views[0].copy_(e.arena.seg[0])
         if check:  # plaintext oracle (NCCL all-reduce of the same models)
