@@ -172,7 +172,7 @@ class DeviceBackend:
         batch_size = hyperparameters_pb.batch_size or 32
         total_steps = max(1, int(learning_task_pb.num_local_updates))
         src = _Batches(train_dataset, batch_size, shuffle=True, pin=self.device.type == "cuda",
-                       seed=learning_task_pb.global_iteration, cache=self._ds_cache)
+                       seed=learning_task_pb.global_iteration, cache=self._ds_cache, **self._batch_format())
         spe = max(1, src.steps_per_epoch)
         batches = []
         while len(batches) < total_steps:
@@ -254,6 +254,12 @@ class DeviceBackend:
             out[code] = res
         return out
 
+    def _batch_format(self):
+        """Cached host copies of a dataset are kept in what the device consumes: the model dtype, NHWC on CUDA."""
+        if self.device.type != "cuda":
+            return {}
+        return {"x_dtype": self.eval_arena.model_dtype, "channels_last": True}
+
     EVAL_CACHE_LIMIT_BYTES = 8 << 30   # evaluation splits up to this total stay resident in HBM between rounds
 
     def _eval_batches(self, ds, batch_size):
@@ -265,7 +271,7 @@ class DeviceBackend:
             return hit[1]
         cuda = self.device.type == "cuda"
         batches, nbytes = [], 0
-        for x, y in _Batches(ds, batch_size, shuffle=False, pin=cuda, cache=self._ds_cache):
+        for x, y in _Batches(ds, batch_size, shuffle=False, pin=cuda, cache=self._ds_cache, **self._batch_format()):
             x = x.to(self.device, non_blocking=True)
             y = y.to(self.device, non_blocking=True)
             if x.is_floating_point():

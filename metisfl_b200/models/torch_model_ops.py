@@ -80,9 +80,14 @@ class _Batches:
     ``cache`` (a dict owned by the caller, one per learner) keeps the pinned copy of an array dataset and a pinned
     gather buffer across tasks, so a task costs one host-side gather instead of a fresh pin + pageable H2D copies."""
 
-    def __init__(self, dataset: ModelDataset, batch_size: int, shuffle: bool, pin: bool, seed: int = 0, cache=None):
+    def __init__(self, dataset: ModelDataset, batch_size: int, shuffle: bool, pin: bool, seed: int = 0, cache=None,
+                 x_dtype: Optional[torch.dtype] = None, channels_last: bool = False):
+        """``x_dtype`` / ``channels_last`` (only with ``cache``): keep the cached copy of a floating-point ``x`` in the
+        dtype and memory layout the device wants (e.g. bf16 NHWC), converted ONCE - a batch is then a plain DMA into
+        the step's static input buffer, with no conversion kernel and half the bytes."""
         self.loader = None
         self.gather = None
+        self.nhwc_shape = None
         x = dataset.get_x()
         if isinstance(x, torch.utils.data.DataLoader):
             self.loader = x
@@ -94,18 +99,28 @@ class _Batches:
             self.batch_size = batch_size
         else:
             pin = bool(pin and torch.cuda.is_available())
-            ent = cache.get((id(dataset), pin)) if cache is not None else None
+            key = (id(dataset), pin, x_dtype, bool(channels_last))
+            ent = cache.get(key) if cache is not None else None
             if ent is None:
                 tx, ty = _as_tensor(x), _as_tensor(dataset.get_y())
                 if ty is not None and ty.dtype in (torch.int32, torch.int16, torch.uint8, torch.int8):
                     ty = ty.long()
+                nhwc = None
+                if cache is not None and tx.is_floating_point():
+                    if x_dtype is not None and tx.dtype != x_dtype:
+                        tx = tx.to(x_dtype)
+                    if channels_last and tx.dim() == 4:
+                        # stored as [N, H*W*C] rows (physically NHWC); batches are handed out as NCHW views of it
+                        n_, c_, h_, w_ = tx.shape
+                        nhwc = (h_, w_, c_)
+                        tx = tx.permute(0, 2, 3, 1).contiguous().view(n_, -1)
                 if pin:
                     tx = tx.pin_memory()
                     ty = ty.pin_memory() if ty is not None else None
-                ent = {"x": tx, "y": ty, "gx": None, "gy": None, "ref": dataset}  # ref keeps id(dataset) unique
+                ent = {"x": tx, "y": ty, "gx": None, "gy": None, "nhwc": nhwc, "ref": dataset}  # ref: id() stays unique
                 if cache is not None:
-                    cache[(id(dataset), pin)] = ent
-            self.x, self.y = ent["x"], ent["y"]
+                    cache[key] = ent
+            self.x, self.y, self.nhwc_shape = ent["x"], ent["y"], ent["nhwc"]
             if shuffle and pin and cache is not None:
                 if ent["gx"] is None:
                     ent["gx"] = torch.empty_like(self.x).pin_memory()
@@ -134,7 +149,11 @@ class _Batches:
         else:
             x, y = self.x, self.y
         for i in range(0, self.n, self.batch_size):
-            yield x[i:i + self.batch_size], (y[i:i + self.batch_size] if y is not None else None)
+            xb = x[i:i + self.batch_size]
+            if self.nhwc_shape is not None:   # NHWC rows -> NCHW view with channels_last strides (no copy)
+                h_, w_, c_ = self.nhwc_shape
+                xb = xb.view(xb.shape[0], h_, w_, c_).permute(0, 3, 1, 2)
+            yield xb, (y[i:i + self.batch_size] if y is not None else None)
 
 
 class TorchModelOps(ModelOps):
