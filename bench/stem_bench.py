@@ -32,7 +32,8 @@ w = torch.randn(k, c, 3, 3, device="cuda").to(torch.bfloat16).contiguous(memory_
 gy = torch.randn(n, k, h, h, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
 res = {"shape": [n, c, h, h, k]}
 res["fprop_cudnn_us"] = timeit(lambda: torch.nn.functional.conv2d(x, w, padding=1))
-res["fprop_own_us"] = timeit(lambda: C._StemFn.apply(x, w))
+res["fprop_own_us"] = timeit(lambda: C._StemFn.apply(x, w))            # FMA kernel (K11s)
+res["fprop_im2col_gemm_us"] = timeit(lambda: C._StemGemmFn.apply(x, w))  # patch matrix + K10
 res["wgrad_cudnn_us"] = timeit(lambda: torch.ops.aten.convolution_backward(
     gy, x, w, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1, [False, True, False]))
 # the weight-gradient kernel pair called directly (through autograd the Python overhead would dominate the timing)
@@ -45,6 +46,10 @@ def own_wgrad():
                                             st.cuda_stream)
     _lib.check(rc, "mfl_conv_stem_wgrad_bf16", launches=2)
 res["wgrad_own_us"] = timeit(own_wgrad)
+from metisfl_b200.ops import gemm as G  # noqa: E402
+patches = torch.empty((n * h * h, 32), dtype=torch.bfloat16, device="cuda")
+g2 = gy.permute(0, 2, 3, 1).reshape(n * h * h, k)
+res["wgrad_im2col_gemm_us"] = timeit(lambda: G.gemm_ex(g2, patches, a_mn=True, b_mn=True))   # split-k K10 + finalize
 ref = torch.nn.functional.conv2d(x.float(), w.float(), padding=1)
 res["fprop_max_err"] = float((C._StemFn.apply(x, w).float() - ref).abs().max())
 print(json.dumps(res))

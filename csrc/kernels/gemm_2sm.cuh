@@ -237,6 +237,9 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   } else if (warp >= 4) {  // ===== epilogue (both CTAs): own 128 rows of the pair's tile =====
     const int wq = warp & 3;
     uint32_t t = 0;
+    // staging-slab parity runs ACROSS tiles: BN = 192 has three bf16 chunks per tile, and a per-tile counter would
+    // reuse the slab whose TMA store `wait_group.read 1` still allows to be in flight
+    uint32_t chunk = 0;
     for (int w = cluster_id; w < num_tiles; w += n_clusters, ++t) {
       int tm, tn;
       tile_coords(w, tiles_m, tiles_n, tm, tn);
@@ -259,9 +262,8 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       if (p.tma_store) {
         constexpr int cols = C_FP32 ? 32 : 64;
         uint8_t* slabs = store_slabs + wq * 8192;
-        uint32_t chunk = 0;
 #pragma unroll 1
-        for (int c = 0; c < BN; c += cols, ++chunk) {
+        for (int c = 0; c < BN; c += cols) {
           uint32_t r[cols];
           tmem_ld_32x32(tacc + (uint32_t)c, r);
           if constexpr (!C_FP32) tmem_ld_32x32(tacc + (uint32_t)(c + 32), r + 32);
@@ -287,6 +289,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             tma_store_2d(&tmap_c, slab, n0 + c, m0 + wq * 32);
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
+          ++chunk;  // counts issued stores only (skipped chunks must not flip the slab parity)
         }
       } else {
 #pragma unroll 1

@@ -256,6 +256,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   } else if (warp >= 4) {  // ===== epilogue: TMEM -> registers -> global =====
     const int wq = warp & 3;  // TMEM lane quarter this warp may access
     uint32_t t = 0;
+    // staging-slab parity runs ACROSS tiles: with an odd number of chunks per tile (one for BN = 64 bf16) a per-tile
+    // counter would reuse the slab whose TMA store `wait_group.read 1` still allows to be in flight
+    uint32_t chunk = 0;
     for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++t) {
       const int cls = w / work_per_cls;
       const int tile = (w - cls * work_per_cls) / splits;
@@ -281,9 +284,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
         // the TMA store engine (which also clips the ragged M / N edges).
         constexpr int cols = C_FP32 ? 32 : 64;  // columns per 128-byte slab row
         uint8_t* slabs = store_slabs + wq * 8192;
-        uint32_t chunk = 0;
 #pragma unroll 1
-        for (int c = 0; c < BN; c += cols, ++chunk) {
+        for (int c = 0; c < BN; c += cols) {
           uint32_t r[cols];
           tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)c, r);
           if constexpr (!C_FP32) tmem_ld_32x32(tmem_base + ((uint32_t)(wq * 32) << 16) + buf * BN + (uint32_t)(c + 32), r + 32);
@@ -317,6 +319,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
             }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
+          ++chunk;  // counts issued stores only (skipped chunks past N must not flip the slab parity)
         }
       } else {
 #pragma unroll 1

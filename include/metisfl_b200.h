@@ -266,6 +266,10 @@ int mfl_conv_stem_supported(int c, int k);
 int mfl_conv_stem_fprop_bf16(void* y, const void* x, const void* w, int n, int h, int wd, int c, int k, void* stream);
 int mfl_conv_stem_wgrad_bf16(void* dw, const void* dy, const void* x, float* ws, int n, int h, int wd, int c, int k,
                              int accumulate, void* stream);
+/* The stem on the tensor cores: patches[n*h*w, 32] (bf16; column (r*3+s)*c + ch, zero padded; c <= 3).  Forward is
+ * then mfl_gemm_bf16(y, patches, w32) with w32 = the [k, 9c] filters padded to 32 columns, the weight gradient
+ * mfl_gemm_bf16_ws(dw32, dy as MN-major A, patches as MN-major B) - see metisfl_b200/ops/conv.py: _StemGemmFn. */
+int mfl_conv_stem_im2col_bf16(void* patches, const void* x, int n, int h, int wd, int c, void* stream);
 
 /* ---- K16: fused softmax cross-entropy for a language-model head (csrc/kernels/cross_entropy.cu): per-row loss and
  * d(loss)/d(logits) in one pass pair over bf16 logits, no fp32 copy.  logits [rows, vocab] bf16 with row pitch ld,

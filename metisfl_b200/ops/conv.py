@@ -46,6 +46,7 @@ def _bind():
         L.mfl_conv_stem_supported.argtypes = [i, i]
         L.mfl_conv_stem_fprop_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, vp]
         L.mfl_conv_stem_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, vp]
+        L.mfl_conv_stem_im2col_bf16.argtypes = [vp, vp, i, i, i, i, vp]
         L.mfl_conv2d_wgrad_bf16.argtypes = [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, vp]
         L.mfl_conv2d_dgrad_bf16.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
         L.mfl_conv2d_fprop_bf16_ws.argtypes = [vp, vp, vp, vp, C.c_size_t, i, i, i, i, i, i, i, i, i, vp]
@@ -233,6 +234,56 @@ class _StemFn(torch.autograd.Function):
         return gx, gw
 
 
+STEM_GEMM = os.environ.get("MFL_STEM_GEMM", "1") != "0"   # default path: the stem as im2col + K10 GEMMs
+_PATCH_COLS = 32
+
+
+def stem_gemm_supported(x: torch.Tensor, w: torch.Tensor, stride, padding, dilation=(1, 1), groups=1) -> bool:
+    """3x3 / stride 1 / padding 1 over an image with at most 3 channels (27 patch values fit a 32-wide row)."""
+    return (x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dim() == 4
+            and x.shape[1] <= 3 and tuple(w.shape[2:]) == (3, 3) and tuple(stride) == (1, 1)
+            and tuple(padding) == (1, 1) and tuple(dilation) == (1, 1) and groups == 1 and w.shape[0] % 8 == 0
+            and _lib.available())
+
+
+class _StemGemmFn(torch.autograd.Function):
+    """The stem on the tensor cores (``csrc/kernels/conv_stem.cu: stem_im2col_kernel``): one small kernel writes the
+    [N*H*W, 32] patch matrix, the forward is ``patches . W32^T`` on K10, the weight gradient ``dY^T . patches`` on K10
+    with split k (both operands read MN-major, no transposed copies).  The patch matrix (64 bytes per pixel) is kept
+    for the backward pass."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        from metisfl_b200.ops import gemm as G
+        n, c, h, wd = x.shape
+        k = w.shape[0]
+        x = x.contiguous(memory_format=torch.channels_last)
+        patches = torch.empty((n * h * wd, _PATCH_COLS), dtype=torch.bfloat16, device=x.device)
+        rc = _bind().mfl_conv_stem_im2col_bf16(patches.data_ptr(), x.data_ptr(), n, h, wd, c, _lib.stream_ptr())
+        _lib.check(rc, "mfl_conv_stem_im2col_bf16")
+        w_rows = w.permute(0, 2, 3, 1).reshape(k, 9 * c)            # [K, R, S, C]: a view of NHWC-stored filters
+        w32 = torch.nn.functional.pad(w_rows, (0, _PATCH_COLS - 9 * c))
+        y = G.gemm_nt(patches, w32)                                  # [N*H*W, K]
+        ctx.save_for_backward(patches, x, w)
+        return y.view(n, h, wd, k).permute(0, 3, 1, 2)               # NCHW view of the NHWC result
+
+    @staticmethod
+    def backward(ctx, gy):
+        from metisfl_b200.ops import gemm as G
+        patches, x, w = ctx.saved_tensors
+        n, c, h, wd = x.shape
+        k = w.shape[0]
+        gx = gw = None
+        if ctx.needs_input_grad[0]:  # an image that wants a gradient: rare, leave it to the library
+            gx = torch.ops.aten.convolution_backward(gy, x, w, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1,
+                                                     [True, False, False])[0]
+        if ctx.needs_input_grad[1]:
+            g2 = gy.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1).reshape(n * h * wd, k)
+            gw32 = G.gemm_ex(g2, patches, a_mn=True, b_mn=True)      # [K, 32] = dY^T . patches, reduction over pixels
+            gw = gw32[:, :9 * c].reshape(k, 3, 3, c).permute(0, 3, 1, 2)
+        return gx, gw
+
+
 def conv3x3_dgrad(gy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     """K15 in data-gradient mode: dX of ``conv3x3(x, w)`` from gy [N,K,H,W]; w is the FORWARD filter [K,C,3,3]."""
     n, k, h, wd = gy.shape
@@ -344,7 +395,7 @@ def conv2d(x: torch.Tensor, w: torch.Tensor, bias=None, stride=(1, 1), padding=(
     padding = (padding, padding) if isinstance(padding, int) else tuple(padding)
     if isinstance(padding, tuple) and groups == 1 and stem_supported(x, w, stride, padding) and \
             (dilation == 1 or tuple(dilation) == (1, 1)):
-        y = _StemFn.apply(x, w)
+        y = _StemGemmFn.apply(x, w) if (STEM_GEMM and stem_gemm_supported(x, w, stride, padding)) else _StemFn.apply(x, w)
         return y if bias is None else y + bias.view(1, -1, 1, 1)
     if isinstance(padding, tuple) and supported(x, w, stride, padding, dilation if not isinstance(dilation, int)
                                                 else (dilation, dilation), groups):
@@ -480,6 +531,9 @@ class OverlappedConv2d(nn.Conv2d):
     def forward(self, x):
         if (x.is_cuda and self.bias is None and self.padding_mode == "zeros" and not isinstance(self.padding, str)
                 and torch.is_grad_enabled()):
+            if HYBRID and STEM_GEMM and stem_gemm_supported(x, self.weight, self.stride, self.padding, self.dilation,
+                                                              self.groups):
+                return _StemGemmFn.apply(x, self.weight)   # the 3-channel stem: im2col + K10 (fwd and dW)
             return _OverlapConvFn.apply(x, self.weight, self.stride, self.padding, self.dilation, self.groups)
         return super().forward(x)
 

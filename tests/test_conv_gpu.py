@@ -149,6 +149,9 @@ def test_stem_convolution_matches_reference(n, c, h, w, k):
 
 
 def test_resnet18_with_b200_conv_tracks_cudnn():
+    """Every convolution on the hand-written kernels (stem as im2col + K10 included): the loss matches the cuDNN
+    bf16 model, and the gradients are as close to an fp32 run of the same network as cuDNN's bf16 gradients are
+    (two bf16 runs differ from each other by rounding noise that ReLU masks amplify, so fp32 is the yardstick)."""
     from metisfl_b200.models.zoo import ResNet18
     from metisfl_b200.ops import conv
     torch.manual_seed(0)
@@ -156,17 +159,27 @@ def test_resnet18_with_b200_conv_tracks_cudnn():
     ours = ResNet18().cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
     ours.load_state_dict(ref.state_dict())
     conv.use_b200_conv(ours)
+    exact = ResNet18().cuda().to(memory_format=torch.channels_last)
+    exact.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
     x = torch.randn(32, 3, 32, 32, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     y = torch.randint(0, 10, (32,), device="cuda")
     losses = []
     for model in (ref, ours):
         loss = F.cross_entropy(model(x).float(), y)
         loss.backward()
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
+    F.cross_entropy(exact(x.float()), y).backward()
     assert abs(losses[0] - losses[1]) < 5e-2, losses
-    gr = dict(ref.named_parameters())["layers.0.conv1.weight"].grad.float()
-    go = dict(ours.named_parameters())["layers.0.conv1.weight"].grad.float()
-    assert torch.nn.functional.cosine_similarity(gr.flatten(), go.flatten(), dim=0) > 0.98
+    cos = lambda a, b: float(torch.nn.functional.cosine_similarity(a.flatten().float(), b.flatten().float(), dim=0))
+    pe = dict(exact.named_parameters())
+    worst = 1.0
+    for (name, pr), (_, po) in zip(ref.named_parameters(), ours.named_parameters()):
+        if pr.dim() != 4:
+            continue
+        c_lib, c_own = cos(pr.grad, pe[name].grad), cos(po.grad, pe[name].grad)
+        assert c_own > c_lib - 0.03 and c_own > 0.9, (name, c_own, c_lib)
+        worst = min(worst, c_own)
+    assert worst > 0.9
 
 
 def test_hybrid_dispatch_gradients_match_the_library_path():
@@ -178,22 +191,27 @@ def test_hybrid_dispatch_gradients_match_the_library_path():
     x = torch.randn(32, 3, 32, 32, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     y = torch.randint(0, 10, (32,), device="cuda")
     grads = []
-    for hybrid in (False, True):
+    for hybrid, dtype in ((False, torch.bfloat16), (True, torch.bfloat16), (False, torch.float32)):
         torch.manual_seed(0)
         m = ResNet18().to(memory_format=torch.channels_last)
         conv.use_overlapped_wgrad(m)
-        arena = ModelArena(m, "cuda", torch.bfloat16)
+        arena = ModelArena(m, "cuda", dtype)
         old = conv.HYBRID
         conv.HYBRID = hybrid
         try:
-            F.cross_entropy(m(x).float(), y).backward()
+            F.cross_entropy(m(x.to(dtype)).float(), y).backward()
             conv.join()
         finally:
             conv.HYBRID = old
         torch.cuda.synchronize()
-        grads.append(arena.grad[0].float().clone())
-    err = (grads[0] - grads[1]).norm() / grads[0].norm()
-    assert err < 2e-2, float(err)
+        grads.append(torch.cat([p.grad.float().flatten() for p in m.parameters()]))   # same order in every run
+    lib, hyb, exact = grads
+    # two bf16 runs differ by rounding noise (the stem's forward now runs on another kernel, ReLU masks flip): the
+    # yardstick is the fp32 run of the same network
+    err_lib = float((lib - exact).norm() / exact.norm())
+    err_hyb = float((hyb - exact).norm() / exact.norm())
+    assert err_hyb < 1.5 * err_lib + 1e-2, (err_hyb, err_lib)
+    assert float(torch.nn.functional.cosine_similarity(hyb, exact, dim=0)) > 0.95
 
 
 def test_overlapped_wgrad_matches_autograd_eager_and_in_a_graph():
@@ -247,3 +265,24 @@ def test_weight_stationary_conv3x3_matches_reference(n, c, h, w, k):
     torch.testing.assert_close(y.float(), ref, atol=3e-2, rtol=3e-2)
     torch.testing.assert_close(stats[0], y.float().sum(dim=(0, 2, 3)), atol=0.5, rtol=2e-2)
     torch.testing.assert_close(stats[1], (y.float() ** 2).sum(dim=(0, 2, 3)), atol=0.5, rtol=2e-2)
+
+
+@pytest.mark.parametrize("n,c,h,w,k", [(128, 3, 32, 32, 64), (5, 3, 9, 7, 64), (16, 1, 28, 28, 32), (4, 2, 6, 6, 8)])
+def test_stem_as_im2col_plus_gemm_matches_fp32_reference(n, c, h, w, k):
+    """The stem on the tensor cores: patch matrix + K10 forward, split-k K10 weight gradient (both operands MN-major)."""
+    from metisfl_b200.ops import conv as C
+    g = torch.Generator().manual_seed(n + c + h + k)
+    x = torch.randn(n, c, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, 3, 3, generator=g) / 3).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(n, k, h, w, generator=g).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    assert C.stem_gemm_supported(x, wt, (1, 1), (1, 1))
+    wr = wt.clone().requires_grad_()
+    y = C._StemGemmFn.apply(x, wr)
+    y.backward(gy)
+    xf, wf = x.float(), wt.float().requires_grad_()
+    ref = torch.nn.functional.conv2d(xf, wf, padding=1)
+    ref.backward(gy.float())
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    torch.testing.assert_close(y.float(), ref, atol=3e-2, rtol=3e-2)
+    scale = max(1.0, float(wf.grad.abs().max()))
+    assert float((wr.grad.float() - wf.grad).abs().max()) < 2e-2 * scale, (float((wr.grad.float() - wf.grad).abs().max()), scale)
