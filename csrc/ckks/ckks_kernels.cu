@@ -27,6 +27,13 @@ using namespace ::mfl::ckks;
 
 constexpr int kNttThreads = 1024;
 
+// Shared-memory placement of coefficient i of the polynomial a CTA works on: one 8-byte pad after every 16
+// coefficients.  The last two radix-4 passes touch coefficients 4 and 1 apart with 16- and 4-coefficient strides
+// between lanes; unpadded, the 32 lanes of a warp then fall on 4 bank pairs (8-way conflicts on all eight accesses of
+// a butterfly: about a third of the transform's time); padded they spread over all 16 (q4 = 1) or 11 (q4 = 4).
+__device__ __forceinline__ uint32_t px(uint32_t i) { return i + (i >> 4); }
+static size_t poly_smem_bytes(int log_n) { return sizeof(uint64_t) * (((size_t)1 << log_n) + ((size_t)1 << log_n >> 4) + 1); }
+
 struct Ctx {  // by-value copy of mfl_ckks_ctx for kernel parameters
   mfl_ckks_ctx c;
 };
@@ -43,45 +50,86 @@ __device__ __forceinline__ uint64_t d_add(uint64_t a, uint64_t b, uint64_t q) {
 __device__ __forceinline__ uint64_t d_sub(uint64_t a, uint64_t b, uint64_t q) { return a >= b ? a - b : a + q - b; }
 
 // Forward negacyclic NTT of one polynomial held in shared memory (Cooley-Tukey, natural -> bit-reversed).
+// Radix 4: two consecutive radix-2 stages (m, 2m) are applied to four elements in registers, so a polynomial of 2^14
+// coefficients takes 7 passes over shared memory and 7 block barriers instead of 14 (one leading radix-2 stage when
+// log_n is odd).  Same butterflies, same twiddle table, same results bit for bit as the radix-2 loop.
 __device__ void ntt_forward_smem(uint64_t* x, const uint64_t* __restrict__ w, const uint64_t* __restrict__ wp,
                                  uint64_t q, int log_n) {
-  const int n = 1 << log_n, half = n >> 1;
-  int t = n;
-  for (int m = 1; m < n; m <<= 1) {
+  const int n = 1 << log_n;
+  int t = n, m = 1;
+  if (log_n & 1) {  // one radix-2 stage first
     t >>= 1;
-    const int log_t = __ffs(t) - 1;
-    for (int b = threadIdx.x; b < half; b += blockDim.x) {
-      const int i = b >> log_t, j = b & (t - 1);
-      const int idx = (i << (log_t + 1)) + j;
-      const uint64_t s = __ldg(w + m + i), sp = __ldg(wp + m + i);
-      const uint64_t u = x[idx], v = d_mul_shoup(x[idx + t], s, sp, q);
-      x[idx] = d_add(u, v, q);
-      x[idx + t] = d_sub(u, v, q);
+    for (int b = threadIdx.x; b < (n >> 1); b += blockDim.x) {
+      const uint64_t s = __ldg(w + 1), sp = __ldg(wp + 1);
+      const uint64_t u = x[px(b)], v = d_mul_shoup(x[px(b + t)], s, sp, q);
+      x[px(b)] = d_add(u, v, q);
+      x[px(b + t)] = d_sub(u, v, q);
     }
     __syncthreads();
+    m = 2;
+  }
+  for (; m < n; m <<= 2) {
+    // stage A: (m, t/2) pairs at distance t/2 ... written with t = distance of stage A's pairs
+    t >>= 1;                       // pair distance of the first of the two stages
+    const int q4 = t >> 1;         // pair distance of the second stage = quarter of the 2t-wide block
+    const int log_q4 = __ffs(q4) - 1;
+    for (int b = threadIdx.x; b < (n >> 2); b += blockDim.x) {
+      const int i = b >> log_q4, j = b & (q4 - 1);
+      const int idx = (i << (log_q4 + 2)) + j;
+      const uint64_t w1 = __ldg(w + m + i), w1p = __ldg(wp + m + i);
+      const uint64_t w2 = __ldg(w + 2 * m + 2 * i), w2p = __ldg(wp + 2 * m + 2 * i);
+      const uint64_t w3 = __ldg(w + 2 * m + 2 * i + 1), w3p = __ldg(wp + 2 * m + 2 * i + 1);
+      const uint64_t a0 = x[px(idx)], a1 = x[px(idx + q4)], a2 = x[px(idx + 2 * q4)], a3 = x[px(idx + 3 * q4)];
+      const uint64_t v2 = d_mul_shoup(a2, w1, w1p, q), v3 = d_mul_shoup(a3, w1, w1p, q);
+      const uint64_t b0 = d_add(a0, v2, q), b2 = d_sub(a0, v2, q);
+      const uint64_t b1 = d_add(a1, v3, q), b3 = d_sub(a1, v3, q);
+      const uint64_t u1 = d_mul_shoup(b1, w2, w2p, q), u3 = d_mul_shoup(b3, w3, w3p, q);
+      x[px(idx)] = d_add(b0, u1, q);
+      x[px(idx + q4)] = d_sub(b0, u1, q);
+      x[px(idx + 2 * q4)] = d_add(b2, u3, q);
+      x[px(idx + 3 * q4)] = d_sub(b2, u3, q);
+    }
+    __syncthreads();
+    t >>= 1;
   }
 }
 
-// Inverse (Gentleman-Sande, bit-reversed -> natural), including the 1/N scaling.
+// Inverse (Gentleman-Sande, bit-reversed -> natural), including the 1/N scaling; radix 4 like the forward transform
+// (the trailing radix-2 stage when log_n is odd), with the 1/N factor folded into the last pass.
 __device__ void ntt_inverse_smem(uint64_t* x, const uint64_t* __restrict__ w, const uint64_t* __restrict__ wp,
                                  uint64_t q, uint64_t n_inv, uint64_t n_inv_shoup, int log_n) {
-  const int n = 1 << log_n, half = n >> 1;
-  int t = 1;
-  for (int m = n; m > 1; m >>= 1) {
-    const int h = m >> 1;
+  const int n = 1 << log_n;
+  int t = 1, m = n;
+  for (; m > 2; m >>= 2) {
+    const int h = m >> 1;           // twiddle base of the first stage (pairs at distance t)
     const int log_t = __ffs(t) - 1;
-    for (int b = threadIdx.x; b < half; b += blockDim.x) {
-      const int i = b >> log_t, j = b & (t - 1);
-      const int idx = (i << (log_t + 1)) + j;
-      const uint64_t s = __ldg(w + h + i), sp = __ldg(wp + h + i);
-      const uint64_t u = x[idx], v = x[idx + t];
-      x[idx] = d_add(u, v, q);
-      x[idx + t] = d_mul_shoup(d_sub(u, v, q), s, sp, q);
+    for (int b = threadIdx.x; b < (n >> 2); b += blockDim.x) {
+      const int i = b >> log_t, j = b & (t - 1);      // i indexes blocks of 4t elements
+      const int idx = (i << (log_t + 2)) + j;
+      const uint64_t s0 = __ldg(w + h + 2 * i), s0p = __ldg(wp + h + 2 * i);
+      const uint64_t s1 = __ldg(w + h + 2 * i + 1), s1p = __ldg(wp + h + 2 * i + 1);
+      const uint64_t s2 = __ldg(w + (h >> 1) + i), s2p = __ldg(wp + (h >> 1) + i);
+      const uint64_t a0 = x[px(idx)], a1 = x[px(idx + t)], a2 = x[px(idx + 2 * t)], a3 = x[px(idx + 3 * t)];
+      const uint64_t b0 = d_add(a0, a1, q), b1 = d_mul_shoup(d_sub(a0, a1, q), s0, s0p, q);
+      const uint64_t b2 = d_add(a2, a3, q), b3 = d_mul_shoup(d_sub(a2, a3, q), s1, s1p, q);
+      x[px(idx)] = d_add(b0, b2, q);
+      x[px(idx + 2 * t)] = d_mul_shoup(d_sub(b0, b2, q), s2, s2p, q);
+      x[px(idx + t)] = d_add(b1, b3, q);
+      x[px(idx + 3 * t)] = d_mul_shoup(d_sub(b1, b3, q), s2, s2p, q);
     }
     __syncthreads();
-    t <<= 1;
+    t <<= 2;
   }
-  for (int i = threadIdx.x; i < n; i += blockDim.x) x[i] = d_mul_shoup(x[i], n_inv, n_inv_shoup, q);
+  if (m == 2) {  // odd log_n: the last radix-2 stage (h = 1, pairs at distance n / 2)
+    const uint64_t s = __ldg(w + 1), sp = __ldg(wp + 1);
+    for (int b = threadIdx.x; b < (n >> 1); b += blockDim.x) {
+      const uint64_t u = x[px(b)], v = x[px(b + t)];
+      x[px(b)] = d_add(u, v, q);
+      x[px(b + t)] = d_mul_shoup(d_sub(u, v, q), s, sp, q);
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) x[px(i)] = d_mul_shoup(x[px(i)], n_inv, n_inv_shoup, q);
   __syncthreads();
 }
 
@@ -92,11 +140,11 @@ __global__ void __launch_bounds__(kNttThreads, 1) ntt_rows_kernel(const __grid_c
   for (size_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
     const int l = (int)(r % cx.c.n_limbs);
     uint64_t* g = rows + r * n;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) sm[i] = g[i];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) sm[px(i)] = g[i];
     __syncthreads();
     if (inverse) ntt_inverse_smem(sm, cx.c.ipsi[l], cx.c.ipsi_shoup[l], cx.c.q[l], cx.c.n_inv[l], cx.c.n_inv_shoup[l], cx.c.log_n);
     else ntt_forward_smem(sm, cx.c.psi[l], cx.c.psi_shoup[l], cx.c.q[l], cx.c.log_n);
-    for (int i = threadIdx.x; i < n; i += blockDim.x) g[i] = sm[i];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) g[i] = sm[px(i)];
     __syncthreads();
   }
 }
@@ -295,12 +343,12 @@ __global__ void __launch_bounds__(kNttThreads, 1) encrypt_kernel(const __grid_co
     for (uint32_t b = threadIdx.x; b < nb16; b += blockDim.x) {
       rng.block(ctr0 | b, 0, r);
 #pragma unroll
-      for (int j = 0; j < 16; ++j) sm[j * nb16 + b] = signed_to_mod(ternary_from_bits(r[j]), q);
+      for (int j = 0; j < 16; ++j) sm[px(j * nb16 + b)] = signed_to_mod(ternary_from_bits(r[j]), q);
     }
     __syncthreads();
     ntt_forward_smem(sm, w, wp, q, log_n);
     for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) {
-      const uint64_t u = sm[i];
+      const uint64_t u = sm[px(i)];
       c0[i] = d_mul_shoup(u, pk0[i], pk0s[i], q);
       c1[i] = d_mul_shoup(u, pk1[i], pk1s[i], q);
     }
@@ -313,22 +361,22 @@ __global__ void __launch_bounds__(kNttThreads, 1) encrypt_kernel(const __grid_co
         const uint32_t i = j * nb8 + b;
         uint64_t t = signed_to_mod(gaussian_from_bits(r[2 * j], r[2 * j + 1], kSigma), q);
         if (i % gap == 0) t = d_add(t, double_to_mod(m[i / gap], q, two40), q);
-        sm[i] = t;
+        sm[px(i)] = t;
       }
     }
     __syncthreads();
     ntt_forward_smem(sm, w, wp, q, log_n);
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) c0[i] = d_add(c0[i], sm[i], q);
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) c0[i] = d_add(c0[i], sm[px(i)], q);
     __syncthreads();
     // pass 3: c1 += NTT(e1)
     for (uint32_t b = threadIdx.x; b < nb8; b += blockDim.x) {
       rng.block(ctr0 | b, 2, r);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) sm[j * nb8 + b] = signed_to_mod(gaussian_from_bits(r[2 * j], r[2 * j + 1], kSigma), q);
+      for (int j = 0; j < 8; ++j) sm[px(j * nb8 + b)] = signed_to_mod(gaussian_from_bits(r[2 * j], r[2 * j + 1], kSigma), q);
     }
     __syncthreads();
     ntt_forward_smem(sm, w, wp, q, log_n);
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) c1[i] = d_add(c1[i], sm[i], q);
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) c1[i] = d_add(c1[i], sm[px(i)], q);
     __syncthreads();
   }
 }
@@ -345,11 +393,11 @@ __global__ void __launch_bounds__(kNttThreads, 1) decrypt_kernel(const __grid_co
     const uint64_t* c0 = ct + ((size_t)c * 2 * L + l) * N;
     const uint64_t* c1 = c0 + (size_t)L * N;
     const uint64_t *s = sk + (size_t)l * N, *ss = sks + (size_t)l * N;
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) sm[i] = d_add(c0[i], d_mul_shoup(c1[i], s[i], ss[i], q), q);
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) sm[px(i)] = d_add(c0[i], d_mul_shoup(c1[i], s[i], ss[i], q), q);
     __syncthreads();
     ntt_inverse_smem(sm, cx.c.ipsi[l], cx.c.ipsi_shoup[l], q, cx.c.n_inv[l], cx.c.n_inv_shoup[l], log_n);
     uint64_t* out = residues + ((size_t)c * L + l) * N;
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) out[i] = sm[i];
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) out[i] = sm[px(i)];
     __syncthreads();
   }
 }
@@ -563,19 +611,19 @@ __global__ void __launch_bounds__(kNttThreads, 1) rescale_kernel(const __grid_co
     const uint32_t p = job / Lo, l = job % Lo;
     const uint64_t q = cx.c.q[l];
     const uint64_t* last = ct_in + ((size_t)p * L + (L - 1)) * N;
-    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) sm[i] = last[i];
+    for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) sm[px(i)] = last[i];
     __syncthreads();
     ntt_inverse_smem(sm, cx.c.ipsi[L - 1], cx.c.ipsi_shoup[L - 1], ql, cx.c.n_inv[L - 1], cx.c.n_inv_shoup[L - 1], log_n);
     for (uint32_t i = threadIdx.x; i < N; i += blockDim.x) {
-      const uint64_t c = sm[i];
-      sm[i] = c > ql / 2 ? d_sub(c % q, ql % q, q) : c % q;
+      const uint64_t c = sm[px(i)];
+      sm[px(i)] = c > ql / 2 ? d_sub(c % q, ql % q, q) : c % q;
     }
     __syncthreads();
     ntt_forward_smem(sm, cx.c.psi[l], cx.c.psi_shoup[l], q, log_n);
     const uint64_t* cin = ct_in + ((size_t)p * L + l) * N;
     uint64_t* co = ct_out + ((size_t)p * Lo + l) * N;
     for (uint32_t i = threadIdx.x; i < N; i += blockDim.x)
-      co[i] = d_mul_shoup(d_sub(cin[i], sm[i], q), ra.qinv[l], ra.qinv_shoup[l], q);
+      co[i] = d_mul_shoup(d_sub(cin[i], sm[px(i)], q), ra.qinv[l], ra.qinv_shoup[l], q);
     __syncthreads();
   }
 }
@@ -610,7 +658,7 @@ using namespace mfl::ckksdev;
 extern "C" int mfl_ckks_ntt(const mfl_ckks_ctx* ctx, uint64_t* rows, size_t n_rows, int inverse, void* stream) {
   if (int rc = check_ctx(ctx)) return rc;
   if (n_rows == 0) return 0;
-  const size_t smem = sizeof(uint64_t) << ctx->log_n;
+  const size_t smem = poly_smem_bytes(ctx->log_n);
   if (int rc = allow_smem(ntt_rows_kernel, smem)) return rc;
   Ctx cx{*ctx};
   const int blocks = (int)std::min<size_t>(n_rows, (size_t)sm_count());
@@ -639,7 +687,7 @@ extern "C" int mfl_ckks_encrypt(const mfl_ckks_ctx* ctx, const double* coeffs, u
   if (n_ct == 0) return 0;
   ChaChaKey key;
   for (int i = 0; i < 8; ++i) key.k[i] = key256[i];
-  const size_t smem = sizeof(uint64_t) << ctx->log_n;
+  const size_t smem = poly_smem_bytes(ctx->log_n);
   if (int rc = allow_smem(encrypt_kernel, smem)) return rc;
   Ctx cx{*ctx};
   const int blocks = (int)std::min<size_t>((size_t)n_ct * ctx->n_limbs, (size_t)sm_count());
@@ -651,7 +699,7 @@ extern "C" int mfl_ckks_decrypt(const mfl_ckks_ctx* ctx, const uint64_t* ct, uin
                                 const uint64_t* sk_shoup, uint64_t* residues, void* stream) {
   if (int rc = check_ctx(ctx)) return rc;
   if (n_ct == 0) return 0;
-  const size_t smem = sizeof(uint64_t) << ctx->log_n;
+  const size_t smem = poly_smem_bytes(ctx->log_n);
   if (int rc = allow_smem(decrypt_kernel, smem)) return rc;
   Ctx cx{*ctx};
   const int blocks = (int)std::min<size_t>((size_t)n_ct * ctx->n_limbs, (size_t)sm_count());
@@ -722,7 +770,7 @@ extern "C" int mfl_ckks_rescale(const mfl_ckks_ctx* ctx, const uint64_t* ct_in, 
   if (int rc = check_ctx(ctx)) return rc;
   MFL_ARG(ctx->n_limbs >= 2, "ckks_rescale: no limb left to drop");
   if (n_ct == 0) return 0;
-  const size_t smem = sizeof(uint64_t) << ctx->log_n;
+  const size_t smem = poly_smem_bytes(ctx->log_n);
   if (int rc = allow_smem(rescale_kernel, smem)) return rc;
   Ctx cx{*ctx};
   RescaleArgs ra{};
