@@ -114,3 +114,51 @@ def test_keras_backend_trains_within_the_step_budget_and_reports_metadata():
     assert int(fresh._model.seen[0]) == int(m.seen[0]) == 7 * 16
     ev = fresh.evaluate_model(_dataset(), 32, ["accuracy"])
     assert ev["accuracy"] > 0.5 and fresh.infer_model(_dataset(8, 5)).shape == (8, 3)
+
+
+def test_optimizer_configs_map_onto_the_compiled_optimizer():
+    """``construct_optimizer`` overwrites only what the federation configures (keras_model_ops.py:245-283): proto3
+    zero values of optional hyper-parameters keep what the model was compiled with; the learning rate is always set."""
+    m = FakeKerasModel()
+    m.optimizer = SimpleNamespace(learning_rate=0.5, momentum=0.3, mu=0.01, beta_1=0.8, beta_2=0.9, epsilon=1e-5,
+                                  weight_decay=0.0)
+    ops = KerasModelOps(model=m)
+    ops.construct_optimizer(model_pb2.OptimizerConfig(vanilla_sgd=model_pb2.VanillaSGD(learning_rate=0.1)))
+    close = lambda a, b: abs(a - b) < 1e-6 * max(1.0, abs(b))   # proto floats are fp32
+    assert close(m.optimizer.learning_rate, 0.1) and m.optimizer.momentum == 0.3
+    ops.construct_optimizer(model_pb2.OptimizerConfig(fed_prox=model_pb2.FedProx(learning_rate=0.2, proximal_term=0.5)))
+    assert close(m.optimizer.learning_rate, 0.2) and m.optimizer.mu == 0.5
+    ops.construct_optimizer(model_pb2.OptimizerConfig(adam=model_pb2.Adam(learning_rate=0.001, beta_1=0.95)))
+    assert close(m.optimizer.learning_rate, 0.001) and abs(m.optimizer.beta_1 - 0.95) < 1e-6
+    assert m.optimizer.beta_2 == 0.9 and m.optimizer.epsilon == 1e-5            # unset in the message: untouched
+    ops.construct_optimizer(model_pb2.OptimizerConfig(
+        adam_weight_decay=model_pb2.AdamWeightDecay(learning_rate=0.003, weight_decay=0.02)))
+    assert close(m.optimizer.learning_rate, 0.003) and abs(m.optimizer.weight_decay - 0.02) < 1e-7
+    assert ops.construct_optimizer(None) is m.optimizer                          # nothing configured: nothing changes
+
+
+def test_set_weights_casts_to_the_models_dtypes_and_rejects_a_different_architecture():
+    import pytest
+    ops = KerasModelOps(model=FakeKerasModel())
+    names, trainables, values = ops.get_model_weights()
+    as64 = [v.astype(np.float64) if v.dtype.kind == "f" else v for v in values]   # e.g. an fp64 community model
+    as64[0] = as64[0] + 1.0
+    ops.set_model_weights(names, trainables, as64)
+    assert ops._model.w.dtype == np.float32 and np.allclose(ops._model.w, values[0] + 1.0)
+    with pytest.raises(ValueError):
+        ops.set_model_weights(names[:2], trainables[:2], values[:2])
+
+
+def test_empty_splits_and_missing_training_data():
+    import pytest
+    ops = KerasModelOps(model=FakeKerasModel())
+    assert ops.evaluate_model(None, 32) == {}
+    task = metis_pb2.LearningTask(global_iteration=1, num_local_updates=2)
+    hyper = metis_pb2.Hyperparameters(batch_size=16, optimizer=model_pb2.OptimizerConfig(
+        vanilla_sgd=model_pb2.VanillaSGD(learning_rate=0.1)))
+    with pytest.raises(RuntimeError):
+        ops.train_model(None, task, hyper)
+    done = ops.train_model(_dataset(), task, hyper)          # no validation / test split: metadata still complete
+    assert done.execution_metadata.completed_batches == 2
+    with pytest.raises(RuntimeError):
+        ops.infer_model(None)
