@@ -108,9 +108,10 @@ class DriverSessionBase(object):
         if want in (False, "false", "off", "no", "0") or self.neural_engine == "echo" or self.launcher == "ssh":
             return {}
         rule = env.global_model_config.aggregation_rule.aggregation_rule_name
-        n = len(env.learners)
-        ok = rule in ("FedAvg", "FedStride", "FedRec", "FedAsync") and self._he_scheme is None
-        ok = ok and (self.launcher == "local" or n == 1)   # one process is one rank: in-process only with one learner
+        members = [i for i, l in enumerate(env.learners) if getattr(l, "in_fabric", True)]
+        n = len(members)
+        ok = n > 0 and rule in ("FedAvg", "FedStride", "FedRec", "FedAsync") and self._he_scheme is None
+        ok = ok and (self.launcher == "local" or n == 1)   # one process is one rank: in-process only with one member
         forced = want in (True, "true", "on", "yes", "1")
         if not forced:
             ok = ok and torch.cuda.is_available() and n <= torch.cuda.device_count() and n <= 16
@@ -127,8 +128,8 @@ class DriverSessionBase(object):
         dtype = env.model_dtype or (self._model_dtype and {torch.bfloat16: "bf16", torch.float32: "fp32",
                                                            torch.float16: "fp16"}.get(self._model_dtype))
         specs = {}
-        for i in range(n):
-            t = "rank={},world={},init=tcp://127.0.0.1:{},id=fabric0,rule={},staging=2,executor=0".format(i, n, port, rule)
+        for rank, i in enumerate(members):   # learners outside the fabric (`DeviceFabric: false`) keep the host path
+            t = "rank={},world={},init=tcp://127.0.0.1:{},id=fabric0,rule={},staging=2,executor=0".format(rank, n, port, rule)
             specs[i] = t + (",dtype={}".format(dtype) if dtype else "")
         MetisLogger.info("Device fabric: %d learner(s), rule %s, models stay on the GPUs", n, rule)
         return specs

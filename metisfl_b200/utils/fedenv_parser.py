@@ -191,6 +191,9 @@ class Learner(RemoteHost):
         self.learner_id = learner_def_map.get("LearnerID")
         self.cuda_devices = learner_def_map.get("CudaDevices", [])
         self.logical_learners = learner_def_map.get("LogicalLearners", 1)
+        # extension: `DeviceFabric: false` keeps THIS learner on the host path (model bytes through the controller) even
+        # when the rest of the federation forms an on-box fabric - e.g. a learner on another machine
+        self.in_fabric = str(learner_def_map.get("DeviceFabric", True)).lower() not in ("false", "off", "no", "0")
         self.dataset_configs = DatasetConfigs(learner_def_map.get("DatasetConfigs"))
 
     def __str__(self):

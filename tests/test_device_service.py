@@ -105,6 +105,86 @@ def test_two_gloo_learner_processes_share_a_fabric(tmp_path, monkeypatch, rule, 
         assert "Traceback" not in log, log[-3000:]
 
 
+def test_aggregate_on_device_mixes_a_slot_with_a_staged_wire_model(tmp_path):
+    """The aggregation command itself, without the services around it: one source is the fabric learner's slot, the
+    other a wire model staged by the executor rank; the community model must be exactly w0 * slot + w1 * staged, and
+    `return_model_bytes` must hand it back as a wire model."""
+    from metisfl_b200.learner.device_backend import DeviceBackend, FabricSpec
+    from metisfl_b200.models.torch_model_ops import save_torch_model
+    from metisfl_b200.ops.pack import arena_to_model_pb
+    from metisfl_b200.proto import learner_pb2
+    torch.manual_seed(1)
+    model = FashionMnistMLP()
+    save_torch_model(model, str(tmp_path / "m"))
+    be = DeviceBackend(str(tmp_path / "m"), "cpu", FabricSpec(fabric_id="t", model_dtype="fp32"))
+    try:
+        eng = be.engine
+        eng._publish_all(0)                                    # the fabric learner's slot = the initial model
+        slot = eng.publish_slot(0)
+        local = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        other = FashionMnistMLP()
+        with torch.no_grad():
+            for p_ in other.parameters():
+                p_.add_(0.5)
+        be2 = DeviceBackend(str(tmp_path / "m"), "cpu", FabricSpec(fabric_id="u", model_dtype="fp32"))
+        be2.engine.arena.module.load_state_dict(other.state_dict())
+        staged_pb = arena_to_model_pb(be2.engine.arena)        # what a host-path learner would have sent
+        be2.close()
+        req = learner_pb2.AggregateOnDeviceRequest(rule="FedAvg", global_iteration=1, first_block=True, last_block=True,
+                                                   quantify=True, return_model_bytes=True, executor_rank=0)
+        req.sources.add(learner_id="in", device_rank=0, slot=slot, version=1, weight=0.25)
+        src = req.sources.add(learner_id="out", weight=0.75)
+        src.staged_model.CopyFrom(staged_pb)
+        resp = be.aggregate(req)
+        assert resp.ack.status and len(resp.quantifiers) == len(local) and len(resp.community_model.variables) == len(local)
+        got = eng.community_state_dict()
+        want = {k: 0.25 * local[k].float() + 0.75 * other.state_dict()[k].float() for k in local}
+        for k in local:
+            torch.testing.assert_close(got[k].float().cpu(), want[k], atol=1e-6, rtol=1e-6)
+        back = {v.name: np.frombuffer(v.plaintext_tensor.tensor_spec.value, dtype=np.float32)
+                for v in resp.community_model.variables}
+        for k in local:
+            np.testing.assert_allclose(back[k], want[k].numpy().ravel(), atol=1e-6)
+    finally:
+        be.close()
+
+
+@pytest.mark.timeout(300)
+def test_learner_outside_the_fabric_is_staged_into_it(tmp_path, monkeypatch):
+    """A mixed federation: learner 0 hosts the (world-1) fabric, learner 1 carries `DeviceFabric: false` and stays on
+    the host path.  Its model bytes reach the controller, travel inside the aggregation command into a staging slot
+    of the executor rank and are averaged with the fabric learner's slot by the same kernel; the community model's
+    bytes are pulled off the device for it every round."""
+    d = _env(**{"TerminationSignals.FederationRounds": 3, "TerminationSignals.ExecutionCutoffTimeMins": 3})
+    fe = d["FederationEnvironment"]
+    fe["DeviceFabric"] = True
+    fe["ModelDType"] = "fp32"
+    fe["Learners"][1]["DeviceFabric"] = False
+    snap = tmp_path / "snap_mixed"
+    monkeypatch.setenv("METISFL_SNAPSHOT_DIR", str(snap))
+    torch.manual_seed(0)
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(128, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / "w_mixed"), launcher="inprocess", banner=False)
+    assert sorted(s._fabric_specs) == [0] and "world=1" in s._fabric_specs[0]
+    stats = s.run(request_every_secs=0.3)
+    c = _counters(stats)
+    assert c["fabric_learners"] == 1 and c["aggregation_failures"] == 0
+    assert c["model_bytes_received"] > 3 * 400_000          # the outside learner's model, every round
+    rounds = [m for m in stats["federation_runtime_metadata"]["metadata"] if m.get("completed_by_learner_id")]
+    assert max(len(m["completed_by_learner_id"]) for m in rounds) == 2   # both learners contributed to a round
+    model, it = _final_model(str(snap))
+    assert it >= 2 and all(np.isfinite(v).all() for v in model.values())
+    ev = [e for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
+    assert max(len(e["evaluations"]) for e in ev) == 2                   # and both evaluate the community model
+    # the same federation entirely on the host path (same seeds): the same community model when they stopped together
+    s_host, stats_host, snap_host = _run(tmp_path, "mixed_host", False, monkeypatch, n_learners=2)
+    ref, it_ref = _final_model(snap_host)
+    assert set(ref) == set(model)
+    if it_ref == it:
+        for k in ref:
+            np.testing.assert_allclose(model[k], ref[k], atol=5e-5, rtol=1e-3)
+
+
 # ---- GPU tier: the same control path on the kernels --------------------------------------------------------------
 def _resnet_recipe(n, seed):
     def recipe():
