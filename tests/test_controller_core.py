@@ -243,3 +243,129 @@ def test_clean_leave_shrinks_the_barrier():
     f.core.wait_idle()
     assert f.core.global_iteration() == 2
     f.core.shutdown()
+
+
+# ---- device aggregation commands (no GPU: a fake fabric that answers with references) ---------------------------
+def _ref_model(rank, slot, version, numel=8):
+    """A control-only model as a fabric learner sends it: one fp32 variable, no bytes, `TensorSpec.device_slot` set."""
+    from metisfl_b200.proto import model_pb2
+    m = model_pb2.Model()
+    var = m.variables.add(name="w", trainable=True)
+    spec = var.plaintext_tensor.tensor_spec
+    spec.length = numel
+    spec.dimensions.append(numel)
+    spec.type.type = model_pb2.DType.FLOAT32
+    spec.type.byte_order = model_pb2.DType.LITTLE_ENDIAN_ORDER
+    spec.device_slot.device_rank = rank
+    spec.device_slot.slot = slot
+    spec.device_slot.version = version
+    return m.SerializeToString()
+
+
+class FabricFederation:
+    """Controller whose learners answer RunTask with device-slot references; the aggregation callback records the
+    command it is given and answers like an executor rank would (a reference to the community buffer)."""
+    COMMUNITY = 0xFFFFFFFF
+
+    def __init__(self, rule="FedAvg", protocol=1, n=2, examples=None, stride=0, fail_first=False):
+        p = _core.ControllerParams()
+        p.rule, p.protocol, p.stride_length = rule, protocol, stride
+        p.batch_size, p.epochs = 10, 1
+        if rule in ("FedRec", "FedAsync"):
+            p.lineage_length_eviction, p.lineage_length = True, 2
+        self.lock = threading.Lock()
+        self.commands, self.tokens, self.rank_of, self.task_no = [], {}, {}, {}
+        self.fail_first = fail_first
+        self.core = _core.Controller(p, self._run, self._eval, self._aggregate)
+        self.examples = examples or [100] * n
+
+    def _run(self, items, fm, ref=None):
+        for (lid, host, port, cert, iteration, updates, pct) in items:
+            threading.Thread(target=self._complete, args=(lid, iteration, updates), daemon=True).start()
+
+    def _complete(self, lid, iteration, updates):
+        with self.lock:
+            self.task_no[lid] = self.task_no.get(lid, 0) + 1
+            n = self.task_no[lid]
+        rank = int(lid.rsplit(":", 1)[1]) - 9100      # the first task can arrive before join() has returned
+        model = _ref_model(rank, slot=n % 2, version=n)
+        t0 = time.time()
+        while lid not in self.tokens and time.time() - t0 < 5:
+            time.sleep(0.005)
+        try:
+            self.core.learner_completed_task(lid, self.tokens[lid], model, iteration, 1.0, updates, 10, 10.0, 1.0, b"")
+        except Exception:
+            pass  # shutdown races
+
+    def _eval(self, learners, model, batch_size, idx, iteration, ref=None):
+        for l in learners:
+            self.core.evaluation_completed(l[0], idx, b"")
+
+    def _aggregate(self, req):
+        with self.lock:
+            self.commands.append(req)
+            first = len(self.commands) == 1
+        if self.fail_first and first:
+            return {"error": "injected failure"}
+        return {"model_ref": _ref_model(0, self.COMMUNITY, req["global_iteration"] + 1), "device_ms": 0.125,
+                "quantifiers": [(7, 1, 32)], "model_bytes": None, "error": None}
+
+    def join(self, i):
+        lid, tok = self.core.add_learner("127.0.0.1", 9100 + i, b"", b"", self.examples[i], 0, 0)
+        self.tokens[lid], self.rank_of[lid] = tok, i
+        return lid
+
+    def wait_commands(self, n, timeout=20):
+        t0 = time.time()
+        while time.time() - t0 < timeout:
+            with self.lock:
+                if len(self.commands) >= n:
+                    return
+            time.sleep(0.01)
+        raise AssertionError(f"only {len(self.commands)} aggregation commands")
+
+
+def test_synchronous_round_is_commanded_with_slots_and_scaling_factors():
+    f = FabricFederation(n=2, examples=[100, 300])
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    ids = [f.join(i) for i in range(2)]
+    f.wait_commands(2)
+    f.core.wait_idle()
+    full = [c for c in f.commands if len(c["sources"]) == 2]
+    assert full, [len(c["sources"]) for c in f.commands]   # a round with both learners (the first may close with one)
+    c = full[0]
+    assert c["rule"] == "FedAvg" and c["first_block"] and c["last_block"] and c["quantify"]
+    by_id = {s["learner_id"]: s for s in c["sources"]}
+    assert set(by_id) == set(ids)
+    assert by_id[ids[0]]["device_rank"] == 0 and by_id[ids[1]]["device_rank"] == 1
+    assert all(s["staged_model"] is None for s in c["sources"])           # references only: nothing to stage
+    assert abs(by_id[ids[0]]["weight"] - 0.25) < 1e-9 and abs(by_id[ids[1]]["weight"] - 0.75) < 1e-9
+    md = [m for m in f.core.get_runtime_metadata_lineage(0) if m["model_aggregation_block_duration_ms"]]
+    assert md and md[0]["device_timed"] and md[0]["model_aggregation_block_duration_ms"][0] == 0.125
+    assert md[0]["model_tensor_quantifiers"][0] == (7, 1, 32)            # the fabric's counts, not a host pass
+    assert f.core.aggregation_failures() == 0
+    f.core.shutdown()
+
+
+def test_fedrec_command_carries_the_previous_contribution():
+    f = FabricFederation(rule="FedRec", protocol=2, n=1, examples=[100])
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    f.join(0)
+    f.wait_commands(3)
+    f.core.wait_idle()
+    first, second = f.commands[0], f.commands[1]
+    assert first["rule"] == "FedRec" and len(first["sources"]) == 1 and not first["sources"][0]["has_previous"]
+    s = second["sources"][0]
+    assert s["has_previous"] and s["previous_slot"] == first["sources"][0]["slot"] and s["slot"] != s["previous_slot"]
+    assert abs(s["previous_weight"] - first["sources"][0]["weight"]) < 1e-12 and second["z"] > 0
+    f.core.shutdown()
+
+
+def test_failed_device_aggregation_closes_the_round_and_is_counted():
+    f = FabricFederation(n=1, examples=[100], fail_first=True)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    f.join(0)
+    f.wait_commands(3)          # the federation keeps going after the failed command
+    f.core.wait_idle()
+    assert f.core.aggregation_failures() == 1
+    f.core.shutdown()
