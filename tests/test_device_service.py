@@ -42,6 +42,10 @@ def _run(tmp_path, tag, fabric, monkeypatch, n_learners=1, launcher="inprocess",
     if protocol:
         fe["CommunicationProtocol"]["Name"] = protocol
         fe["ModelStoreConfig"]["LineageLength"] = 2
+    if protocol == "SEMI_SYNCHRONOUS":   # task sizes are recomputed from the learners' (device-timed) ms per batch
+        fe["CommunicationProtocol"]["Specifications"] = {"SemiSynchronousLambda": 1,
+                                                         "SemiSynchronousRecomputeSteps": True}
+        fe["GlobalModelConfig"]["AggregationRule"].setdefault("RuleSpecifications", {})["StrideLength"] = 1
     snap = tmp_path / f"snap_{tag}"
     monkeypatch.setenv("METISFL_SNAPSHOT_DIR", str(snap))
     torch.manual_seed(0)
@@ -86,7 +90,7 @@ def test_single_learner_device_path_matches_host_path(tmp_path, monkeypatch):
 
 @pytest.mark.timeout(240)
 @pytest.mark.parametrize("rule,protocol", [("FedAvg", None), ("FedStride", None), ("FedAsync", "Asynchronous"),
-                                           ("FedRec", "Asynchronous")])
+                                           ("FedRec", "Asynchronous"), ("FedStride", "SEMI_SYNCHRONOUS")])
 def test_two_gloo_learner_processes_share_a_fabric(tmp_path, monkeypatch, rule, protocol):
     """Controller + 2 learner processes (`Launcher: local`), world-2 fabric over gloo: the control path of every rule."""
     s, stats, snap = _run(tmp_path, "w2", True, monkeypatch, n_learners=2, launcher="local", rule=rule,
