@@ -369,3 +369,25 @@ def test_failed_device_aggregation_closes_the_round_and_is_counted():
     f.core.wait_idle()
     assert f.core.aggregation_failures() == 1
     f.core.shutdown()
+
+
+def test_fedstride_round_is_commanded_block_by_block():
+    """Stride 1 with two learners: one command per block; the first one starts the running result, the last one
+    finishes it (and is the only one that quantifies); the metadata lists both blocks with their device times."""
+    f = FabricFederation(rule="FedStride", n=2, examples=[100, 100], stride=1)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    ids = [f.join(i) for i in range(2)]
+    f.wait_commands(6)
+    f.core.wait_idle()
+    md = [m for m in f.core.get_runtime_metadata_lineage(0) if len(m["model_aggregation_block_size"]) == 2]
+    assert md, [m["model_aggregation_block_size"] for m in f.core.get_runtime_metadata_lineage(0)]
+    assert md[0]["model_aggregation_block_size"] == [1.0, 1.0] and md[0]["model_aggregation_block_duration_ms"] == [0.125, 0.125]
+    # find two consecutive commands of one round
+    pairs = [(a, b) for a, b in zip(f.commands, f.commands[1:])
+             if a["global_iteration"] == b["global_iteration"] and a["first_block"] and not a["last_block"]]
+    assert pairs
+    a, b = pairs[0]
+    assert not b["first_block"] and b["last_block"] and len(a["sources"]) == len(b["sources"]) == 1
+    assert {a["sources"][0]["learner_id"], b["sources"][0]["learner_id"]} == set(ids)
+    assert abs(a["sources"][0]["weight"] - 0.5) < 1e-9 and b["quantify"]
+    f.core.shutdown()
