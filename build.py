@@ -80,7 +80,9 @@ def build_core(force=False, verbose=False):
     ext = sysconfig.get_config_var("EXT_SUFFIX")
     out = os.path.join(ROOT, "metisfl_b200", "_core" + ext)
     if force or _stale(out, srcs + _headers()):
-        cmd = ["g++", "-O3", "-std=c++17", "-shared", "-fPIC", "-fopenmp", "-fvisibility=hidden",
+        # -ffp-contract=off: the aggregation rules round every w * x term before adding it (reference semantics, golden
+        # vectors); a fused multiply-add in the AVX-512 clones of the inner loops would skip that rounding
+        cmd = ["g++", "-O3", "-std=c++17", "-shared", "-fPIC", "-fopenmp", "-ffp-contract=off", "-fvisibility=hidden",
                "-I", pybind11.get_include(), "-I", sysconfig.get_paths()["include"],
                "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "csrc")] + srcs + ["-o", out]
         _run(cmd, verbose)
@@ -97,7 +99,7 @@ def build_tools(force=False, verbose=False):
     for s in srcs:
         out = os.path.join(ROOT, "metisfl_b200", "bin", os.path.basename(s)[:-3].replace("_main", ""))
         if force or _stale(out, [s] + core + _headers()):
-            _run(["g++", "-O3", "-std=c++17", "-fopenmp", "-pthread", "-I", os.path.join(ROOT, "include"),
+            _run(["g++", "-O3", "-std=c++17", "-fopenmp", "-ffp-contract=off", "-pthread", "-I", os.path.join(ROOT, "include"),
                   "-I", os.path.join(ROOT, "csrc"), s] + core + ["-o", out], verbose)
         outs.append(out)
     return outs

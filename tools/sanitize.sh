@@ -21,7 +21,7 @@ case "${1:-memcheck}" in
   tsan)
     mkdir -p build/tsan
     CORE=$(ls csrc/core/*.cc csrc/ckks/*.cc)
-    g++ -O1 -g -std=c++17 -shared -fPIC -Wno-unknown-pragmas -fsanitize=thread \
+    g++ -O1 -g -std=c++17 -shared -fPIC -ffp-contract=off -Wno-unknown-pragmas -fsanitize=thread \
       -I "$(python -c 'import pybind11;print(pybind11.get_include())')" \
       -I "$(python -c 'import sysconfig;print(sysconfig.get_paths()["include"])')" -I include -I csrc $CORE \
       -o "build/tsan/_core$(python -c 'import sysconfig;print(sysconfig.get_config_var("EXT_SUFFIX"))')"
