@@ -194,3 +194,49 @@ def test_echo_learners_drive_the_controller_without_training(tmp_path):
     assert len(md) >= 3 and all(len(m["completed_by_learner_id"]) == 2 for m in md[:3])
     tasks = stats["learners_models_results"]["learner_task"]
     assert len(tasks) == 2
+
+
+@pytest.mark.timeout(300)
+def test_ssh_launcher_over_a_local_exec_transport(tmp_path, monkeypatch):
+    """`Launcher: ssh` (the reference's only launcher, driver_session.py:225-262) end to end: the driver builds the
+    remote commands, ships the model archive and the dataset recipes, and the controller / learners it starts that way
+    run a federation.  There is no sshd in this image, so `fabric.Connection` is replaced by a transport that runs the
+    very same command lines with `bash -c` and copies the very same files - everything above the socket is exercised."""
+    import shutil
+    import fabric
+
+    calls = {"run": [], "put": [], "hosts": set()}
+
+    class LocalExecConnection:
+        def __init__(self, host=None, port=None, user=None, connect_kwargs=None, **kw):
+            calls["hosts"].add((host, user))
+            self.env = dict(os.environ)
+            self.env["PYTHONPATH"] = ROOT + os.pathsep + self.env.get("PYTHONPATH", "")
+
+        def run(self, cmd, **kw):
+            calls["run"].append(cmd)
+            return subprocess.run(["bash", "-c", cmd], env=self.env, stdout=subprocess.DEVNULL,
+                                  stderr=subprocess.DEVNULL, check=False)
+
+        def put(self, local, remote):
+            calls["put"].append((os.path.basename(local), remote))
+            shutil.copy(local, remote)
+
+        def close(self):
+            pass
+
+    monkeypatch.setattr(fabric, "Connection", LocalExecConnection)
+    d = _env(**{"TerminationSignals.FederationRounds": 2, "TerminationSignals.ExecutionCutoffTimeMins": 3})
+    d["FederationEnvironment"]["Learners"] = d["FederationEnvironment"]["Learners"][:1]
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(96, 1), None, _recipe(32, 3),
+                      working_dir=str(tmp_path / "w"), launcher="ssh", banner=False)
+    stats = s.run(request_every_secs=0.5)
+    assert len(stats["federation_runtime_metadata"]["metadata"]) >= 2
+    assert stats["community_model_results"]["community_evaluation"]
+    # one remote command for the controller, mkdir + one command for the learner; the learner got its files
+    assert any("metisfl" in c and "controller" in c for c in calls["run"])
+    learner_cmds = [c for c in calls["run"] if "learner" in c and "tar -xzf" in c]
+    assert len(learner_cmds) == 1 and "mkdir -p /tmp/metis/workdir_learner_" in learner_cmds[0]
+    shipped = [name for name, _ in calls["put"]]
+    assert any(name.endswith(".tar.gz") for name in shipped) and len(shipped) >= 3   # model archive + 2 recipes
+    assert calls["hosts"] == {("localhost", "root")}
