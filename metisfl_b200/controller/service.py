@@ -136,6 +136,10 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         self._server_holder = GRPCServerMaxMsgLength(max_workers=max_workers, server_entity=self.params_pb.server_entity)
         self._server = self._server_holder.server
         controller_pb2_grpc.add_ControllerServiceServicer_to_server(self, self._server)
+        # the reference's server also answers the standard health-checking and reflection services
+        # (controller_servicer.cc:80-84): grpc_health_probe / grpcurl work against this one too
+        from metisfl_b200.proto.grpc_std_services import add_standard_services
+        self._health = add_standard_services(self._server, ["metisfl.ControllerService"])
         self._server.start()
         if self._snapshot_dir:
             self._snapshot_thread = threading.Thread(target=self._snapshot_loop, daemon=True)
@@ -224,6 +228,8 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
                 MetisLogger.warning("snapshot failed: %r", e)
 
     def stop(self, grace=1.0):
+        if getattr(self, "_health", None) is not None:
+            self._health.enter_graceful_shutdown()
         self._shutdown_event.set()
         if self._snapshot_dir:
             try:

@@ -29,17 +29,21 @@ class LearnerServicer(learner_pb2_grpc.LearnerServiceServicer):
         self.__not_serving_event = threading.Event()
         self.__shutdown_event = threading.Event()
         self.__grpc_server = None
+        self.__health = None
 
     def init_servicer(self):
         self.__grpc_server = GRPCServerMaxMsgLength(max_workers=self.servicer_workers,
                                                     server_entity=self.learner.learner_server_entity)
         learner_pb2_grpc.add_LearnerServiceServicer_to_server(self, self.__grpc_server.server)
+        from metisfl_b200.proto.grpc_std_services import add_standard_services
+        self.__health = add_standard_services(self.__grpc_server.server, ["metisfl.LearnerService"])
         self.__grpc_server.server.start()
         MetisLogger.info("Learner servicer listening on %s", self.learner.host_port_identifier())
         self.learner.join_federation()
 
     def wait_servicer(self):
         self.__shutdown_event.wait()
+        self.__health.enter_graceful_shutdown()
         self.__grpc_server.server.stop(None)
 
     def _refuse(self, context):
