@@ -70,5 +70,12 @@ def test_health_check_and_reflection_answer_like_the_standard_services():
         assert answers[2].WhichOneof("message_response") == "error_response"
         assert answers[2].error_response.error_code == grpc.StatusCode.NOT_FOUND.value[0]
         ch.close()
+        # the operations helper built on the two services
+        from metisfl_b200.utils import grpc_probe
+        status, names = grpc_probe.probe(f"127.0.0.1:{port}", list_services=True)
+        assert status == "SERVING" and "metisfl.ControllerService" in names
+        assert grpc_probe.main([f"127.0.0.1:{port}", "--service", "metisfl.ControllerService"]) == 0
     finally:
         ctrl.stop()
+    from metisfl_b200.utils import grpc_probe
+    assert grpc_probe.main([f"127.0.0.1:{port}", "--timeout", "1"]) == 1      # the server is gone
