@@ -141,6 +141,9 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
         from metisfl_b200.proto.grpc_std_services import add_standard_services
         self._health = add_standard_services(self._server, ["metisfl.ControllerService"])
         self._server.start()
+        from metisfl_b200.controller.metrics import ControllerMetrics
+        self._metrics = ControllerMetrics(self)      # METISFL_PROMETHEUS_PORT: optional scrape endpoint
+        self._metrics.start()
         if self._snapshot_dir:
             self._snapshot_thread = threading.Thread(target=self._snapshot_loop, daemon=True)
             self._snapshot_thread.start()
@@ -230,6 +233,8 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
     def stop(self, grace=1.0):
         if getattr(self, "_health", None) is not None:
             self._health.enter_graceful_shutdown()
+        if getattr(self, "_metrics", None) is not None:
+            self._metrics.stop()
         self._shutdown_event.set()
         if self._snapshot_dir:
             try:

@@ -135,3 +135,39 @@ def test_heartbeat_evicts_a_learner_that_stopped_answering(tmp_path, monkeypatch
         assert service.core.global_iteration() >= it0 + 2   # rounds keep completing with the survivor
     finally:
         sess.shutdown_federation()
+
+
+def test_prometheus_endpoint_reports_the_federation(tmp_path, monkeypatch):
+    """METISFL_PROMETHEUS_PORT: the controller's counters (rounds, learners, received model bytes, aggregation time)
+    are scraped over HTTP while a small federation runs, and stay consistent with the runtime metadata."""
+    import socket
+    import urllib.request
+    from test_e2e_cpu import _env, _recipe
+    from metisfl_b200.driver.driver_session import DriverSession
+    from metisfl_b200.models.zoo import FashionMnistMLP
+    from metisfl_b200.utils.fedenv_parser import FederationEnvironment
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    monkeypatch.setenv("METISFL_PROMETHEUS_PORT", str(port))
+    d = _env(**{"TerminationSignals.FederationRounds": 2, "TerminationSignals.ExecutionCutoffTimeMins": 2})
+    d["FederationEnvironment"]["Learners"] = d["FederationEnvironment"]["Learners"][:1]
+    session = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(96, 1), None, _recipe(32, 3),
+                            working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    session.initialize_federation()
+    try:
+        session.monitor_federation(request_every_secs=0.3)
+        text = urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics", timeout=5).read().decode()
+    finally:
+        session.shutdown_federation()
+    values = {}
+    for line in text.splitlines():
+        if line.startswith("metisfl_"):
+            k, v = line.rsplit(" ", 1)
+            values[k] = float(v)
+    assert values["metisfl_global_iteration"] >= 2 and values["metisfl_learners"] == 1
+    assert values["metisfl_model_bytes_received_total"] > 400_000          # host path: models travel as bytes
+    assert values["metisfl_aggregation_failures_total"] == 0
+    assert values["metisfl_last_aggregation_duration_ms"] > 0 and values["metisfl_last_round_duration_seconds"] > 0
+    assert values["metisfl_fabric_learners"] == 0 and values["metisfl_last_aggregation_device_timed"] == 0
