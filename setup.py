@@ -24,6 +24,6 @@ setup(
     package_data={"metisfl_b200": ["lib/*.so", "_core*.so", "bin/*", "resources/**/*"]},
     python_requires=">=3.10",
     install_requires=["torch>=2.4", "numpy", "protobuf>=4", "grpcio", "PyYAML", "cloudpickle", "cryptography"],
-    extras_require={"ssh": ["fabric"]},
+    extras_require={"ssh": ["fabric"], "metrics": ["prometheus_client"]},
     cmdclass={"build_py": BuildNative},
 )
