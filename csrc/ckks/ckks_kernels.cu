@@ -745,7 +745,9 @@ extern "C" int mfl_ckks_fused_weighted_sum_mc(const mfl_ckks_ctx* ctx, const uin
   for (int t = 0; t < world; ++t) { fa.out[t] = outs[t]; fa.pads[t] = signal_pads[t]; }
   fa.mc_out = mc_out;
   fa.rank = rank; fa.world = world; fa.words = words;
-  static const int bulk_mode = [] { const char* e = getenv("MFL_CKKS_BULK"); return e ? atoi(e) : 1; }();
+  // MFL_CKKS_BULK=1 selects the cp.async.bulk-fed variant; both variants are bound by the inbound link and measured
+  // the same (5.85-6.0 ms for ResNet-18 on 8 GPUs), so the thread-load kernel stays the default
+  static const int bulk_mode = [] { const char* e = getenv("MFL_CKKS_BULK"); return e ? atoi(e) : 0; }();
   if (bulk_mode && world > 1 && n_src <= kWsMaxSrc && words % kWsChunkWords == 0 && ctx->log_n >= 9) {
     const size_t stage_bytes = (size_t)n_src * kWsChunkWords * 8;
     const int stages = (int)std::min<size_t>(16, (kWsSmemBudget - 512) / stage_bytes);
