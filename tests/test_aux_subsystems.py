@@ -3,6 +3,8 @@ snapshot of the controller."""
 import json
 import os
 
+import pytest
+
 import numpy as np
 import torch
 
@@ -137,6 +139,7 @@ def test_heartbeat_evicts_a_learner_that_stopped_answering(tmp_path, monkeypatch
         sess.shutdown_federation()
 
 
+@pytest.mark.timeout(180)
 def test_prometheus_endpoint_reports_the_federation(tmp_path, monkeypatch):
     """METISFL_PROMETHEUS_PORT: the controller's counters (rounds, learners, received model bytes, aggregation time)
     are scraped over HTTP while a small federation runs, and stay consistent with the runtime metadata."""
