@@ -53,7 +53,7 @@ void WeightedSumT(size_t n, const std::vector<const char*>& srcs, const std::vec
   for (size_t base = 0; base < n; base += kSumChunk) {
     const size_t m = std::min(kSumChunk, n - base);
     if (acc) std::memcpy(a, out + base * sizeof(T), m * sizeof(T));
-    else std::memset(a, 0, m * sizeof(T));
+    else std::fill(a, a + m, T(0));   // (T may be a small class type: bf16 / fp16 wrappers)
     for (size_t l = 0; l < L; ++l) {
       std::memcpy(x, srcs[l] + base * sizeof(T), m * sizeof(T));
       // a negative weight subtracts the positive term (what the reference's SUBTRACTION merge does), which stays
