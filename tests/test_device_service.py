@@ -109,6 +109,40 @@ def test_two_gloo_learner_processes_share_a_fabric(tmp_path, monkeypatch, rule, 
         assert "Traceback" not in log, log[-3000:]
 
 
+@pytest.mark.timeout(300)
+def test_world_two_fabric_plus_one_learner_outside(tmp_path, monkeypatch):
+    """Three learner processes: two form a world-2 fabric (gloo), the third carries `DeviceFabric: false`.  Every
+    rank takes part in the commanded aggregation, only the executor rank unpacks the outsider's wire model into its
+    staging slot, and the outsider keeps receiving the community model as bytes."""
+    import copy
+    from test_e2e_cpu import _free_ports
+    d = _env(**{"TerminationSignals.FederationRounds": 3, "TerminationSignals.ExecutionCutoffTimeMins": 3})
+    fe = d["FederationEnvironment"]
+    third = copy.deepcopy(fe["Learners"][1])
+    third["LearnerID"] = "localhost-3"
+    third["GRPCServicer"]["Port"] = _free_ports(1)[0]
+    third["DeviceFabric"] = False
+    fe["Learners"].append(third)
+    fe["DeviceFabric"] = True
+    fe["ModelDType"] = "fp32"
+    snap = tmp_path / "snap_w2p1"
+    monkeypatch.setenv("METISFL_SNAPSHOT_DIR", str(snap))
+    torch.manual_seed(0)
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(128, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / "w_w2p1"), launcher="local", banner=False)
+    assert sorted(s._fabric_specs) == [0, 1] and all("world=2" in v for v in s._fabric_specs.values())
+    stats = s.run(request_every_secs=0.3)
+    c = _counters(stats)
+    assert c["fabric_learners"] == 2 and c["aggregation_failures"] == 0 and c["model_bytes_received"] > 400_000
+    rounds = [m for m in stats["federation_runtime_metadata"]["metadata"] if m.get("completed_by_learner_id")]
+    assert max(len(m["completed_by_learner_id"]) for m in rounds) == 3
+    model, it = _final_model(str(snap))
+    assert it >= 2 and all(np.isfinite(v).all() for v in model.values())
+    for name in ("learner0", "learner1", "learner2"):
+        log = open(os.path.join(str(tmp_path / "w_w2p1"), name + ".log"), errors="replace").read()
+        assert "Traceback" not in log, log[-3000:]
+
+
 def test_aggregate_on_device_mixes_a_slot_with_a_staged_wire_model(tmp_path):
     """The aggregation command itself, without the services around it: one source is the fabric learner's slot, the
     other a wire model staged by the executor rank; the community model must be exactly w0 * slot + w1 * staged, and
