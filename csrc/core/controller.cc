@@ -514,6 +514,12 @@ bool Controller::AggregateBlockOnDevice(const std::vector<std::pair<std::string,
     }
     dr.sources.push_back(std::move(src));
   }
+  if (!any_device && !dr.sources.empty() && device_contributors_ > 0 &&
+      (params_.rule == "FedRec" || params_.rule == "FedAsync"))
+    // the rolling state of this federation lives on the device fabric: folding a byte-carried model on the host
+    // would start a second, diverging community model - refuse loudly instead (counted as an aggregation failure)
+    throw std::runtime_error("asynchronous rule on a device fabric: a contribution without a device slot cannot be "
+                             "folded (keep every learner of an asynchronous federation inside the fabric)");
   if (!any_device || dr.sources.empty()) return false;
   dr.z = z;
   DeviceAggregateResult out;

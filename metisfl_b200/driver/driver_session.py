@@ -111,6 +111,9 @@ class DriverSessionBase(object):
         members = [i for i, l in enumerate(env.learners) if getattr(l, "in_fabric", True)]
         n = len(members)
         ok = n > 0 and rule in ("FedAvg", "FedStride", "FedRec", "FedAsync") and self._he_scheme is None
+        # the asynchronous rules keep their rolling state on the executor GPU: a learner outside the fabric would be
+        # folded on the host into a second, diverging community model - such a federation stays on the host path
+        ok = ok and not (rule in ("FedRec", "FedAsync") and n < len(env.learners))
         ok = ok and (self.launcher == "local" or n == 1)   # one process is one rank: in-process only with one member
         forced = want in (True, "true", "on", "yes", "1")
         if not forced:

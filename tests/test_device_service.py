@@ -116,7 +116,9 @@ def test_world_two_fabric_plus_one_learner_outside(tmp_path, monkeypatch):
     staging slot, and the outsider keeps receiving the community model as bytes."""
     import copy
     from test_e2e_cpu import _free_ports
-    d = _env(**{"TerminationSignals.FederationRounds": 3, "TerminationSignals.ExecutionCutoffTimeMins": 3})
+    # many rounds: the outside learner starts first (no rendezvous to wait for) and a synchronous federation runs with
+    # whoever has joined, so a three-round budget can be used up before the two fabric processes are even listening
+    d = _env(**{"TerminationSignals.FederationRounds": 120, "TerminationSignals.ExecutionCutoffTimeMins": 3})
     fe = d["FederationEnvironment"]
     third = copy.deepcopy(fe["Learners"][1])
     third["LearnerID"] = "localhost-3"
@@ -363,3 +365,22 @@ def test_multi_gpu_fabric_through_driver_session(tmp_path, monkeypatch, world, r
     assert c["model_bytes_received"] == 0 and c["fabric_learners"] == world and c["aggregation_failures"] == 0, logs
     model, it = _bf16_model(snap)
     assert it >= 2 and all(torch.isfinite(v).all() for v in model.values()), logs
+
+
+def test_asynchronous_rules_do_not_mix_fabric_and_outside_learners(tmp_path):
+    """FedRec / FedAsync keep their rolling state on the executor GPU, so a federation with a learner outside the
+    fabric is planned on the host path as a whole (and refused when the fabric was demanded)."""
+    for want, expect_error in (("auto", False), (True, True)):
+        d = _env(**{"GlobalModelConfig.AggregationRule.Name": "FedAsync"})
+        fe = d["FederationEnvironment"]
+        fe["CommunicationProtocol"]["Name"] = "Asynchronous"
+        fe["ModelStoreConfig"]["LineageLength"] = 2
+        fe["DeviceFabric"] = want
+        fe["Learners"][1]["DeviceFabric"] = False
+        make = lambda: DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(64, 1), None, _recipe(32, 3),
+                                     working_dir=str(tmp_path / f"w_{want}"), launcher="inprocess", banner=False)
+        if expect_error:
+            with pytest.raises(RuntimeError):
+                make()
+        else:
+            assert make()._fabric_specs == {}
