@@ -199,7 +199,10 @@ PYBIND11_MODULE(_core, m) {
     py::list out;
     for (auto& v : vars) {
       py::dict d;
-      d["name"] = std::string(v.name); d["trainable"] = v.trainable; d["ciphertext"] = v.ciphertext;
+      // names come off the wire: bytes that are not UTF-8 (a corrupted or hostile message) must not turn into an
+      // exception half-way through the list
+      d["name"] = py::reinterpret_steal<py::object>(PyUnicode_DecodeUTF8(v.name.data(), (Py_ssize_t)v.name.size(), "replace"));
+      d["trainable"] = v.trainable; d["ciphertext"] = v.ciphertext;
       d["length"] = v.t.length; d["dimensions"] = v.t.dims; d["dtype"] = v.t.dtype;
       d["byte_order"] = v.t.byte_order; d["fortran_order"] = v.t.fortran;
       d["value"] = py::bytes(v.t.value.data(), v.t.value.size());

@@ -2,6 +2,8 @@
 # Sanitizer targets (the reference has none).
 #   tools/sanitize.sh memcheck|racecheck|synccheck|initcheck [core|train] - compute-sanitizer over the kernel tests
 #                                                                 (ONE tool per gpurun call, see B200_PROFILING.md)
+#   tools/sanitize.sh asan                                      - AddressSanitizer + UBSan build of the host core under the
+#                                                                 wire-codec property tests and the aggregation rules (CPU only)
 #   tools/sanitize.sh tsan                                      - ThreadSanitizer build of the host controller core (OpenMP off:
 #                                                                 libgomp is not instrumented and only yields false positives)
 #                                                                 + the protocol tests (CPU only)
@@ -33,5 +35,22 @@ case "${1:-memcheck}" in
     LD_PRELOAD="$(g++ -print-file-name=libtsan.so)" TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" \
       python -m pytest tests/test_controller_core.py tests/test_policies_and_stores.py -x -q -p no:cacheprovider
     ;;
-  *) echo "usage: $0 memcheck|racecheck|synccheck|initcheck|tsan"; exit 2;;
+  asan)
+    # AddressSanitizer + UBSan build of the host core under the wire-codec property tests (untrusted learner bytes)
+    # and the aggregation rules (payload-length checks)
+    mkdir -p build/asan
+    CORE=$(ls csrc/core/*.cc csrc/ckks/*.cc)
+    EXT="$(python -c 'import sysconfig;print(sysconfig.get_config_var("EXT_SUFFIX"))')"
+    g++ -O1 -g -std=c++17 -shared -fPIC -fopenmp -ffp-contract=off -fsanitize=address,undefined -fno-omit-frame-pointer \
+      -I "$(python -c 'import pybind11;print(pybind11.get_include())')" \
+      -I "$(python -c 'import sysconfig;print(sysconfig.get_paths()["include"])')" -I include -I csrc $CORE \
+      -o "build/asan/_core$EXT"
+    cp "metisfl_b200/_core$EXT" "build/asan/_core_regular$EXT"
+    trap 'cp "build/asan/_core_regular$EXT" "metisfl_b200/_core$EXT"' EXIT
+    cp "build/asan/_core$EXT" "metisfl_b200/_core$EXT"
+    LD_PRELOAD="$(g++ -print-file-name=libasan.so):$(g++ -print-file-name=libubsan.so)" \
+      ASAN_OPTIONS="detect_leaks=0:halt_on_error=1" UBSAN_OPTIONS="print_stacktrace=1" \
+      python -m pytest tests/test_wire_fuzz.py tests/test_proto_codec.py tests/test_aggregation_rules.py -x -q -p no:cacheprovider
+    ;;
+  *) echo "usage: $0 memcheck|racecheck|synccheck|initcheck|tsan|asan"; exit 2;;
 esac
