@@ -186,6 +186,13 @@ bool ParseHeader(std::string_view blob, CtHeader& h) {
   if (blob.size() < sizeof(CtHeader)) return false;
   std::memcpy(&h, blob.data(), sizeof(h));
   if (std::memcmp(h.magic, "MFCK", 4) != 0 || h.version != 1 || h.n_limbs == 0 || h.n_limbs > kMaxLimbs) return false;
+  // the blob comes off the wire (a learner's ciphertext): every field later code divides by, shifts by or indexes
+  // with is bounded here - ring dimension, odd moduli below 2^62, a finite positive scale, slots within the ring
+  if (h.log_n < 1 || h.log_n > 17) return false;
+  for (uint32_t i = 0; i < h.n_limbs; ++i)
+    if (h.q[i] < 3 || (h.q[i] & 1) == 0 || h.q[i] >= (1ull << 62)) return false;
+  if (!(h.scale > 0.0) || !std::isfinite(h.scale)) return false;
+  if (h.slots == 0 || h.slots > (1u << h.log_n) / 2) return false;
   return blob.size() == sizeof(CtHeader) + (size_t)h.n_ct * ct_words(h) * 8;
 }
 

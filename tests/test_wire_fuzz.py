@@ -97,3 +97,65 @@ def test_mutated_models_parse_or_raise(vars_, data):
     fm = _core.build_federated_model(3, 7, bytes(blob))
     c, it, inner = _core.parse_federated_model(fm)
     assert (c, it, inner) == (3, 7, bytes(blob))
+
+
+# ---- ciphertext blobs (the PWA rule hands learner-supplied ciphertexts to the host scheme) ------------------------
+import struct
+
+import pytest
+
+
+@pytest.fixture(scope="module")
+def ciphertext(tmp_path_factory):
+    from metisfl_b200.encryption import fhe
+    s = fhe.CKKS(4096, 52, backend="host")
+    s.gen_crypto_context_and_keys(str(tmp_path_factory.mktemp("crypto")), seed=5)
+    return s.encrypt(np.linspace(-1, 1, 100))
+
+
+def _patched(blob, offset, fmt, value):
+    b = bytearray(blob)
+    struct.pack_into(fmt, b, offset, value)
+    return bytes(b)
+
+
+def test_hostile_ciphertext_headers_are_rejected(ciphertext):
+    """CtHeader (64 bytes): magic, version u16 @4, log_n u8 @6, n_limbs u8 @7, n_ct u32 @8, slots u32 @12,
+    n_values u64 @16, scale f64 @24, q[4] u64 @32.  Every field the scheme later divides by, shifts by or sizes a
+    buffer with must be refused when it is out of range - with an exception, not a crash."""
+    ok = _core.ckks_header(ciphertext)
+    assert ok["n_ct"] == 1 and ok["log_n"] == 14
+    _core.ckks_weighted_average([ciphertext, ciphertext], [0.5, 0.5])           # the well-formed case works
+    hostile = [
+        _patched(ciphertext, 32, "<Q", 0),                  # modulus 0: division by zero in the weight encoding
+        _patched(ciphertext, 32, "<Q", 4),                  # even modulus
+        _patched(ciphertext, 40, "<Q", 1 << 63),            # modulus beyond the 62-bit arithmetic
+        _patched(ciphertext, 6, "<B", 63),                  # ring dimension 2^63
+        _patched(ciphertext, 6, "<B", 0),
+        _patched(ciphertext, 7, "<B", 0),                   # no limbs
+        _patched(ciphertext, 7, "<B", 9),                   # more limbs than the header has room for
+        _patched(ciphertext, 8, "<I", 2),                   # claims two ciphertexts, carries one
+        _patched(ciphertext, 12, "<I", 0),                  # zero slots
+        _patched(ciphertext, 12, "<I", 1 << 20),            # more slots than the ring has
+        _patched(ciphertext, 24, "<d", float("nan")),       # scale
+        _patched(ciphertext, 24, "<d", -1.0),
+        ciphertext[:-8], ciphertext + b"\\0" * 8, ciphertext[:40], b"",
+    ]
+    for blob in hostile:
+        for call in (lambda b: _core.ckks_header(b), lambda b: _core.ckks_rescale(b),
+                     lambda b: _core.ckks_weighted_average([b, b], [0.5, 0.5]),
+                     lambda b: _core.ckks_weighted_average([ciphertext, b], [0.5, 0.5])):
+            with pytest.raises((RuntimeError, ValueError)):
+                call(blob)
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.data())
+def test_mutated_ciphertext_headers_parse_or_raise(ciphertext, data):
+    b = bytearray(ciphertext)
+    for _ in range(data.draw(st.integers(1, 3))):
+        b[data.draw(st.integers(0, 63))] = data.draw(st.integers(0, 255))
+    try:
+        _core.ckks_weighted_average([bytes(b), bytes(b)], [0.25, 0.75])
+    except (RuntimeError, ValueError):
+        pass
