@@ -48,10 +48,20 @@ def unpack_model_into_arena(model_pb: model_pb2.Model, arena) -> None:
     for i, var in enumerate(model_pb.variables):
         if not var.HasField("plaintext_tensor"):
             raise RuntimeError("unpack_model_into_arena handles plaintext tensors; decrypt ciphertexts first")
+        if not positional and var.name not in by_name:
+            raise ValueError(f"variable {var.name!r} is not part of this model")
         info = layout.variables[i] if positional else by_name[var.name]
         spec = var.plaintext_tensor.tensor_spec
         if spec.length != info.numel:
             raise ValueError(f"variable {var.name}: {spec.length} values on the wire, {info.numel} in the model")
+        # the payload is copied / cast on the device by element count: it must hold exactly that many elements of the
+        # type it declares (a short or mistyped value would make the kernel read past the staging buffer)
+        wire_type = int(spec.type.type)
+        if not 0 <= wire_type < len(dtypes.WIRE_SIZE):
+            raise ValueError(f"variable {var.name}: unknown wire data type {wire_type}")
+        if len(spec.value) != info.numel * dtypes.WIRE_SIZE[wire_type]:
+            raise ValueError(f"variable {var.name}: {len(spec.value)} payload bytes for {info.numel} "
+                             f"{dtypes.WIRE_NAMES[wire_type]} values")
         seg = layout.segments[info.segment]
         swap = spec.type.byte_order == model_pb2.DType.BIG_ENDIAN_ORDER
         key = (int(spec.type.type), dtypes.torch_to_wire(seg.dtype), swap)

@@ -376,6 +376,14 @@ class FederationEngine:
         """One fused launch over explicitly named slots (the controller-commanded path)."""
         install = self.arena.master[0] if (self.direct_install and self.arena.master[0] is not self.arena.seg[0]) else None
         nb = self.layout.total_bytes
+        # the (rank, slot) pairs come from messages (a learner's device_slot reference, relayed by the controller): they
+        # are turned into device addresses below, so they are bounded here
+        for r, sl in sources:
+            if not (0 <= int(r) < self.world and 0 <= int(sl) < self.n_slots):
+                raise ValueError("aggregation source (rank {}, slot {}) is outside this fabric ({} ranks, {} slots per "
+                                 "rank)".format(r, sl, self.world, self.n_slots))
+        if len(weights) != len(sources):
+            raise ValueError("aggregation needs one weight per source")
         if self.device.type != "cuda" or not self.fabric.peer_mapped:
             return self._aggregate_host(None, weights, sources=sources, accumulate=accumulate)
         srcs = [self._slot_ptr(int(r), int(sl)) for r, sl in sources]
@@ -506,6 +514,12 @@ class FederationEngine:
         assert self.async_rule, f"fold_async: rule {cfg.rule} is synchronous"
         r, j = divmod(learner, self.k)
         nb = self.layout.total_bytes
+        # learner index and slot numbers arrive in messages on the service path and become device addresses below
+        if not (0 <= r < self.world):
+            raise ValueError("fold_async: learner {} is outside this fabric ({} learners)".format(learner, self.world * self.k))
+        for name, val in (("slot", slot), ("previous_slot", previous_slot)):
+            if val is not None and not (0 <= int(val) < self.n_slots):
+                raise ValueError("fold_async: {} {} is outside the {} slots of a rank".format(name, val, self.n_slots))
         if task_no is None:
             task_no = self.task_counter[j] if r == self.rank else self._remote_tasks.setdefault(learner, 0) + 1
         if r != self.rank:

@@ -384,3 +384,24 @@ def test_asynchronous_rules_do_not_mix_fabric_and_outside_learners(tmp_path):
                 make()
         else:
             assert make()._fabric_specs == {}
+
+
+def test_out_of_range_device_references_are_refused(tmp_path):
+    """A device_slot reference is data from a message: rank and slot are bounded before they become addresses, and the
+    command is answered with an error instead of reading outside the slot buffers."""
+    from metisfl_b200.learner.device_backend import DeviceBackend, FabricSpec
+    from metisfl_b200.models.torch_model_ops import save_torch_model
+    from metisfl_b200.proto import learner_pb2
+    save_torch_model(FashionMnistMLP(), str(tmp_path / "m"))
+    for rule in ("FedAvg", "FedAsync"):
+        be = DeviceBackend(str(tmp_path / "m"), "cpu", FabricSpec(fabric_id="t" + rule, model_dtype="fp32", rule=rule))
+        try:
+            be.engine._publish_all(0)
+            for rank, slot in ((0, 10_000), (7, 0)):
+                req = learner_pb2.AggregateOnDeviceRequest(rule=rule, global_iteration=1, first_block=True,
+                                                           last_block=True, executor_rank=0, mix=0.5)
+                req.sources.add(learner_id="x", device_rank=rank, slot=slot, version=1, weight=1.0)
+                with pytest.raises(ValueError):
+                    be.aggregate(req)
+        finally:
+            be.close()

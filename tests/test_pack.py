@@ -79,3 +79,33 @@ def test_conv_filters_keep_logical_order_on_the_wire():
     x = torch.randn(2, 3, 4, 4)
     src.eval(); dst.eval()
     torch.testing.assert_close(src(x), dst(x))
+
+
+def test_unpack_refuses_payloads_that_do_not_match_their_declaration():
+    """A wire model from outside (an off-box learner staged by the executor rank) is data, not code: a value shorter
+    than its declared length, an unknown dtype code or an unknown variable is refused before anything is copied."""
+    import pytest
+    from metisfl_b200.models.zoo import FashionMnistMLP
+    from metisfl_b200.ops.pack import arena_to_model_pb, unpack_model_into_arena
+    from metisfl_b200.parallel.arena import ModelArena
+    arena = ModelArena(FashionMnistMLP(), "cpu", torch.float32)
+    good = arena_to_model_pb(arena)
+    unpack_model_into_arena(good, arena)                      # the well-formed model installs
+    short = type(good)(); short.CopyFrom(good)
+    spec = short.variables[0].plaintext_tensor.tensor_spec
+    spec.value = spec.value[:-4]
+    with pytest.raises(ValueError):
+        unpack_model_into_arena(short, arena)
+    typed = type(good)(); typed.CopyFrom(good)
+    typed.variables[0].plaintext_tensor.tensor_spec.type.type = 9     # declares FLOAT64, carries fp32 bytes
+    with pytest.raises(ValueError):
+        unpack_model_into_arena(typed, arena)
+    named = type(good)(); named.CopyFrom(good)
+    named.variables[0].name = "no.such.variable"      # (same count + unknown names = positional matching, by design)
+    del named.variables[-1]                            # a different count: names must resolve
+    with pytest.raises(ValueError):
+        unpack_model_into_arena(named, arena)
+    wrong_len = type(good)(); wrong_len.CopyFrom(good)
+    wrong_len.variables[0].plaintext_tensor.tensor_spec.length += 1
+    with pytest.raises(ValueError):
+        unpack_model_into_arena(wrong_len, arena)
