@@ -13,6 +13,29 @@ if TESTS_DIR not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "multiprocess: starts controller / learner PROCESSES on ports picked a moment "
+                                       "earlier; a failed attempt is repeated once (a port can be taken in between, a "
+                                       "process can be slow to come up on a loaded box)")
+
+
+def pytest_runtest_protocol(item, nextitem):
+    """One more attempt for tests marked ``multiprocess`` (no rerun plugin in this image).  The first failure is
+    reported as a warning so that a genuinely intermittent bug does not go unnoticed."""
+    if item.get_closest_marker("multiprocess") is None:
+        return None
+    from _pytest.runner import runtestprotocol
+    item.ihook.pytest_runtest_logstart(nodeid=item.nodeid, location=item.location)
+    reports = runtestprotocol(item, nextitem=nextitem, log=False)
+    failed = [r for r in reports if r.failed]
+    if failed:
+        import warnings
+        warnings.warn("{} failed on its first attempt and is repeated once:\n{}".format(
+            item.nodeid, str(failed[0].longrepr)[-1500:]))
+        reports = runtestprotocol(item, nextitem=nextitem, log=False)
+    for r in reports:
+        item.ihook.pytest_runtest_logreport(report=r)
+    item.ihook.pytest_runtest_logfinish(nodeid=item.nodeid, location=item.location)
+    return True
 
 
 def pytest_collection_modifyitems(config, items):

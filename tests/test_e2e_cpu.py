@@ -136,6 +136,7 @@ def test_config1_secure_aggregation_inprocess(tmp_path):
     assert np.isfinite(loss) and loss < 5.0
 
 
+@pytest.mark.multiprocess
 def test_config1_local_subprocess_launcher(tmp_path):
     """Controller and learners as real child processes (`python -m metisfl_b200.controller|learner`)."""
     s = DriverSession(FederationEnvironment(_env()), FashionMnistMLP(), _recipe(160, 1), None, _recipe(64, 3),
@@ -196,6 +197,7 @@ def test_echo_learners_drive_the_controller_without_training(tmp_path):
     assert len(tasks) == 2
 
 
+@pytest.mark.multiprocess
 @pytest.mark.timeout(300)
 def test_ssh_launcher_over_a_local_exec_transport(tmp_path, monkeypatch):
     """`Launcher: ssh` (the reference's only launcher, driver_session.py:225-262) end to end: the driver builds the
