@@ -463,7 +463,7 @@ bool Controller::AggregateBlockOnDevice(const std::vector<std::pair<std::string,
                                         const std::map<std::string, std::vector<ModelBytes>>& models,
                                         const std::map<std::string, double>& weights, bool first_block,
                                         bool last_block, RuntimeMetadata& md, Aggregated* result) {
-  if (!dispatcher_ || params_.rule == "PWA") return false;
+  if (!dispatcher_) return false;
   DeviceAggregateRequest dr;
   dr.rule = params_.rule;
   dr.global_iteration = global_iteration_;
@@ -521,6 +521,11 @@ bool Controller::AggregateBlockOnDevice(const std::vector<std::pair<std::string,
     throw std::runtime_error("asynchronous rule on a device fabric: a contribution without a device slot cannot be "
                              "folded (keep every learner of an asynchronous federation inside the fabric)");
   if (!any_device || dr.sources.empty()) return false;
+  if (params_.rule == "PWA")
+    // ciphertexts that live on the GPUs are reduced there (K8); one that arrived as bytes cannot join them
+    for (auto& s : dr.sources)
+      if (s.staged_model)
+        throw std::runtime_error("PWA on a device fabric: every contribution has to be a device reference");
   dr.z = z;
   DeviceAggregateResult out;
   if (!dispatcher_->AggregateOnDevice(dr, &out)) return false;

@@ -110,12 +110,17 @@ class DriverSessionBase(object):
         rule = env.global_model_config.aggregation_rule.aggregation_rule_name
         members = [i for i, l in enumerate(env.learners) if getattr(l, "in_fabric", True)]
         n = len(members)
+        forced = want in (True, "true", "on", "yes", "1")
         ok = n > 0 and rule in ("FedAvg", "FedStride", "FedRec", "FedAsync") and self._he_scheme is None
+        # encrypted FedAvg on the fabric (ciphertexts in peer-visible HBM, K8 reduces them over NVLink): on request
+        # only (`DeviceFabric: true`), and only when every learner is a member - a ciphertext that arrives as bytes
+        # cannot be added to one that lives on a GPU
+        if rule == "PWA" and self._he_scheme is not None and forced and n == len(env.learners) and n > 0:
+            ok = True
         # the asynchronous rules keep their rolling state on the executor GPU: a learner outside the fabric would be
         # folded on the host into a second, diverging community model - such a federation stays on the host path
         ok = ok and not (rule in ("FedRec", "FedAsync") and n < len(env.learners))
         ok = ok and (self.launcher == "local" or n == 1)   # one process is one rank: in-process only with one member
-        forced = want in (True, "true", "on", "yes", "1")
         if not forced:
             ok = ok and torch.cuda.is_available() and n <= torch.cuda.device_count() and n <= 16
         if not ok:

@@ -39,7 +39,7 @@ class FabricSpec:
     world: int = 1
     init_method: str = ""            # torch.distributed rendezvous, e.g. tcp://127.0.0.1:29511 (unused when world == 1)
     fabric_id: str = "fabric0"
-    rule: str = "FedAvg"             # FedAvg | FedStride | FedRec | FedAsync
+    rule: str = "FedAvg"             # FedAvg | FedStride | FedRec | FedAsync | PWA (needs the learner's HE key files)
     staging_slots: int = 2           # per rank, for models of learners outside the fabric
     executor_rank: int = 0
     model_dtype: Optional[str] = None
@@ -59,15 +59,31 @@ class FabricSpec:
         return t + (",dtype=" + self.model_dtype if self.model_dtype else "")
 
 
+def _spec_of(var_pb):
+    return var_pb.ciphertext_tensor.tensor_spec if var_pb.HasField("ciphertext_tensor") else \
+        var_pb.plaintext_tensor.tensor_spec
+
+
 def _has_bytes(model_pb) -> bool:
-    return len(model_pb.variables) > 0 and len(model_pb.variables[0].plaintext_tensor.tensor_spec.value) > 0
+    return len(model_pb.variables) > 0 and len(_spec_of(model_pb.variables[0]).value) > 0
 
 
 def _ref_of(model_pb):
     if not len(model_pb.variables):
         return None
-    spec = model_pb.variables[0].plaintext_tensor.tensor_spec
+    spec = _spec_of(model_pb.variables[0])
     return spec.device_slot if spec.HasField("device_slot") else None
+
+
+def _as_ciphertext_ref(model_pb):
+    """A reference model whose variables are marked as ciphertext: what a learner of a secure federation reports.  The
+    controller keeps treating it as an opaque reference (``controller.cc: DeviceSlotOf`` reads the slot of either
+    kind)."""
+    out = model_pb2.Model()
+    for v in model_pb.variables:
+        nv = out.variables.add(name=v.name, trainable=v.trainable)
+        nv.ciphertext_tensor.tensor_spec.CopyFrom(_spec_of(v))
+    return out
 
 
 def _on_device(fn):
@@ -87,7 +103,8 @@ def _on_device(fn):
 class DeviceBackend:
     """One per learner process: a ``FederationEngine`` rank plus a private evaluation copy of the module."""
 
-    def __init__(self, model_dir: str, device, fabric: FabricSpec, loss_fn=None, endpoint=None, certificate=b""):
+    def __init__(self, model_dir: str, device, fabric: FabricSpec, loss_fn=None, endpoint=None, certificate=b"",
+                 he_scheme_config_pb=None):
         self.fabric = fabric
         self._endpoint, self._certificate = endpoint, certificate or b""
         self.device = torch.device(device if device is not None else ("cuda" if torch.cuda.is_available() else "cpu"))
@@ -111,7 +128,9 @@ class DeviceBackend:
         # the controller owns the scaling factors, so nothing is pre-scaled at publish time (no in-switch reduction);
         # the working copy is separate from the community buffer so that evaluation of version v and training from
         # version v can overlap
-        cfg = EngineConfig(learners_per_gpu=1, model_dtype=dtype, rule=fabric.rule, nvls=False,
+        # PWA: the engine keeps its synchronous buffers; encryption / reduction / decryption are driven from here
+        cfg = EngineConfig(learners_per_gpu=1, model_dtype=dtype, rule="FedAvg" if fabric.rule == "PWA" else fabric.rule,
+                           nvls=False,
                            staging_slots=fabric.staging_slots, executor_rank=fabric.executor_rank,
                            direct_install=False)
         self.engine = FederationEngine(lambda: module, cfg, loss_fn=loss_fn, device=self.device)
@@ -123,6 +142,14 @@ class DeviceBackend:
                 _gemm.use_b200_linear(eval_module)
         self.eval_arena = ModelArena(eval_module, self.device, dtype)
         assert self.eval_arena.layout.total_bytes == self.engine.layout.total_bytes
+        self.secure = None
+        if fabric.rule == "PWA":
+            he = he_scheme_config_pb
+            if he is None or not he.enabled or he.WhichOneof("config") != "ckks_scheme_config":
+                raise RuntimeError("rule PWA on the device fabric needs the learner's CKKS configuration (key files)")
+            from metisfl_b200.parallel.secure import FabricSecure
+            self.secure = FabricSecure(self.engine, he.crypto_context_file, he.public_key_file, he.private_key_file,
+                                       he.ckks_scheme_config.batch_size, he.ckks_scheme_config.scaling_factor_bits)
         # every rank learns every rank's service endpoint, so the controller can command the whole fabric as soon as
         # ONE of its learners has joined (the fused kernel needs all ranks to launch)
         self._peers = self.engine.fabric.all_gather_object((self._endpoint or "", bytes(self._certificate)))
@@ -153,7 +180,7 @@ class DeviceBackend:
             with self._comm_lock:
                 live = eng.async_rule and eng.version > 0  # folds are already landing in the buffers: keep them
                 if (self._installed_bytes_iteration != key or iteration is None) and not live:
-                    eng.install_community_model(model_pb)
+                    self._install_bytes(model_pb)
                     self._installed_bytes_iteration = key
             return None
         ref = _ref_of(model_pb)
@@ -162,6 +189,29 @@ class DeviceBackend:
             if not eng.is_executor or eng.version < self._known_version:
                 eng.version = max(eng.version, self._known_version)
         return ref
+
+    def _install_bytes(self, model_pb):
+        """A model that arrived as bytes -> the community buffer.  Encrypted models (the driver's initial ship of a
+        secure federation, ``driver_session.py:334-342`` with ``he_scheme``; an encrypted snapshot) are decrypted
+        with this learner's private key first, like ``model_ops.py:24-57``."""
+        eng = self.engine
+        if not model_pb.variables[0].HasField("ciphertext_tensor"):
+            return eng.install_community_model(model_pb)
+        if self.secure is None:
+            raise RuntimeError("an encrypted model reached a learner that holds no keys")
+        from metisfl_b200.parallel.secure import FabricSecure
+        if len(model_pb.variables) == 1 and model_pb.variables[0].name == FabricSecure.SNAPSHOT_VARIABLE:
+            return self.secure.install_blob(model_pb.variables[0].ciphertext_tensor.tensor_spec.value)
+        from metisfl_b200.utils.proto_messages_factory import ModelProtoMessages
+        codec = ModelProtoMessages.TensorSpecProto
+        names, trainables, values = [], [], []
+        for var in model_pb.variables:
+            spec = var.ciphertext_tensor.tensor_spec
+            flat = self.secure.host.decrypt(spec.value, spec.length)
+            names.append(var.name)
+            trainables.append(var.trainable)
+            values.append(codec.proto_tensor_spec_with_list_values_to_numpy_array_like(spec, flat))
+        eng.install_community_model(ModelProtoMessages.construct_model_pb_from_np(values, names, trainables))
 
     # -- training ---------------------------------------------------------------------------------------------------
     @_on_device
@@ -205,6 +255,9 @@ class DeviceBackend:
         stats = {"loss": [float(loss)]} if loss is not None else {}
         slot = eng.publish_slot(0)
         local_ref = eng.reference_model_pb(slot, version=eng.task_counter[0])
+        if self.secure is not None:   # the published model leaves this learner's hands only as a ciphertext
+            self.secure.encrypt_slot(slot)
+            local_ref = _as_ciphertext_ref(local_ref)
         meta = ModelProtoFactory.CompletedLearningTaskProtoMessage(
             weights_values=[], weights_trainable=[], weights_names=[], train_stats=stats,
             completed_epochs=steps / spe, global_iteration=learning_task_pb.global_iteration,
@@ -347,7 +400,18 @@ class DeviceBackend:
                 t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 t0.record(tstream)
             wall0 = time.perf_counter()
-            if not eng.async_rule:
+            if self.secure is not None:
+                # encrypted FedAvg: the controller's scaling factors, by fabric rank; the reduction runs on ciphertexts
+                # (K8 over NVLink) and every learner decrypts its own copy of the encrypted community model
+                w = [0.0] * eng.world
+                for src in req.sources:
+                    if len(src.staged_model.variables) or not 0 <= int(src.device_rank) < eng.world:
+                        raise ValueError("secure aggregation on the fabric takes device references of fabric ranks only")
+                    w[int(src.device_rank)] = float(src.weight)
+                self.secure.reduce(w)
+                self.secure.decrypt_install()
+                version = eng.global_iteration
+            elif not eng.async_rule:
                 sources, weights, staged = [], [], 0
                 for src in req.sources:
                     if len(src.staged_model.variables):
@@ -381,7 +445,7 @@ class DeviceBackend:
                 resp.device_ms = t0.elapsed_time(t1)
             else:
                 resp.device_ms = (time.perf_counter() - wall0) * 1e3
-            if req.quantify and req.last_block:
+            if req.quantify and req.last_block and self.secure is None:   # plaintext statistics only
                 eng.quantify_community()
                 rep = eng.quantifier_report()
                 for info in eng.layout.variables:
@@ -389,7 +453,19 @@ class DeviceBackend:
                     resp.quantifiers.add(tensor_non_zeros=int(nz), tensor_zeros=int(z), tensor_size_bytes=int(nbytes))
             resp.version = version
             resp.community_ref.CopyFrom(eng.reference_model_pb(eng.COMMUNITY_SLOT, version))
-            if req.return_model_bytes:
+            if self.secure is not None:
+                resp.community_ref.CopyFrom(_as_ciphertext_ref(resp.community_ref))
+                if req.return_model_bytes:   # what the controller may keep (snapshots) stays encrypted
+                    from metisfl_b200.parallel.secure import FabricSecure
+                    blob = self.secure.community_blob()
+                    var = resp.community_model.variables.add(name=FabricSecure.SNAPSHOT_VARIABLE, trainable=True)
+                    spec = var.ciphertext_tensor.tensor_spec
+                    spec.length = self.secure.n
+                    spec.dimensions.append(self.secure.n)
+                    spec.type.type = model_pb2.DType.FLOAT64
+                    spec.type.byte_order = model_pb2.DType.LITTLE_ENDIAN_ORDER
+                    spec.value = blob
+            elif req.return_model_bytes:
                 resp.community_model.CopyFrom(eng.community_model_pb())
         from metisfl_b200.learner.learner_servicer import _ack
         resp.ack.CopyFrom(_ack(True))

@@ -72,7 +72,7 @@ class Learner(object):
                 pub = SSLConfigurator.gen_public_ssl_config_pb_as_stream(ssl)
                 cert = pub.ssl_config_stream.public_certificate_stream
             self._device_backend = DeviceBackend(
-                model_dir, device, spec, certificate=cert,
+                model_dir, device, spec, certificate=cert, he_scheme_config_pb=he_scheme_config_pb,
                 endpoint="{}:{}".format(learner_server_entity.hostname, learner_server_entity.port))
         self._datasets = None
         self._he_scheme = None

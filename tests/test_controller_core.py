@@ -246,12 +246,13 @@ def test_clean_leave_shrinks_the_barrier():
 
 
 # ---- device aggregation commands (no GPU: a fake fabric that answers with references) ---------------------------
-def _ref_model(rank, slot, version, numel=8):
-    """A control-only model as a fabric learner sends it: one fp32 variable, no bytes, `TensorSpec.device_slot` set."""
+def _ref_model(rank, slot, version, numel=8, ciphertext=False):
+    """A control-only model as a fabric learner sends it: one fp32 variable, no bytes, `TensorSpec.device_slot` set
+    (under `ciphertext_tensor` when the learner of a secure federation reports an encrypted slot)."""
     from metisfl_b200.proto import model_pb2
     m = model_pb2.Model()
     var = m.variables.add(name="w", trainable=True)
-    spec = var.plaintext_tensor.tensor_spec
+    spec = (var.ciphertext_tensor if ciphertext else var.plaintext_tensor).tensor_spec
     spec.length = numel
     spec.dimensions.append(numel)
     spec.type.type = model_pb2.DType.FLOAT32
@@ -267,9 +268,14 @@ class FabricFederation:
     command it is given and answers like an executor rank would (a reference to the community buffer)."""
     COMMUNITY = 0xFFFFFFFF
 
-    def __init__(self, rule="FedAvg", protocol=1, n=2, examples=None, stride=0, fail_first=False):
+    def __init__(self, rule="FedAvg", protocol=1, n=2, examples=None, stride=0, fail_first=False, he_context="",
+                 bytes_from=()):
         p = _core.ControllerParams()
         p.rule, p.protocol, p.stride_length = rule, protocol, stride
+        if he_context:
+            p.he_crypto_context_file = he_context
+        self.ciphertext = rule == "PWA"
+        self.bytes_from = set(bytes_from)     # ranks whose learners answer with (ciphertext) bytes instead of references
         p.batch_size, p.epochs = 10, 1
         if rule in ("FedRec", "FedAsync"):
             p.lineage_length_eviction, p.lineage_length = True, 2
@@ -288,7 +294,9 @@ class FabricFederation:
             self.task_no[lid] = self.task_no.get(lid, 0) + 1
             n = self.task_no[lid]
         rank = int(lid.rsplit(":", 1)[1]) - 9100      # the first task can arrive before join() has returned
-        model = _ref_model(rank, slot=n % 2, version=n)
+        model = _ref_model(rank, slot=n % 2, version=n, ciphertext=self.ciphertext)
+        if rank in self.bytes_from:
+            model = self.bytes_model
         t0 = time.time()
         while lid not in self.tokens and time.time() - t0 < 5:
             time.sleep(0.005)
@@ -307,7 +315,8 @@ class FabricFederation:
             first = len(self.commands) == 1
         if self.fail_first and first:
             return {"error": "injected failure"}
-        return {"model_ref": _ref_model(0, self.COMMUNITY, req["global_iteration"] + 1), "device_ms": 0.125,
+        return {"model_ref": _ref_model(0, self.COMMUNITY, req["global_iteration"] + 1, ciphertext=self.ciphertext),
+                "device_ms": 0.125,
                 "quantifiers": [(7, 1, 32)], "model_bytes": None, "error": None}
 
     def join(self, i):
@@ -390,4 +399,56 @@ def test_fedstride_round_is_commanded_block_by_block():
     assert not b["first_block"] and b["last_block"] and len(a["sources"]) == len(b["sources"]) == 1
     assert {a["sources"][0]["learner_id"], b["sources"][0]["learner_id"]} == set(ids)
     assert abs(a["sources"][0]["weight"] - 0.5) < 1e-9 and b["quantify"]
+    f.core.shutdown()
+
+
+def _secure_setup(tmp_path):
+    from metisfl_b200.encryption import fhe
+    from metisfl_b200.proto import model_pb2
+    scheme = fhe.CKKS(4096, 52, backend="host")
+    scheme.gen_crypto_context_and_keys(str(tmp_path / "keys"))
+    m = model_pb2.Model()
+    var = m.variables.add(name="w", trainable=True)
+    spec = var.ciphertext_tensor.tensor_spec
+    spec.length = 8
+    spec.dimensions.append(8)
+    spec.type.type = model_pb2.DType.FLOAT32
+    spec.type.byte_order = model_pb2.DType.LITTLE_ENDIAN_ORDER
+    spec.value = scheme.encrypt(np.arange(8, dtype=np.float64))
+    return scheme.get_crypto_params_files()["crypto_context_file"], m.SerializeToString()
+
+
+def test_secure_round_is_commanded_on_the_fabric(tmp_path):
+    """PWA with learners that report ciphertext REFERENCES: the controller commands the reduction (rule, ranks, its
+    scaling factors) instead of calling the host PWA (`private_weighted_average.cc:24-82`), which has nothing to add."""
+    ctx, initial = _secure_setup(tmp_path)
+    f = FabricFederation(rule="PWA", n=2, examples=[100, 300], he_context=ctx)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, initial))
+    ids = [f.join(i) for i in range(2)]
+    f.wait_commands(2)
+    f.core.wait_idle()
+    full = [c for c in f.commands if len(c["sources"]) == 2]
+    assert full
+    c = full[0]
+    assert c["rule"] == "PWA" and c["first_block"] and c["last_block"]
+    by_id = {s["learner_id"]: s for s in c["sources"]}
+    assert by_id[ids[0]]["device_rank"] == 0 and by_id[ids[1]]["device_rank"] == 1
+    assert all(s["staged_model"] is None for s in c["sources"])
+    assert abs(by_id[ids[0]]["weight"] - 0.25) < 1e-9 and abs(by_id[ids[1]]["weight"] - 0.75) < 1e-9
+    assert f.core.aggregation_failures() == 0
+    f.core.shutdown()
+
+
+def test_secure_round_refuses_to_mix_references_and_ciphertext_bytes(tmp_path):
+    ctx, initial = _secure_setup(tmp_path)
+    f = FabricFederation(rule="PWA", n=2, examples=[100, 100], he_context=ctx, bytes_from=(1,))
+    f.bytes_model = initial
+    f.core.replace_community_model(_core.build_federated_model(0, 0, initial))
+    [f.join(i) for i in range(2)]
+    t0 = time.time()
+    while f.core.aggregation_failures() == 0 and time.time() - t0 < 20:
+        time.sleep(0.02)
+    assert f.core.aggregation_failures() >= 1
+    with f.lock:
+        assert not [c for c in f.commands if len(c["sources"]) == 2]   # no command ever mixed the two kinds
     f.core.shutdown()

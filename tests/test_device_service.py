@@ -410,3 +410,79 @@ def test_out_of_range_device_references_are_refused(tmp_path):
                     be.aggregate(req)
         finally:
             be.close()
+
+
+def _secure_run(tmp_path, tag, fabric, monkeypatch, n_learners=1, launcher="inprocess", rounds=3):
+    d = _env(**{"GlobalModelConfig.AggregationRule.Name": "PWA", "TerminationSignals.FederationRounds": rounds,
+                "TerminationSignals.ExecutionCutoffTimeMins": 3, "LocalModelConfig.OptimizerConfig.LearningRate": 0.0005})
+    fe = d["FederationEnvironment"]
+    fe["HomomorphicEncryption"] = {"Scheme": "CKKS", "BatchSize": 4096, "ScalingFactorBits": 52}
+    fe["Learners"] = fe["Learners"][:n_learners]
+    fe["DeviceFabric"] = fabric
+    fe["ModelDType"] = "fp32"
+    snap = tmp_path / f"snap_{tag}"
+    monkeypatch.setenv("METISFL_SNAPSHOT_DIR", str(snap))
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 10))
+    s = DriverSession(FederationEnvironment(d), model, _recipe(96, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / f"w_{tag}"), launcher=launcher, banner=False)
+    return s, s.run(request_every_secs=0.3), str(snap)
+
+
+def _snapshot_variables(snapshot_dir):
+    import json
+    with open(os.path.join(snapshot_dir, "state.json")) as f:
+        state = json.load(f)
+    with open(os.path.join(snapshot_dir, state["community_model_file"]), "rb") as f:
+        return model_pb2.FederatedModel.FromString(f.read()).model.variables
+
+
+def _last_loss(stats):
+    ev = [e for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
+    assert ev
+    return float(list(ev[-1]["evaluations"].values())[0]["test_evaluation"]["metric_values"]["loss"])
+
+
+@pytest.mark.timeout(300)
+def test_secure_aggregation_on_the_fabric_single_learner(tmp_path, monkeypatch):
+    """PWA with `DeviceFabric: true` (reference flow: SURVEY 3.4): the learner reports a ciphertext REFERENCE, the
+    controller commands the reduction with its scaling factors, the learner decrypts into its community buffer; what
+    the controller stores (snapshots) is a ciphertext."""
+    s, stats, snap = _secure_run(tmp_path, "sec", True, monkeypatch)
+    assert s._fabric_specs and "rule=PWA" in s._fabric_specs[0]
+    c = _counters(stats)
+    assert c["fabric_learners"] == 1 and c["aggregation_failures"] == 0 and c["aggregation_durations_device_timed"]
+    # the only model bytes the controller ever received are the driver's (encrypted) initial model
+    assert c["model_bytes_received"] == 0
+    md = [m for m in stats["federation_runtime_metadata"]["metadata"] if m.get("model_aggregation_block_duration_ms")]
+    assert len(md) >= 3
+    loss = _last_loss(stats)
+    assert np.isfinite(loss) and loss < 5.0
+    variables = _snapshot_variables(snap)
+    assert len(variables) == 1 and variables[0].HasField("ciphertext_tensor")
+    assert len(variables[0].ciphertext_tensor.tensor_spec.value) > 100_000   # one 4096-slot ciphertext is 786 KB
+    # same federation on the host path (ciphertext bytes through the controller): same quality of result
+    s2, stats2, _ = _secure_run(tmp_path, "sechost", False, monkeypatch)
+    assert not s2._fabric_specs and _counters(stats2)["model_bytes_received"] > 100_000
+    assert abs(_last_loss(stats2) - loss) < 0.5
+
+
+@pytest.mark.multiprocess
+@pytest.mark.timeout(300)
+def test_secure_aggregation_on_a_two_rank_gloo_fabric(tmp_path, monkeypatch):
+    s, stats, snap = _secure_run(tmp_path, "sec2", True, monkeypatch, n_learners=2, launcher="local")
+    c = _counters(stats)
+    assert c["fabric_learners"] == 2 and c["aggregation_failures"] == 0 and c["model_bytes_received"] == 0
+    md = [m for m in stats["federation_runtime_metadata"]["metadata"] if m.get("model_aggregation_block_duration_ms")]
+    assert len(md) >= 3
+    loss = _last_loss(stats)
+    assert np.isfinite(loss) and loss < 5.0
+    # the driver holds the private key: the controller's encrypted snapshot decrypts to a sane averaged model
+    variables = _snapshot_variables(snap)
+    assert len(variables) == 1 and variables[0].HasField("ciphertext_tensor")
+    spec = variables[0].ciphertext_tensor.tensor_spec
+    avg = np.asarray(s._he_scheme.decrypt(spec.value, spec.length))
+    assert avg.size >= 784 * 10 + 10 and np.isfinite(avg).all() and 0 < np.abs(avg).max() < 1.0   # (+ arena padding)
+    for name in ("learner0", "learner1"):
+        log = open(os.path.join(str(tmp_path / "w_sec2"), name + ".log"), errors="replace").read()
+        assert "Traceback" not in log, log[-3000:]
