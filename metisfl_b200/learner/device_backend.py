@@ -207,7 +207,7 @@ class DeviceBackend:
         names, trainables, values = [], [], []
         for var in model_pb.variables:
             spec = var.ciphertext_tensor.tensor_spec
-            flat = self.secure.host.decrypt(spec.value, spec.length)
+            flat = self.secure.decrypt_blob(spec.value, spec.length)
             names.append(var.name)
             trainables.append(var.trainable)
             values.append(codec.proto_tensor_spec_with_list_values_to_numpy_array_like(spec, flat))
@@ -257,6 +257,8 @@ class DeviceBackend:
         local_ref = eng.reference_model_pb(slot, version=eng.task_counter[0])
         if self.secure is not None:   # the published model leaves this learner's hands only as a ciphertext
             self.secure.encrypt_slot(slot)
+            if cuda:   # the completion message says "the ciphertext is there": peers will read it
+                torch.cuda.current_stream(self.device).synchronize()
             local_ref = _as_ciphertext_ref(local_ref)
         meta = ModelProtoFactory.CompletedLearningTaskProtoMessage(
             weights_values=[], weights_trainable=[], weights_names=[], train_stats=stats,

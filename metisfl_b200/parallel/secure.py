@@ -208,7 +208,13 @@ class FabricSecure:
         head = gpu_ckks.pack_header(g.log_n, g.n_limbs, self.n_ct, g.slots, self.n, g.scale * g.scale, g.moduli)
         return head + self.ct_out.local.view(torch.int64)[:self.words].cpu().numpy().tobytes()
 
+    def decrypt_blob(self, blob: bytes, n_values: int):
+        """Byte-layout ciphertext (the driver's initial model, a snapshot) -> float64 numpy array."""
+        if self.cuda:
+            return self.g.decrypt(blob, int(n_values))
+        return self.host.decrypt(blob, int(n_values))
+
     def install_blob(self, blob: bytes):
         """An encrypted snapshot back into the community buffer (resume)."""
-        avg = torch.from_numpy(self.host.decrypt(blob, self.n)).to(self.e.device)
+        avg = torch.from_numpy(self.decrypt_blob(blob, self.n)).to(self.e.device)
         self._scatter(avg, self.e.community_views)
