@@ -486,3 +486,63 @@ def test_secure_aggregation_on_a_two_rank_gloo_fabric(tmp_path, monkeypatch):
     for name in ("learner0", "learner1"):
         log = open(os.path.join(str(tmp_path / "w_sec2"), name + ".log"), errors="replace").read()
         assert "Traceback" not in log, log[-3000:]
+
+
+def test_secure_backend_commands_and_the_two_encrypted_byte_forms(tmp_path):
+    """DeviceBackend with rule PWA, without the services around it: the driver's per-variable encrypted model is
+    decrypted into the community buffer, `aggregate` turns the controller's weight into the decrypted average and
+    returns an encrypted snapshot, and that snapshot re-installs (resume); staged byte models are refused."""
+    from metisfl_b200.encryption import fhe
+    from metisfl_b200.learner.device_backend import DeviceBackend, FabricSpec
+    from metisfl_b200.models.torch_model_ops import save_torch_model
+    from metisfl_b200.proto import learner_pb2, metis_pb2
+    from metisfl_b200.utils.proto_messages_factory import ModelProtoMessages
+    torch.manual_seed(3)
+    model = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(20, 4))
+    save_torch_model(model, str(tmp_path / "m"))
+    scheme = fhe.CKKS(4096, 52, backend="host")
+    scheme.gen_crypto_context_and_keys(str(tmp_path / "keys"))
+    files = scheme.get_crypto_params_files()
+    he = metis_pb2.HESchemeConfig(enabled=True, crypto_context_file=files["crypto_context_file"],
+                                  public_key_file=files["public_key_file"], private_key_file=files["private_key_file"])
+    he.ckks_scheme_config.batch_size, he.ckks_scheme_config.scaling_factor_bits = 4096, 52
+    with pytest.raises(RuntimeError):   # PWA without the key files
+        DeviceBackend(str(tmp_path / "m"), "cpu", FabricSpec(fabric_id="nokeys", model_dtype="fp32", rule="PWA"))
+    be = DeviceBackend(str(tmp_path / "m"), "cpu", FabricSpec(fabric_id="s", model_dtype="fp32", rule="PWA"),
+                       he_scheme_config_pb=he)
+    try:
+        eng = be.engine
+        sd = {k: v.detach().clone() + 1.0 for k, v in model.state_dict().items()}
+        names = list(sd)
+        initial = ModelProtoMessages.construct_model_pb_from_np([sd[k] for k in names], names, [True] * len(names),
+                                                                he_scheme=scheme)
+        assert initial.variables[0].HasField("ciphertext_tensor")
+        be._adopt(initial, iteration=0)
+        for k in names:
+            torch.testing.assert_close(eng.community_state_dict()[k], sd[k], atol=1e-6, rtol=0)
+        # the learner's slot = the initial model; the controller weighs it with 0.5
+        eng._publish_all(0)
+        be.secure.encrypt_slot(0)
+        req = learner_pb2.AggregateOnDeviceRequest(rule="PWA", global_iteration=1, first_block=True, last_block=True,
+                                                   quantify=True, return_model_bytes=True, executor_rank=0)
+        req.sources.add(learner_id="a", device_rank=0, slot=0, version=1, weight=0.5)
+        resp = be.aggregate(req)
+        assert resp.ack.status and len(resp.quantifiers) == 0          # no plaintext statistics leave the learner
+        assert resp.community_ref.variables[0].HasField("ciphertext_tensor")
+        assert resp.community_ref.variables[0].ciphertext_tensor.tensor_spec.HasField("device_slot")
+        want = {k: 0.5 * model.state_dict()[k] for k in names}
+        for k in names:
+            torch.testing.assert_close(eng.community_state_dict()[k], want[k], atol=1e-6, rtol=0)
+        assert len(resp.community_model.variables) == 1
+        snap = resp.community_model
+        for v in eng.community_views:
+            v.zero_()
+        be._adopt(snap, iteration=7)
+        for k in names:
+            torch.testing.assert_close(eng.community_state_dict()[k], want[k], atol=1e-6, rtol=0)
+        bad = learner_pb2.AggregateOnDeviceRequest(rule="PWA", global_iteration=2, first_block=True, last_block=True)
+        bad.sources.add(learner_id="b", weight=1.0).staged_model.CopyFrom(initial)
+        with pytest.raises(ValueError):
+            be.aggregate(bad)
+    finally:
+        be.close()
