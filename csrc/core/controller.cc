@@ -66,6 +66,9 @@ Controller::Controller(ControllerParams params, std::shared_ptr<Dispatcher> disp
   else throw std::invalid_argument("unknown communication protocol");
   if (params_.redis) store_ = std::make_unique<RedisModelStore>(params_.redis_host, params_.redis_port, params_.eviction);
   else store_ = std::make_unique<HashMapModelStore>(params_.eviction);
+  if (params_.participation_ratio < 0.f || params_.participation_ratio > 1.f)
+    throw std::invalid_argument("participation_ratio must be in [0, 1] (0 = everybody)");
+  sample_rng_.seed(params_.sampling_seed ? params_.sampling_seed : std::random_device{}());
   if (params_.task_deadline_secs > 0) watchdog_ = std::thread([this] { WatchdogLoop(); });
 }
 
@@ -85,6 +88,33 @@ std::vector<std::string> Controller::ActiveIdsLocked() const {
   std::vector<std::string> ids;
   for (auto& kv : learners_) ids.push_back(kv.first);
   return ids;
+}
+
+bool Controller::Sampling() const {
+  return params_.protocol != Protocol::kAsynchronous && params_.participation_ratio > 0.f &&
+         params_.participation_ratio < 1.f;
+}
+
+std::vector<std::string> Controller::BarrierSetLocked() const {
+  auto active = ActiveIdsLocked();
+  if (!Sampling() || cohort_.empty()) return active;
+  std::vector<std::string> out;
+  for (auto& a : active)
+    if (cohort_.count(a)) out.push_back(a);
+  return out;
+}
+
+std::vector<std::string> Controller::SampleCohortLocked(const std::vector<std::string>& active) {
+  std::vector<std::string> pool(active.begin(), active.end());
+  const size_t k = std::min(pool.size(), (size_t)std::max(1.0, std::ceil((double)params_.participation_ratio * pool.size())));
+  // partial Fisher-Yates: the first k entries are a uniform sample without replacement
+  for (size_t i = 0; i < k; ++i) {
+    std::uniform_int_distribution<size_t> pick(i, pool.size() - 1);
+    std::swap(pool[i], pool[pick(sample_rng_)]);
+  }
+  pool.resize(k);
+  std::sort(pool.begin(), pool.end());
+  return pool;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -154,15 +184,21 @@ void Controller::EvictLocked(const std::string& id, const char* why) {
   local_tasks_.erase(id);
   store_->EraseModels({id});
   device_w_.erase(id);
+  const bool was_in_cohort = cohort_.erase(id) > 0;
   Log("learner %s %s", id, why);
   // a shrinking federation may complete a synchronous barrier
   if (params_.protocol != Protocol::kAsynchronous && !learners_.empty() && !stop_) {
-    pool_.Push([this] {
+    pool_.Push([this, was_in_cohort] {
       {
         std::lock_guard<std::mutex> l(mu_);
         auto* sync = dynamic_cast<SynchronousScheduler*>(scheduler_.get());
         if (!sync) return;
-        auto active = ActiveIdsLocked();
+        if (Sampling() && was_in_cohort && cohort_.empty() && !learners_.empty() && global_iteration_ > 0) {
+          // the whole cohort of this round is gone: nobody is left to reach the barrier, so the round closes without
+          // a contribution and a fresh cohort is drawn from the learners that remain
+          AfterBarrier({}, "");
+        }
+        auto active = BarrierSetLocked();
         if (active.empty()) return;
         // re-check the barrier by replaying an already-completed learner (idempotent insert)
         for (auto& a : active) {
@@ -270,6 +306,7 @@ void Controller::SendRunTasksLocked(const std::vector<std::string>& ids) {
     rec.task_issued_iteration = global_iteration_;
     rec.task_issued_at = now;
     rec.task_in_flight = true;
+    if (Sampling()) cohort_.insert(id);
     items.push_back({rec.endpoint, global_iteration_, rec.num_local_updates, params_.percent_validation});
     if (!metadata_.empty()) {
       metadata_.back().assigned.push_back(id);
@@ -318,7 +355,7 @@ void Controller::ScheduleTasks(const std::string& id) {
   {
     std::lock_guard<std::mutex> l(mu_);
     if (stop_ || !learners_.count(id)) return;
-    const auto active = ActiveIdsLocked();
+    const auto active = BarrierSetLocked();   // with client sampling: this round's cohort
     auto to_schedule = scheduler_->ScheduleNext(id, active);
     if (to_schedule.empty()) return;  // synchronous barrier not reached yet
     AfterBarrier(to_schedule, id);
@@ -326,9 +363,14 @@ void Controller::ScheduleTasks(const std::string& id) {
   FlushOutbox();
 }
 
-void Controller::AfterBarrier(const std::vector<std::string>& to_schedule, const std::string& completing) {
+void Controller::AfterBarrier(const std::vector<std::string>& completed, const std::string& completing) {
   const auto active = ActiveIdsLocked();
-  const auto selected = ScheduledCardinality::Select(to_schedule, active);
+  // without sampling the learners that reached the barrier are the ones that train next; with it, the round
+  // aggregates its cohort (not the stale models of learners that sat it out) and a new cohort is drawn
+  const bool sampling = Sampling();
+  const auto selected = sampling ? completed : ScheduledCardinality::Select(completed, active);
+  const auto to_schedule = sampling ? SampleCohortLocked(active) : completed;
+  if (sampling) cohort_.clear();
   if (metadata_.empty()) return;
   RuntimeMetadata& md = metadata_.back();
   uint32_t contributors = 0;
@@ -373,7 +415,7 @@ void Controller::AfterBarrier(const std::vector<std::string>& to_schedule, const
   ++global_iteration_;
   if (params_.protocol == Protocol::kSemiSynchronous &&
       (global_iteration_ == 2 || params_.semi_sync_recompute))
-    UpdateTaskTemplates(to_schedule);
+    UpdateTaskTemplates(sampling ? active : to_schedule);
   RuntimeMetadata next;
   next.global_iteration = global_iteration_;
   next.started_at = NowSeconds();

@@ -19,6 +19,8 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <random>
+#include <set>
 #include <string>
 #include <thread>
 #include <vector>
@@ -59,7 +61,11 @@ struct ControllerParams {
   EvictionPolicy eviction;
   uint32_t batch_size = 100, epochs = 5;
   float percent_validation = 0.f;
+  // synchronous / semi-synchronous protocols: fraction of the active learners that get a task each round (client
+  // sampling, the "C" of FedAvg).  The reference plumbs the field end to end and never reads it (metis.proto:307,
+  // controller.cc:730-731); here a value in (0, 1) draws a fresh cohort per round.
   float participation_ratio = 1.f;
+  uint64_t sampling_seed = 0;             // 0 = seeded from std::random_device
   std::string he_crypto_context_file;
   uint32_t he_batch_size = 4096, he_scaling_bits = 52;
   uint32_t community_lineage_length = 4;  // community checkpoints kept for GetCommunityModelLineage
@@ -217,6 +223,12 @@ class Controller {
   void SendRunTasksLocked(const std::vector<std::string>& ids);
   void SendEvaluationTasksLocked(const std::vector<std::string>& ids, uint32_t eval_index);
   std::vector<std::string> ActiveIdsLocked() const;
+  // client sampling: the learners the synchronous barrier waits for / the next round's cohort
+  bool Sampling() const;
+  std::vector<std::string> BarrierSetLocked() const;
+  std::vector<std::string> SampleCohortLocked(const std::vector<std::string>& active);
+  std::set<std::string> cohort_;          // learners holding a task of the current round (sampling only)
+  std::mt19937_64 sample_rng_;
   void WatchdogLoop();
   void EvictLocked(const std::string& id, const char* why);
   // Dispatcher calls are queued while mu_ is held and issued after it is released, so a dispatcher

@@ -344,6 +344,7 @@ PYBIND11_MODULE(_core, m) {
       .def_readwrite("batch_size", &ControllerParams::batch_size).def_readwrite("epochs", &ControllerParams::epochs)
       .def_readwrite("percent_validation", &ControllerParams::percent_validation)
       .def_readwrite("participation_ratio", &ControllerParams::participation_ratio)
+      .def_readwrite("sampling_seed", &ControllerParams::sampling_seed)
       .def_readwrite("he_crypto_context_file", &ControllerParams::he_crypto_context_file)
       .def_readwrite("he_batch_size", &ControllerParams::he_batch_size)
       .def_readwrite("he_scaling_bits", &ControllerParams::he_scaling_bits)

@@ -75,6 +75,7 @@ class Learner(object):
                 model_dir, device, spec, certificate=cert, he_scheme_config_pb=he_scheme_config_pb,
                 endpoint="{}:{}".format(learner_server_entity.hostname, learner_server_entity.port))
         self._datasets = None
+        self._holdout_done = False
         self._he_scheme = None
         self._learner_controller_client = GRPCControllerClient(self._controller_server_entity, max_workers=1)
         self._credentials_dir = os.path.join(
@@ -117,6 +118,50 @@ class Learner(object):
                                                      default_class=train.__class__)
             self._datasets = (train, valid, test)
         return self._datasets
+
+    def _apply_validation_holdout(self, pct: float):
+        """``LearningTask.training_dataset_percentage_for_stratified_validation`` (``ValidationPercentage`` in the
+        YAML): a learner without a validation set of its own holds out that fraction of its training examples -
+        per class for classification labels - trains on the rest and reports the hold-out as its validation split.
+        The reference plumbs the field down to the task (``controller.cc:730-731``) and never reads it (quirk Q7).
+        Done once per learner; array datasets only (a ``DataLoader`` has no indexable examples to split)."""
+        pct = float(pct)
+        if 1.0 <= pct < 100.0:   # "10" is read as 10 %
+            pct /= 100.0
+        if self._holdout_done or not (0.0 < pct < 1.0):
+            return
+        self._holdout_done = True
+        import numpy as np
+        train, valid, test = self._load_model_datasets()
+        x, y = train.get_x(), train.get_y()
+        if valid.get_size() > 0 or not hasattr(x, "shape") or not hasattr(y, "shape") or len(x) != len(y) or len(y) < 2:
+            return
+        labels = np.asarray(y.detach().cpu() if hasattr(y, "detach") else y)
+        rng = np.random.default_rng(0)
+        is_cls = isinstance(train, ModelDatasetClassification) and labels.ndim == 1 and labels.dtype.kind in "iub"
+        groups = [np.flatnonzero(labels == c) for c in np.unique(labels)] if is_cls else [np.arange(len(labels))]
+        held = []
+        for g in groups:
+            k = int(round(float(pct) * len(g)))
+            if len(groups) == 1:
+                k = min(max(k, 1), len(g) - 1)
+            held.append(rng.permutation(g)[:min(k, len(g) - 1)] if len(g) > 1 else g[:0])
+        held = np.sort(np.concatenate(held))
+        if held.size == 0:
+            return
+        keep = np.setdiff1d(np.arange(len(labels)), held)
+
+        def part(idx):
+            xs, ys = x[idx], y[idx]
+            if is_cls:
+                cls, cnt = np.unique(labels[idx], return_counts=True)
+                return ModelDatasetClassification(x=xs, y=ys, size=len(idx),
+                                                  examples_per_class={int(c): int(n) for c, n in zip(cls, cnt)})
+            if isinstance(train, ModelDatasetRegression):
+                return ModelDatasetRegression(x=xs, y=ys, size=len(idx))
+            return ModelDataset(x=xs, y=ys, size=len(idx))
+        self._datasets = (part(keep), part(held), test)
+        MetisLogger.info("held out %d of %d training examples for validation", held.size, len(labels))
 
     def _load_model_datasets_size_specs_type_def(self):
         return [(d.get_size(), d.get_model_dataset_specifications(), type(d)) for d in self._load_model_datasets()]
@@ -206,6 +251,7 @@ class Learner(object):
 
     def model_train(self, learning_task_pb: metis_pb2.LearningTask, hyperparameters_pb: metis_pb2.Hyperparameters,
                     model_pb: model_pb2.Model, verbose=False, cancel_event=None):
+        self._apply_validation_holdout(learning_task_pb.training_dataset_percentage_for_stratified_validation)
         train, valid, test = self._load_model_datasets()
         if self._device_backend is not None:
             with self._model_lock:

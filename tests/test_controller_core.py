@@ -15,9 +15,10 @@ class Federation:
     """Controller + N fake learners that answer RunTask by adding ``delta`` to the model."""
 
     def __init__(self, rule="FedAvg", protocol=1, n=3, examples=None, stride=0, deadline=0.0, lineage=None,
-                 semi_lambda=0, auto=True):
+                 semi_lambda=0, auto=True, participation=1.0, sampling_seed=0):
         p = _core.ControllerParams()
         p.rule, p.protocol, p.stride_length = rule, protocol, stride
+        p.participation_ratio, p.sampling_seed = participation, sampling_seed
         p.batch_size, p.epochs = 10, 2
         p.task_deadline_secs = deadline
         p.semi_sync_lambda = semi_lambda
@@ -452,3 +453,75 @@ def test_secure_round_refuses_to_mix_references_and_ciphertext_bytes(tmp_path):
     with f.lock:
         assert not [c for c in f.commands if len(c["sources"]) == 2]   # no command ever mixed the two kinds
     f.core.shutdown()
+
+
+# ---- client sampling (GlobalModelConfig.ParticipationRatio; plumbed but never read in the reference, quirk Q7) ------
+def test_participation_ratio_draws_a_cohort_per_round():
+    f = Federation(n=4, auto=False, participation=0.5, sampling_seed=7)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(4)]
+    for lid, d in zip(ids, (1.0, 2.0, 4.0, 8.0)):
+        f.delta[lid] = d
+    f.core.wait_idle()
+    f.release()          # round 1: everybody who joined holds the initial task
+    f.wait_rounds(8)
+    f.mute.update(ids)
+    time.sleep(0.1)
+    f.core.wait_idle()
+    md = f.core.get_runtime_metadata_lineage(0)
+    assert sorted(md[0]["assigned_to_learner_id"]) == sorted(ids)
+    later = md[1:-1]                                                  # the last round was still open when muted
+    assert len(later) >= 6
+    cohorts = [tuple(sorted(m["assigned_to_learner_id"])) for m in later]
+    assert all(len(c) == 2 for c in cohorts), cohorts                 # ceil(0.5 * 4) learners per round
+    assert all(sorted(m["completed_by_learner_id"]) == sorted(m["assigned_to_learner_id"]) for m in later)
+    assert all(m["model_aggregation_block_size"] == [2.0] for m in later)   # only the cohort is averaged
+    assert len(set(cohorts)) > 1                                      # not the same pair every round
+    # evaluation follows the cohort that trains next
+    assert all(len(e[0]) == 2 for e in f.eval_log[1:])
+    # every round adds the mean of its cohort's deltas (equal example counts): the increments identify the cohort
+    lineage = f.core.get_community_model_lineage(0)
+    vals = [float(model_arrays(_core.parse_federated_model(b)[2])[0][0]) for b in lineage]
+    delta_of = dict(zip(ids, (1.0, 2.0, 4.0, 8.0)))
+    its = [_core.parse_federated_model(b)[1] for b in lineage]
+    by_it = {m["global_iteration"]: m for m in md}
+    for (a, b, it) in zip(vals, vals[1:], its[1:]):
+        cohort = by_it[it]["completed_by_learner_id"]
+        assert abs((b - a) - sum(delta_of[c] for c in cohort) / len(cohort)) < 1e-4
+    f.core.shutdown()
+
+
+def test_round_whose_whole_cohort_leaves_is_closed_and_a_new_cohort_is_drawn():
+    f = Federation(n=3, auto=False, participation=0.34, sampling_seed=3)   # cohorts of ceil(0.34 * 3) = 2 ... of 1 below
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(3)]
+    f.core.wait_idle()
+    f.release()
+    f.wait_rounds(1)
+    f.auto = False       # tasks of the next round stay unanswered
+    time.sleep(0.2)
+    f.core.wait_idle()
+    md = f.core.get_runtime_metadata_lineage(0)
+    open_round = md[-1]
+    cohort = list(open_round["assigned_to_learner_id"])
+    assert 1 <= len(cohort) <= 2 and not open_round["completed_by_learner_id"]
+    it = f.core.global_iteration()
+    for lid in cohort:
+        assert f.core.evict_learner(lid, "test: cohort member gone")
+    t0 = time.time()
+    while f.core.global_iteration() == it and time.time() - t0 < 10:
+        time.sleep(0.01)
+    assert f.core.global_iteration() == it + 1           # closed without contributions, next cohort drawn
+    f.core.wait_idle()
+    md = f.core.get_runtime_metadata_lineage(0)
+    survivors = set(ids) - set(cohort)
+    assert md[-1]["assigned_to_learner_id"] and set(md[-1]["assigned_to_learner_id"]) <= survivors
+    assert f.core.aggregation_failures() == 0
+    f.core.shutdown()
+
+
+def test_participation_ratio_is_validated():
+    p = _core.ControllerParams()
+    p.rule, p.protocol, p.batch_size, p.epochs, p.participation_ratio = "FedAvg", 1, 10, 1, 1.5
+    with pytest.raises(Exception):
+        _core.Controller(p, lambda *a: None, lambda *a: None)

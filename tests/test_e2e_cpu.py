@@ -242,3 +242,63 @@ def test_ssh_launcher_over_a_local_exec_transport(tmp_path, monkeypatch):
     shipped = [name for name, _ in calls["put"]]
     assert any(name.endswith(".tar.gz") for name in shipped) and len(shipped) >= 3   # model archive + 2 recipes
     assert calls["hosts"] == {("localhost", "root")}
+
+
+def test_participation_ratio_through_the_driver(tmp_path):
+    """`GlobalModelConfig.ParticipationRatio: 0.5` with two learners: after the first round (every joiner holds the
+    initial task) each round trains and aggregates ONE sampled learner (the reference parses the field and never reads
+    it, `fedenv_parser.py` / `metis.proto:307`, quirk Q7)."""
+    d = _env(**{"GlobalModelConfig.ParticipationRatio": 0.5, "TerminationSignals.FederationRounds": 5})
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(96, 1), None, _recipe(32, 3),
+                      working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    stats = s.run(request_every_secs=0.3)
+    md = stats["federation_runtime_metadata"]["metadata"]
+    closed = [m for m in md[1:] if m.get("model_aggregation_block_size")]
+    assert len(closed) >= 3
+    assert all(len(m["assigned_to_learner_id"]) == 1 and m["model_aggregation_block_size"] == [1.0] for m in closed)
+    assert stats["community_model_results"]["community_evaluation"]
+
+
+def test_validation_percentage_holds_out_a_stratified_split(tmp_path):
+    """`LocalModelConfig.ValidationPercentage: 0.25` with learners that bring no validation set: each learner trains on
+    75 % of its examples and reports the held-out 25 % (per class) as its validation evaluation (the reference sends the
+    fraction with every task, `controller.cc:730-731`, and no learner reads it - quirk Q7)."""
+    d = _env(**{"LocalModelConfig.ValidationPercentage": 0.25, "TerminationSignals.FederationRounds": 2})
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(96, 1), None, _recipe(32, 3),
+                      working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    stats = s.run(request_every_secs=0.3)
+    ev = [e for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
+    assert ev
+    per_learner = list(ev[-1]["evaluations"].values())
+    assert all(p["validation_evaluation"]["metric_values"].get("loss") for p in per_learner)
+    learners = [svc.learner for name, svc in s._inprocess if name.startswith("learner")]
+    assert len(learners) == 2
+    for l in learners:
+        train, valid, _ = l._datasets
+        assert train.get_size() + valid.get_size() == 96 and 20 <= valid.get_size() <= 28
+        assert set(valid.examples_per_class) <= set(train.examples_per_class)
+
+
+def test_holdout_split_unit():
+    from metisfl_b200.learner.learner import Learner
+    from metisfl_b200.models.model_dataset import ModelDatasetClassification
+    rng = np.random.default_rng(0)
+    y = np.repeat(np.arange(4), [40, 20, 12, 8])
+    x = rng.normal(size=(80, 3)).astype(np.float32)
+    full = ModelDatasetClassification(x=x, y=y, size=80, examples_per_class={0: 40, 1: 20, 2: 12, 3: 8})
+    empty = ModelDatasetClassification()
+    l = Learner.__new__(Learner)
+    l._datasets, l._holdout_done = (full, empty, empty), False
+    l._apply_validation_holdout(25)          # percent form
+    train, valid, _ = l._datasets
+    assert valid.examples_per_class == {0: 10, 1: 5, 2: 3, 3: 2} and train.get_size() == 60
+    assert train.examples_per_class == {0: 30, 1: 15, 2: 9, 3: 6}
+    both = np.concatenate([train.get_x(), valid.get_x()])
+    assert sorted(map(tuple, both.tolist())) == sorted(map(tuple, x.tolist()))   # a partition of the examples
+    l._apply_validation_holdout(0.5)         # once per learner
+    assert l._datasets[0] is train
+    # a learner that brought its own validation set keeps it
+    l2 = Learner.__new__(Learner)
+    l2._datasets, l2._holdout_done = (full, full, empty), False
+    l2._apply_validation_holdout(0.25)
+    assert l2._datasets[0] is full
