@@ -42,3 +42,28 @@ def test_docs_index_points_at_existing_pages():
     for p in pages:
         path = os.path.normpath(os.path.join(ROOT, "docs", p))
         assert os.path.exists(path), p
+
+
+def test_shipped_ckks_artefacts_encrypt_and_aggregate():
+    """`resources/fheparams/cryptoparams/` (reference: `metisfl/resources/fheparams/cryptoparams/`): context + public
+    key + eval-mult key and no private key - enough to encrypt and for the controller's weighted average."""
+    import os
+
+    import numpy as np
+
+    import metisfl_b200
+    from metisfl_b200 import _core
+    from metisfl_b200.encryption import fhe
+    d = os.path.join(os.path.dirname(metisfl_b200.__file__), "resources", "fheparams", "cryptoparams")
+    assert sorted(os.listdir(d)) == ["cryptocontext.txt", "key-eval-mult.txt", "key-public.txt"]
+    learner = fhe.CKKS(backend="host")
+    learner.load_crypto_context_from_file(os.path.join(d, "cryptocontext.txt"))
+    learner.load_public_key_from_file(os.path.join(d, "key-public.txt"))
+    assert learner.batch_size == 4096 and learner.scaling_factor_bits == 52
+    ct = learner.encrypt(np.linspace(-1, 1, 100))
+    h = _core.ckks_header(ct)
+    assert h["n_ct"] == 1 and h["n_values"] == 100 and len(ct) > 786_000
+    controller = fhe.CKKS(backend="host")
+    controller.load_crypto_context_from_file(os.path.join(d, "cryptocontext.txt"))
+    avg = controller.compute_weighted_average([ct, ct], [0.5, 0.5])
+    assert _core.ckks_header(avg)["n_values"] == 100
