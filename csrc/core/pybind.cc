@@ -213,13 +213,18 @@ PYBIND11_MODULE(_core, m) {
     return out;
   });
   m.def("build_model", [](const py::list& vars) {
+    // values are taken through the buffer protocol (bytes, numpy arrays, memoryviews): the tensor bytes are copied
+    // exactly once, from the caller's buffer into the serialized model
     std::string out;
-    std::deque<std::string> keep;  // stable addresses for the string_views below
+    std::deque<std::string> names;
+    std::vector<py::buffer_info> bufs;
+    std::vector<wire::VariableView> views;
+    size_t total = 0;
     for (auto item : vars) {
       py::dict d = py::cast<py::dict>(item);
       wire::VariableView v;
-      keep.push_back(py::cast<std::string>(d["name"]));
-      v.name = keep.back();
+      names.push_back(py::cast<std::string>(d["name"]));
+      v.name = names.back();
       v.trainable = py::cast<bool>(d["trainable"]);
       v.ciphertext = d.contains("ciphertext") && py::cast<bool>(d["ciphertext"]);
       v.t.length = py::cast<uint32_t>(d["length"]);
@@ -227,15 +232,35 @@ PYBIND11_MODULE(_core, m) {
       v.t.dtype = py::cast<int>(d["dtype"]);
       v.t.byte_order = d.contains("byte_order") ? py::cast<int>(d["byte_order"]) : 2;
       v.t.fortran = d.contains("fortran_order") && py::cast<bool>(d["fortran_order"]);
-      keep.push_back(std::string(py::cast<py::bytes>(d["value"])));
-      std::string_view val(keep.back());
+      py::buffer_info info = py::cast<py::buffer>(d["value"]).request();
+      if (info.ndim > 1) throw std::runtime_error("build_model: tensor values must be flat, contiguous buffers");
+      if (info.ndim == 1 && info.shape[0] > 1 && info.strides[0] != info.itemsize)
+        throw std::runtime_error("build_model: tensor values must be contiguous");
+      total += (size_t)info.size * (size_t)info.itemsize + v.name.size() + 64;
+      bufs.push_back(std::move(info));
       if (d.contains("device_slot")) {
         py::tuple t = py::cast<py::tuple>(d["device_slot"]);
         v.t.slot = {true, py::cast<uint32_t>(t[0]), py::cast<uint32_t>(t[1]), py::cast<uint64_t>(t[2]), py::cast<uint64_t>(t[3])};
       }
-      wire::AppendVariable(out, v, &val);
+      views.push_back(std::move(v));
+    }
+    out.reserve(total);
+    for (size_t i = 0; i < views.size(); ++i) {
+      std::string_view val(static_cast<const char*>(bufs[i].ptr), (size_t)bufs[i].size * (size_t)bufs[i].itemsize);
+      wire::AppendVariable(out, views[i], &val);
     }
     return py::bytes(out);
+  });
+  m.def("model_payload_bytes", [](const py::buffer& b) -> py::object {
+    // tensor bytes inside a serialized Model (0 for a control-only model of device-slot references); None if malformed
+    py::buffer_info info = b.request();
+    if (info.ndim > 1 || (info.ndim == 1 && info.shape[0] > 1 && info.strides[0] != info.itemsize)) return py::none();
+    std::string_view sv(static_cast<const char*>(info.ptr), (size_t)info.size * (size_t)info.itemsize);
+    std::vector<wire::VariableView> vars;
+    if (!wire::ParseModel(sv, vars)) return py::none();
+    uint64_t n = 0;
+    for (auto& v : vars) n += v.t.value.size();
+    return py::int_(n);
   });
   m.def("build_federated_model", [](uint32_t contributors, uint32_t iteration, const py::bytes& model) {
     return py::bytes(wire::BuildFederatedModel(contributors, iteration, std::string(model)));
@@ -379,14 +404,19 @@ PYBIND11_MODULE(_core, m) {
         py::gil_scoped_release rel;
         Raise(c.RemoveLearner(id, tok));
       })
-      .def("learner_completed_task", [](Controller& c, const std::string& id, const std::string& tok, const py::bytes& model,
+      .def("learner_completed_task", [](Controller& c, const std::string& id, const std::string& tok, const py::buffer& model,
                                         uint32_t global_iteration, float completed_epochs, uint32_t completed_batches,
                                         uint32_t batch_size, float ms_per_epoch, float ms_per_batch, const py::bytes& meta) {
         TaskMeta tm;
         tm.global_iteration = global_iteration; tm.completed_epochs = completed_epochs; tm.completed_batches = completed_batches;
         tm.batch_size = batch_size; tm.ms_per_epoch = ms_per_epoch; tm.ms_per_batch = ms_per_batch;
         tm.serialized = std::string(meta);
-        std::string ms(model);
+        // any contiguous byte buffer (bytes, or the memoryview slice of the request it arrived in): one copy, into the
+        // string the model store keeps
+        py::buffer_info mi = model.request();
+        if (mi.ndim > 1 || (mi.ndim == 1 && mi.shape[0] > 1 && mi.strides[0] != mi.itemsize))
+          throw std::runtime_error("learner_completed_task: the model must be a contiguous byte buffer");
+        std::string ms(static_cast<const char*>(mi.ptr), (size_t)mi.size * (size_t)mi.itemsize);
         py::gil_scoped_release rel;
         Raise(c.LearnerCompletedTask(id, tok, std::move(ms), std::move(tm)));
       }, py::arg("learner_id"), py::arg("auth_token"), py::arg("model"), py::arg("global_iteration") = 0,

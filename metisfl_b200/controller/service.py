@@ -20,6 +20,7 @@ from google.protobuf.timestamp_pb2 import Timestamp
 from metisfl_b200 import _core
 from metisfl_b200.proto import (controller_pb2, controller_pb2_grpc, learner_pb2, learner_pb2_grpc, metis_pb2,
                                 model_pb2, service_common_pb2)
+from metisfl_b200.proto import envelope
 from metisfl_b200.utils.grpc_services import GRPCChannelMaxMsgLength, GRPCServerMaxMsgLength
 from metisfl_b200.utils.metis_logger import MetisLogger
 
@@ -38,6 +39,11 @@ def _ts(seconds: float) -> Timestamp:
     if seconds:
         t.FromNanoseconds(int(seconds * 1e9))
     return t
+
+
+def _tensor_payload_bytes(model_bytes) -> int:
+    """Tensor bytes inside a serialized ``Model`` (a control-only model with device-slot references has none)."""
+    return int(_core.model_payload_bytes(model_bytes) or 0)
 
 
 def _ack(status=True, message="") -> service_common_pb2.Ack:
@@ -269,16 +275,23 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             return self._channels[learner_id][1]
 
     def _send_run_tasks(self, items, federated_model_bytes, federated_model_ref_bytes=None):
-        fm = model_pb2.FederatedModel.FromString(federated_model_bytes)
-        # learners on the fabric get the control-only twin (device-slot references, a few KB) when there is one
-        fm_ref = model_pb2.FederatedModel.FromString(federated_model_ref_bytes) if federated_model_ref_bytes else None
+        # The community model arrives from the core already serialized: the request is assembled around those bytes
+        # (proto/envelope.py) instead of parse -> copy into a RunTaskRequest -> serialize per learner.  Learners with
+        # the same task template share one request.
+        # Learners on the fabric get the control-only twin (device-slot references, a few KB) when there is one.
+        built = {}
         for (lid, host, port, cert, iteration, updates, pct_valid) in items:
-            req = learner_pb2.RunTaskRequest(
-                federated_model=fm_ref if (fm_ref is not None and lid in self._fabric_of) else fm,
-                task=metis_pb2.LearningTask(global_iteration=iteration, num_local_updates=updates,
-                                            training_dataset_percentage_for_stratified_validation=pct_valid,
-                                            metrics=self._evaluation_metrics),
-                hyperparameters=self._hyper)
+            ref = bool(federated_model_ref_bytes) and lid in self._fabric_of
+            key = (ref, iteration, updates, pct_valid)
+            req = built.get(key)
+            if req is None:
+                rest = learner_pb2.RunTaskRequest(
+                    task=metis_pb2.LearningTask(global_iteration=iteration, num_local_updates=updates,
+                                                training_dataset_percentage_for_stratified_validation=pct_valid,
+                                                metrics=self._evaluation_metrics),
+                    hyperparameters=self._hyper)
+                req = built[key] = envelope.embed(learner_pb2.RunTaskRequest, "federated_model",
+                                                  federated_model_ref_bytes if ref else federated_model_bytes, rest)
             self._rpc_pool.submit(self._do_run_task, lid, host, port, cert, req)
 
     def _do_run_task(self, lid, host, port, cert, req):
@@ -288,14 +301,11 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             self.core.task_failed(lid, f"RunTask: {e}")
 
     def _send_evaluation_tasks(self, learners, model_bytes, batch_size, eval_index, iteration, model_ref_bytes=None):
-        model = model_pb2.Model.FromString(model_bytes)
         E = learner_pb2.EvaluateModelRequest
-        req = E(model=model, batch_size=batch_size, evaluation_dataset=[E.TRAINING, E.VALIDATION, E.TEST],
-                metrics=self._evaluation_metrics)
-        req_ref = None
-        if model_ref_bytes:
-            req_ref = E(model=model_pb2.Model.FromString(model_ref_bytes), batch_size=batch_size,
-                        evaluation_dataset=[E.TRAINING, E.VALIDATION, E.TEST], metrics=self._evaluation_metrics)
+        rest = E(batch_size=batch_size, evaluation_dataset=[E.TRAINING, E.VALIDATION, E.TEST],
+                 metrics=self._evaluation_metrics).SerializeToString()
+        req = envelope.embed(E, "model", model_bytes, rest)   # one request, shared by every learner
+        req_ref = envelope.embed(E, "model", model_ref_bytes, rest) if model_ref_bytes else None
         for (lid, host, port, cert) in learners:
             r = req_ref if (req_ref is not None and lid in self._fabric_of) else req
             self._rpc_pool.submit(self._do_evaluate, lid, host, port, cert, r, eval_index)
@@ -457,16 +467,34 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
             if member is not None and member[0] in self._fabrics:
                 self._fabrics[member[0]]["dissolving"] = True
 
+    # the request is handed over as the bytes that arrived: the model record goes to the core as it is (the core has
+    # its own wire parser), only the few hundred bytes around it are parsed here
+    RAW_REQUEST_METHODS = ("MarkTaskCompleted",)
+
     def MarkTaskCompleted(self, request, context):
-        md = request.task.execution_metadata
-        self.controller_rx_model_bytes += sum(len(v.plaintext_tensor.tensor_spec.value) +
-                                              len(v.ciphertext_tensor.tensor_spec.value)
-                                              for v in request.task.model.variables)
+        R, T = controller_pb2.MarkTaskCompletedRequest, metis_pb2.CompletedLearningTask
+        try:
+            if isinstance(request, (bytes, bytearray, memoryview)):
+                outer = envelope.split(request)
+                task = envelope.merged_bytes(outer, R, "task")
+                inner = envelope.split(task) if task is not None else {}
+                model = envelope.merged_bytes(inner, T, "model")   # a view into the request: copied once, by the core
+                model = model if model is not None else b""
+                meta = envelope.merged_bytes(inner, T, "execution_metadata")
+                md = metis_pb2.TaskExecutionMetadata.FromString(bytes(meta)) if meta is not None \
+                    else metis_pb2.TaskExecutionMetadata()
+                learner_id, auth_token = (bytes(v).decode("utf-8") if v is not None else "" for v in (
+                    envelope.last_bytes(outer, R, "learner_id"), envelope.last_bytes(outer, R, "auth_token")))
+            else:   # called with a parsed message (in-process callers, older stubs)
+                learner_id, auth_token, md = request.learner_id, request.auth_token, request.task.execution_metadata
+                model = request.task.model.SerializeToString()
+        except Exception as e:   # ValueError from the splitter, DecodeError from protobuf
+            context.abort(grpc.StatusCode.INVALID_ARGUMENT, "malformed MarkTaskCompletedRequest: {}".format(e))
+        self.controller_rx_model_bytes += _tensor_payload_bytes(model)
         try:
             self.core.learner_completed_task(
-                request.learner_id, request.auth_token, request.task.model.SerializeToString(),
-                md.global_iteration, md.completed_epochs, md.completed_batches, md.batch_size,
-                md.processing_ms_per_epoch, md.processing_ms_per_batch, md.SerializeToString())
+                learner_id, auth_token, model, md.global_iteration, md.completed_epochs, md.completed_batches,
+                md.batch_size, md.processing_ms_per_epoch, md.processing_ms_per_batch, md.SerializeToString())
         except _core.ControllerError as e:
             self._abort(context, e)
         return controller_pb2.MarkTaskCompletedResponse(ack=_ack())

@@ -43,7 +43,8 @@ class EchoLearner(Learner):
             batch_size=batch, processing_ms_per_epoch=self.sleep_secs * 1e3,
             processing_ms_per_batch=self.sleep_secs * 1e3 / steps)
         self.tasks_echoed += 1
-        return metis_pb2.CompletedLearningTask(model=model_pb, execution_metadata=meta)
+        from metisfl_b200.proto.envelope import WireCompletedTask
+        return WireCompletedTask(model_pb.SerializeToString(), meta)
 
     def model_evaluate(self, model_pb, batch_size, evaluation_datasets_pb, metrics_pb, verbose=False):
         return metis_pb2.ModelEvaluations()

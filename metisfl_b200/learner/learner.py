@@ -191,6 +191,7 @@ class Learner(object):
                 raise RuntimeError("Unknown neural engine '{}' (pytorch | keras | echo).".format(engine))
             from metisfl_b200.models.torch_model_ops import TorchModelOps
             self._model_ops = TorchModelOps(self._model_dir, he_scheme=self._he_scheme_factory(), device=self._device)
+            self._model_ops.wire_tasks = True   # completed tasks leave as bytes built straight from the tensors
         return self._model_ops
 
     # -- federation membership --------------------------------------------------------------------

@@ -55,6 +55,13 @@ class ModelProtoFactory:
                 model_pb=model_pb, task_execution_metadata_pb=self.construct_task_execution_metadata_pb(),
                 aux_metadata=aux_metadata)
 
+        def construct_completed_learning_task_wire(self, aux_metadata="", he_scheme=None):
+            """Same task, with the model serialized straight from the tensors (``proto/envelope.py``)."""
+            from metisfl_b200.proto.envelope import WireCompletedTask
+            model_bytes = ModelProtoMessages.construct_model_bytes_from_np(
+                self.weights_values, self.weights_names, self.weights_trainable, he_scheme=he_scheme)
+            return WireCompletedTask(model_bytes, self.construct_task_execution_metadata_pb(), aux_metadata)
+
     class ModelEvaluationProtoMessage(object):
 
         def __init__(self, metric_values):

@@ -320,7 +320,9 @@ class TorchModelOps(ModelOps):
                     if stats is train_stats and k == "loss":
                         continue
                     stats.setdefault(k, []).append(v)
-        names, trainables, values = self.get_model_weights()
+        # a task that is only going to be sent (the Learner sets ``wire_tasks``) is serialized straight out of the arena
+        wire = getattr(self, "wire_tasks", False)
+        names, trainables, values = ([], [], []) if (wire and self._he_scheme is None) else self.get_model_weights()
         ms_per_batch = total_ms / max(1, steps_done)
         msg = ModelProtoFactory.CompletedLearningTaskProtoMessage(
             weights_values=values, weights_trainable=trainables, weights_names=names,
@@ -331,6 +333,12 @@ class TorchModelOps(ModelOps):
         if verbose:
             MetisLogger.info("task done: %d steps, %.2f ms/batch, loss %s", steps_done, ms_per_batch,
                              train_stats.get("loss", [None])[-1])
+        if wire and self._he_scheme is None:
+            from metisfl_b200.ops import pack
+            from metisfl_b200.proto.envelope import WireCompletedTask
+            return WireCompletedTask(pack.arena_to_model_bytes(self.arena), msg.construct_task_execution_metadata_pb())
+        if wire:
+            return msg.construct_completed_learning_task_wire(he_scheme=self._he_scheme)
         return msg.construct_completed_learning_task_pb(he_scheme=self._he_scheme)
 
     def _eager_step(self, x, y):
@@ -356,6 +364,8 @@ class TorchModelOps(ModelOps):
             weights_values=values, weights_trainable=trainables, weights_names=names, train_stats=stats,
             completed_epochs=epochs, global_iteration=learning_task_pb.global_iteration, completes_batches=steps,
             batch_size=batch_size, processing_ms_per_epoch=total_ms / epochs, processing_ms_per_batch=total_ms / steps)
+        if getattr(self, "wire_tasks", False):
+            return msg.construct_completed_learning_task_wire(he_scheme=self._he_scheme)
         return msg.construct_completed_learning_task_pb(he_scheme=self._he_scheme)
 
     # -- evaluation / inference -----------------------------------------------------------------

@@ -114,3 +114,25 @@ def arena_to_model_pb(arena) -> model_pb2.Model:
             chunk = np.ascontiguousarray(chunk.reshape(k_, r_, s_, c_, seg.dtype.itemsize).transpose(0, 3, 1, 2, 4))
         spec.value = chunk.tobytes()
     return m
+
+
+def arena_to_model_bytes(arena) -> bytes:
+    """``arena_to_model_pb(arena).SerializeToString()`` without the message objects: one device->host copy of the arena,
+    then the core's wire writer copies each variable once, straight out of that host buffer (``_core.build_model``)."""
+    from metisfl_b200 import _core
+    raw = arena.state.detach().to("cpu").numpy()
+    D = model_pb2.DType
+    variables = []
+    for info in arena.layout.variables:
+        seg = arena.layout.segments[info.segment]
+        lo = seg.byte_offset + info.elem_offset * seg.dtype.itemsize
+        chunk = raw[lo:lo + info.numel * seg.dtype.itemsize]
+        if info.channels_last:  # stored [K,R,S,C] -> wire order [K,C,R,S]
+            k_, c_, r_, s_ = info.shape
+            chunk = np.ascontiguousarray(
+                chunk.reshape(k_, r_, s_, c_, seg.dtype.itemsize).transpose(0, 3, 1, 2, 4)).reshape(-1)
+        variables.append({"name": info.name, "trainable": bool(info.trainable), "length": int(info.numel),
+                          "dimensions": [int(d) for d in info.shape], "dtype": int(dtypes.torch_to_wire(seg.dtype)),
+                          "byte_order": int(D.NA if seg.dtype.itemsize == 1 else D.LITTLE_ENDIAN_ORDER),
+                          "value": chunk})
+    return _core.build_model(variables)

@@ -8,6 +8,15 @@ import grpc
 from metisfl_b200.proto import schema
 
 
+def _serializer(message_cls):
+    """Requests assembled at the byte level (``proto/envelope.py``) go out as they are."""
+    def serialize(message):
+        if isinstance(message, (bytes, bytearray)):
+            return bytes(message)
+        return message.SerializeToString()
+    return serialize
+
+
 def make_service(file_name: str, service_name: str):
     sd = schema.file_descriptor(file_name).services_by_name[service_name]
     methods = [(m.name, schema.message_class(m.input_type.name),
@@ -19,7 +28,7 @@ def make_service(file_name: str, service_name: str):
             for name, req, resp in methods:
                 setattr(self, name, channel.unary_unary(
                     f"/{full}/{name}",
-                    request_serializer=req.SerializeToString,
+                    request_serializer=_serializer(req),
                     response_deserializer=resp.FromString))
 
     def _unimplemented(name):
@@ -34,10 +43,13 @@ def make_service(file_name: str, service_name: str):
                     {name: _unimplemented(name) for name, _, _ in methods})
 
     def add_to_server(servicer, server):
+        # methods listed in ``servicer.RAW_REQUEST_METHODS`` get the request as the bytes that arrived (they take the
+        # model record out themselves instead of paying for a full parse + re-serialization)
+        raw = set(getattr(servicer, "RAW_REQUEST_METHODS", ()))
         handlers = {
             name: grpc.unary_unary_rpc_method_handler(
                 getattr(servicer, name),
-                request_deserializer=req.FromString,
+                request_deserializer=None if name in raw else req.FromString,
                 response_serializer=resp.SerializeToString)
             for name, req, resp in methods
         }

@@ -74,8 +74,9 @@ class GRPCControllerClient(GRPCServerClient):
 
     def mark_task_completed(self, learner_id, auth_token, completed_task_pb, request_retries=1,
                             request_timeout=None, block=True):
-        req = proto_factory.ControllerServiceProtoMessages.construct_mark_task_completed_request_pb(
-            learner_id=learner_id, auth_token=auth_token, completed_learning_task_pb=completed_task_pb)
+        # assembled around the serialized task (proto/envelope.py): no copy of the model into a request object
+        from metisfl_b200.proto import envelope
+        req = envelope.mark_task_completed_request(learner_id, auth_token, completed_task_pb)
         return self._call("MarkTaskCompleted", req, lambda r: r.ack.status, request_retries, request_timeout, block)
 
     def get_community_model_evaluation_lineage(self, num_backtracks, request_retries=1, request_timeout=None,

@@ -465,6 +465,41 @@ class ModelProtoMessages(object):
         return model_pb2.Model(variables=variables)
 
     @classmethod
+    def construct_model_bytes_from_np(cls, weights_values, weights_names, weights_trainable, he_scheme=None) -> bytes:
+        """The serialized ``Model`` of ``construct_model_pb_from_np`` without the protobuf objects in between: the core's
+        wire writer copies every tensor once, straight out of the array's buffer (``_core.build_model``).  The reference
+        builds ``TensorSpec`` -> ``PlaintextTensor`` -> ``Variable`` -> ``Model`` and serializes (:419-465, :543-564): a
+        copy of every tensor per level."""
+        from metisfl_b200 import _core
+        D = model_pb2.DType
+        variables = []
+        for name, trainable, value in zip(weights_names, weights_trainable, weights_values):
+            if torch is not None and isinstance(value, torch.Tensor):
+                t = value.detach().contiguous().cpu()
+                code, dims, length, fortran = dtypes.torch_to_wire(t.dtype), list(t.shape), t.numel(), False
+                order = D.NA if t.element_size() == 1 else (D.LITTLE_ENDIAN_ORDER if sys.byteorder == "little"
+                                                            else D.BIG_ENDIAN_ORDER)
+                raw = t.reshape(-1).view(torch.uint8).numpy() if t.numel() else b""
+                plain = t
+            else:
+                arr = np.asarray(value)
+                code, dims, length = dtypes.numpy_to_wire(arr.dtype), list(arr.shape), arr.size
+                fortran = bool(arr.flags.f_contiguous and not arr.flags.c_contiguous)
+                order = cls.TensorSpecProto._byte_order(arr.dtype)
+                flat = np.ascontiguousarray(arr.reshape(-1, order="F" if fortran else "C"))
+                raw = flat.view(np.uint8) if flat.size else b""
+                plain = arr
+            entry = {"name": name, "trainable": bool(trainable), "length": int(length), "dimensions": dims,
+                     "dtype": int(code), "byte_order": int(order), "fortran_order": fortran, "value": raw}
+            if he_scheme is not None:   # the ciphertext replaces the payload; shape / dtype describe the plaintext
+                flat64 = plain.detach().float().cpu().numpy().ravel() if (torch is not None and isinstance(
+                    plain, torch.Tensor)) else np.asarray(plain).ravel()
+                entry["value"] = he_scheme.encrypt(flat64.astype(np.float64))
+                entry["ciphertext"] = True
+            variables.append(entry)
+        return _core.build_model(variables)
+
+    @classmethod
     def construct_federated_model_pb(cls, num_contributors, model_pb):
         assert isinstance(model_pb, model_pb2.Model)
         return model_pb2.FederatedModel(num_contributors=num_contributors, model=model_pb)

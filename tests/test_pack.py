@@ -109,3 +109,19 @@ def test_unpack_refuses_payloads_that_do_not_match_their_declaration():
     wrong_len.variables[0].plaintext_tensor.tensor_spec.length += 1
     with pytest.raises(ValueError):
         unpack_model_into_arena(wrong_len, arena)
+
+
+def test_arena_to_model_bytes_equals_the_message_path():
+    """Serialized straight out of the arena == the message built variable by variable (channels-last filters included)."""
+    import torch
+
+    from metisfl_b200.ops import pack
+    from metisfl_b200.parallel.arena import ModelArena
+    from metisfl_b200.proto import model_pb2
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.Flatten(),
+                              torch.nn.Linear(8, 4)).to(memory_format=torch.channels_last)
+    arena = ModelArena(net, torch.device("cpu"), torch.float32)
+    want = pack.arena_to_model_pb(arena)
+    got = model_pb2.Model.FromString(pack.arena_to_model_bytes(arena))
+    assert got == want and len(got.variables) == len(list(net.state_dict()))
