@@ -51,7 +51,7 @@ case "${1:-memcheck}" in
     LD_PRELOAD="$(g++ -print-file-name=libasan.so):$(g++ -print-file-name=libubsan.so)" \
       ASAN_OPTIONS="detect_leaks=0:halt_on_error=1" UBSAN_OPTIONS="print_stacktrace=1" \
       python -m pytest tests/test_wire_fuzz.py tests/test_proto_codec.py tests/test_aggregation_rules.py tests/test_ckks_host.py \
-        tests/test_controller_core.py tests/test_policies_and_stores.py -x -q -p no:cacheprovider
+        tests/test_controller_core.py tests/test_policies_and_stores.py tests/test_envelope.py -x -q -p no:cacheprovider
     ;;
   *) echo "usage: $0 memcheck|racecheck|synccheck|initcheck|tsan|asan"; exit 2;;
 esac
