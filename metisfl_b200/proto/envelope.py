@@ -17,6 +17,7 @@ from __future__ import annotations
 from typing import Dict, List, Tuple
 
 _LEN = 2  # wire type of length-delimited records (strings, bytes, embedded messages)
+MAX_TOP_LEVEL_RECORDS = 4096
 
 
 def _varint(n: int) -> bytes:
@@ -67,7 +68,11 @@ def split(buf) -> Dict[int, List[Tuple[int, object]]]:
                 return val, i
             shift += 7
 
+    records = 0
     while i < n:
+        records += 1
+        if records > MAX_TOP_LEVEL_RECORDS:   # the requests taken apart here have a handful; this walk is Python
+            raise ValueError("too many top-level records")
         key, i = varint(i)
         field, wt = key >> 3, key & 7
         if field == 0:

@@ -157,3 +157,9 @@ def test_controller_takes_mark_task_completed_as_raw_bytes_and_rejects_garbage()
             assert e.value.code() == grpc.StatusCode.INVALID_ARGUMENT
     finally:
         ctrl.stop()
+
+
+def test_split_bounds_the_number_of_records():
+    with pytest.raises(ValueError):
+        envelope.split(b"\x08\x01" * (envelope.MAX_TOP_LEVEL_RECORDS + 1))
+    assert len(envelope.split(b"\x08\x01" * 100)[1]) == 100
