@@ -13,7 +13,6 @@ the controller, ``driver_session.py:334-342``) and is unpacked on the device (K1
 """
 from __future__ import annotations
 
-import math
 import threading
 import time
 from dataclasses import dataclass
