@@ -546,3 +546,37 @@ def test_secure_backend_commands_and_the_two_encrypted_byte_forms(tmp_path):
             be.aggregate(bad)
     finally:
         be.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+@pytest.mark.skipif(not os.environ.get("METISFL_TEST_SECURE_FABRIC_GPU"),
+                    reason="CUDA tier of the secure fabric: written after this round's GPU budget was spent; set "
+                           "METISFL_TEST_SECURE_FABRIC_GPU=1 to run it (first thing to validate on the next GPU call)")
+def test_secure_aggregation_on_the_fabric_gpu(tmp_path, monkeypatch):
+    """The secure round through DriverSession with K6 / K7 / K8 on one GPU: encrypted snapshot, finite loss, and the
+    decrypted community model equal to the learner's plaintext model (one learner: weight 1)."""
+    d = _env(**{"GlobalModelConfig.AggregationRule.Name": "PWA", "TerminationSignals.FederationRounds": 3,
+                "TerminationSignals.ExecutionCutoffTimeMins": 3, "LocalModelConfig.OptimizerConfig.LearningRate": 0.0005})
+    fe = d["FederationEnvironment"]
+    fe["HomomorphicEncryption"] = {"Scheme": "CKKS", "BatchSize": 4096, "ScalingFactorBits": 52}
+    fe["Learners"] = fe["Learners"][:1]
+    fe["Learners"][0]["CudaDevices"] = [0]
+    fe["DeviceFabric"] = True
+    fe["ModelDType"] = "bf16"
+    snap = tmp_path / "snap_secgpu"
+    monkeypatch.setenv("METISFL_SNAPSHOT_DIR", str(snap))
+    torch.manual_seed(0)
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(128, 1), None, _recipe(64, 3),
+                      working_dir=str(tmp_path / "w_secgpu"), launcher="inprocess", banner=False,
+                      model_dtype=torch.bfloat16)
+    stats = s.run(request_every_secs=0.3)
+    c = _counters(stats)
+    assert c["fabric_learners"] == 1 and c["aggregation_failures"] == 0 and c["model_bytes_received"] == 0
+    loss = _last_loss(stats)
+    assert np.isfinite(loss) and loss < 5.0
+    variables = _snapshot_variables(str(snap))
+    assert len(variables) == 1 and variables[0].HasField("ciphertext_tensor")
+    spec = variables[0].ciphertext_tensor.tensor_spec
+    avg = np.asarray(s._he_scheme.decrypt(spec.value, spec.length))
+    assert np.isfinite(avg).all() and 0 < np.abs(avg).max() < 10.0
