@@ -431,7 +431,7 @@ ModelBytes Controller::ComputeCommunityModel(const std::vector<std::string>& sel
   // participants: the completing learner for per-contribution rules (Q2), otherwise every selected
   // learner that actually has a stored model (Q14)
   std::vector<std::string> parts;
-  if (single) parts.push_back(completing);
+  if (single) { if (!completing.empty()) parts.push_back(completing); }  // empty: a round closed without contributions
   else
     for (auto& id : selected)
       if (store_->GetLearnerLineageLength(id) > 0) parts.push_back(id);
