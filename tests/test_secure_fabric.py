@@ -26,8 +26,8 @@ def keys(tmp_path_factory):
     return SecureAggregator.generate_keys(d, 4096, 52)
 
 
-def _engine():
-    cfg = EngineConfig(learners_per_gpu=1, model_dtype=torch.float32, use_cuda_graph=False, direct_install=False)
+def _engine(dtype=torch.float32):
+    cfg = EngineConfig(learners_per_gpu=1, model_dtype=dtype, use_cuda_graph=False, direct_install=False)
     return FederationEngine(_BNNet, cfg, device="cpu")
 
 
@@ -67,3 +67,19 @@ def test_reduce_checks_its_arguments(keys):
         sec.reduce([0.5, 0.5])            # one weight per fabric rank
     with pytest.raises(RuntimeError):
         sec.reduce([1.0])                 # nothing was published yet
+
+
+def test_bfloat16_arena_round_trips_through_the_ciphertext(keys):
+    """The GPU learners keep their models in bf16: the encoder takes float64, the decrypted average is cast back."""
+    eng = _engine(torch.bfloat16)
+    sec = FabricSecure(eng, keys["crypto_context_file"], keys["public_key_file"], keys["private_key_file"])
+    g = torch.Generator().manual_seed(2)
+    for i in sec.segments:
+        v = eng.slot_views[0][i]
+        v.copy_(torch.randn(v.shape, generator=g).to(v.dtype))
+    sec.encrypt_slot(0)
+    sec.reduce([1.0])
+    sec.decrypt_install()
+    for i in sec.segments:   # weight 1: the same bf16 values come back exactly (error 1e-10 << half a bf16 ulp)
+        assert eng.community_views[i].dtype == eng.slot_views[0][i].dtype
+        assert torch.equal(eng.community_views[i], eng.slot_views[0][i])
