@@ -255,7 +255,10 @@ def test_participation_ratio_through_the_driver(tmp_path):
     md = stats["federation_runtime_metadata"]["metadata"]
     closed = [m for m in md[1:] if m.get("model_aggregation_block_size")]
     assert len(closed) >= 3
-    assert all(len(m["assigned_to_learner_id"]) == 1 and m["model_aggregation_block_size"] == [1.0] for m in closed)
+    # (a learner that joins while a round is open gets the initial task and widens that round: only the rounds after
+    # both have joined are required to be cohorts of one)
+    ones = [m for m in closed if len(m["assigned_to_learner_id"]) == 1 and m["model_aggregation_block_size"] == [1.0]]
+    assert len(ones) >= 3 and all(m in ones for m in closed[-2:])
     assert stats["community_model_results"]["community_evaluation"]
 
 
