@@ -490,7 +490,9 @@ class ControllerServicer(controller_pb2_grpc.ControllerServiceServicer):
                 model = request.task.model.SerializeToString()
         except Exception as e:   # ValueError from the splitter, DecodeError from protobuf
             context.abort(grpc.StatusCode.INVALID_ARGUMENT, "malformed MarkTaskCompletedRequest: {}".format(e))
-        self.controller_rx_model_bytes += _tensor_payload_bytes(model)
+        n_payload = _tensor_payload_bytes(model)
+        with self._fabric_lock:   # several RPC threads report at once
+            self.controller_rx_model_bytes += n_payload
         try:
             self.core.learner_completed_task(
                 learner_id, auth_token, model, md.global_iteration, md.completed_epochs, md.completed_batches,
