@@ -270,9 +270,10 @@ class FabricFederation:
     COMMUNITY = 0xFFFFFFFF
 
     def __init__(self, rule="FedAvg", protocol=1, n=2, examples=None, stride=0, fail_first=False, he_context="",
-                 bytes_from=()):
+                 bytes_from=(), participation=1.0):
         p = _core.ControllerParams()
         p.rule, p.protocol, p.stride_length = rule, protocol, stride
+        p.participation_ratio, p.sampling_seed = participation, 11
         if he_context:
             p.he_crypto_context_file = he_context
         self.ciphertext = rule == "PWA"
@@ -525,3 +526,23 @@ def test_participation_ratio_is_validated():
     p.rule, p.protocol, p.batch_size, p.epochs, p.participation_ratio = "FedAvg", 1, 10, 1, 1.5
     with pytest.raises(Exception):
         _core.Controller(p, lambda *a: None, lambda *a: None)
+
+
+def test_sampled_cohorts_are_commanded_on_the_fabric():
+    """Client sampling + device fabric: the aggregation command names the cohort's slots only, with scaling factors
+    normalised over the cohort (every rank still launches - the fused kernel is collective - but reads two sources)."""
+    f = FabricFederation(n=4, examples=[100, 100, 300, 300], participation=0.5)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    ids = [f.join(i) for i in range(4)]
+    with f.lock:
+        joined_at = len(f.commands)      # rounds already run while the others were still joining
+    f.wait_commands(joined_at + 7)
+    f.core.wait_idle()
+    with f.lock:
+        later = f.commands[joined_at + 2:]   # (a learner that joined while a round was open widened that round)
+    assert later and all(len(c["sources"]) == 2 for c in later), [len(c["sources"]) for c in f.commands]
+    for c in later:
+        assert abs(sum(s["weight"] for s in c["sources"]) - 1.0) < 1e-9
+        assert {s["learner_id"] for s in c["sources"]} <= set(ids)
+    assert f.core.aggregation_failures() == 0
+    f.core.shutdown()
