@@ -391,10 +391,13 @@ class DriverSessionBase(object):
         proto = self.federation_environment.communication_protocol
         metric = self.federation_environment.evaluation_metric
         start = time.time()
+        evals_checked_up_to = 0
         while True:
             time.sleep(request_every_secs)
             self._children_alive()
-            metadata = self._driver_controller_grpc_client.get_runtime_metadata(num_backtracks=0).metadata
+            # the newest entries only: the reference asks for the whole lineage on every poll (driver_session.py:
+            # 423-480), which grows with the number of rounds and is served under the controller's lock
+            metadata = self._driver_controller_grpc_client.get_runtime_metadata(num_backtracks=1).metadata
             if (proto.is_synchronous or proto.is_semi_synchronous) and sig.federation_rounds and len(metadata) > 0:
                 if max(m.global_iteration for m in metadata) > sig.federation_rounds:
                     MetisLogger.info("Exceeded federation rounds cutoff point. Exiting ...")
@@ -404,7 +407,11 @@ class DriverSessionBase(object):
                 if max(m.global_iteration for m in metadata) > sig.federation_rounds * max(1, self.num_participating_learners):
                     MetisLogger.info("Exceeded community update cutoff point. Exiting ...")
                     return
-            results = self._driver_controller_grpc_client.get_community_model_evaluation_lineage(-1)
+            current = max((m.global_iteration for m in metadata), default=0)
+            # evaluations filed since the last poll, plus the two newest ones again (their answers may still be arriving)
+            window = max(4, current - evals_checked_up_to + 2)
+            results = self._driver_controller_grpc_client.get_community_model_evaluation_lineage(window)
+            evals_checked_up_to = max(0, current - 2)
             for res in results.community_evaluation:
                 scores = [float(ev.test_evaluation.metric_values[metric]) for ev in res.evaluations.values()
                           if metric in ev.test_evaluation.metric_values]
