@@ -305,3 +305,19 @@ def test_holdout_split_unit():
     l2._datasets, l2._holdout_done = (full, full, empty), False
     l2._apply_validation_holdout(0.25)
     assert l2._datasets[0] is full
+
+
+def test_metric_cutoff_ends_the_federation(tmp_path):
+    """`TerminationSignals.MetricCutoffScore`: the driver stops as soon as the learners' mean test metric reaches it
+    (`driver_session.py:423-480`); here the bar is 0, so the first filed evaluation ends the run."""
+    d = _env(**{"TerminationSignals.FederationRounds": 500, "TerminationSignals.MetricCutoffScore": 0.0,
+                "TerminationSignals.ExecutionCutoffTimeMins": 3})
+    s = DriverSession(FederationEnvironment(d), FashionMnistMLP(), _recipe(96, 1), None, _recipe(32, 3),
+                      working_dir=str(tmp_path / "w"), launcher="inprocess", banner=False)
+    import time
+    t0 = time.time()
+    stats = s.run(request_every_secs=0.3)
+    assert time.time() - t0 < 60
+    md = stats["federation_runtime_metadata"]["metadata"]
+    assert 1 <= max(m["global_iteration"] for m in md) < 500
+    assert [e for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
