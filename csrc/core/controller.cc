@@ -446,6 +446,16 @@ ModelBytes Controller::ComputeCommunityModel(const std::vector<std::string>& sel
     stats.push_back(s);
   }
   auto weights = ComputeScalingFactors(params_.scaling, learners_.size(), stats);
+  if (params_.rule == "FedAvg" || params_.rule == "PWA") {
+    // A lone participant of a larger federation gets its RAW count from the scalers (train_dataset_size_scaler.cc:
+    // 7-49 - meant for the rolling rules, which divide by the running sum z).  The stateless rules multiply by the
+    // factor as it is, so a round that closes with one contributor (a sampled cohort of one, a first round that a
+    // late joiner missed) would publish count x model.  Their factors are normalised to sum 1 over the contributors.
+    double total = 0;
+    for (auto& kv : weights) total += kv.second;
+    if (total > 0 && std::fabs(total - 1.0) > 1e-12)
+      for (auto& kv : weights) kv.second /= total;
+  }
   size_t stride = parts.size();
   if (params_.rule == "FedStride" && params_.stride_length > 0) stride = params_.stride_length;
   if (stride == 0) stride = 1;

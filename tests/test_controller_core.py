@@ -546,3 +546,28 @@ def test_sampled_cohorts_are_commanded_on_the_fabric():
         assert {s["learner_id"] for s in c["sources"]} <= set(ids)
     assert f.core.aggregation_failures() == 0
     f.core.shutdown()
+
+
+def test_a_round_with_one_contributor_publishes_that_model_not_a_multiple_of_it():
+    """Stateless FedAvg + a lone contributor in a federation of two (a sampled cohort of one): the scalers hand out the
+    RAW example count for a single participant (meant for the rolling rules, `train_dataset_size_scaler.cc:7-49`); the
+    community model must still be that learner's model, i.e. grow by its delta per round."""
+    f = Federation(n=2, auto=False, participation=0.5, sampling_seed=5, examples=[100, 300])
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(2)]
+    f.delta[ids[0]], f.delta[ids[1]] = 1.0, 2.0
+    f.core.wait_idle()
+    f.release()
+    f.wait_rounds(7)
+    f.mute.update(ids)
+    time.sleep(0.1)
+    f.core.wait_idle()
+    md = {m["global_iteration"]: m for m in f.core.get_runtime_metadata_lineage(0)}
+    lineage = [_core.parse_federated_model(b) for b in f.core.get_community_model_lineage(0)]
+    vals = [(it, float(model_arrays(m)[0][0])) for _, it, m in lineage]
+    assert all(np.isfinite(v) and v < 100 for _, v in vals), vals
+    delta_of = {ids[0]: 1.0, ids[1]: 2.0}
+    for (_, a), (it, b) in zip(vals, vals[1:]):
+        who = md[it]["completed_by_learner_id"]
+        assert len(who) == 1 and abs((b - a) - delta_of[who[0]]) < 1e-5, (it, a, b, who)
+    f.core.shutdown()

@@ -259,7 +259,10 @@ def test_participation_ratio_through_the_driver(tmp_path):
     # both have joined are required to be cohorts of one)
     ones = [m for m in closed if len(m["assigned_to_learner_id"]) == 1 and m["model_aggregation_block_size"] == [1.0]]
     assert len(ones) >= 3 and all(m in ones for m in closed[-2:])
-    assert stats["community_model_results"]["community_evaluation"]
+    # a cohort of one publishes that learner's model (not example-count x model): the community model stays sane
+    ev = [e for e in stats["community_model_results"]["community_evaluation"] if e.get("evaluations")]
+    losses = [float(list(e["evaluations"].values())[0]["test_evaluation"]["metric_values"]["loss"]) for e in ev]
+    assert losses and all(np.isfinite(l) and l < 10 for l in losses), losses
 
 
 def test_validation_percentage_holds_out_a_stratified_split(tmp_path):
