@@ -333,6 +333,9 @@ class FederationEngine:
         w = list(weights) if weights is not None else scaling_factors(
             cfg.scaling, [self.examples[i] for i in ids],
             [max(1, self.completed_batches[i]) for i in ids], self.num_learners)
+        if weights is None and len(ids) == 1:
+            w = [1.0]   # a lone participant's factor from the scalers is its RAW count (for the rolling rules, which
+            #             divide by z); the synchronous rules multiply by it as it is
         stride = cfg.stride_length if (cfg.rule == "FedStride" and cfg.stride_length > 0) else len(ids)
         stride = min(stride, 64)
         install = self.arena.master[0] if (self.direct_install and self.arena.master[0] is not self.arena.seg[0]) else None

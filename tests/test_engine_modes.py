@@ -65,3 +65,20 @@ def test_fedstride_blocks_equal_fedavg_in_engine():
     b.run_round(data)
     for k, v in a.community_state_dict().items():
         torch.testing.assert_close(v, b.community_state_dict()[k], atol=1e-6, rtol=1e-6)
+
+
+def test_lone_participant_publishes_its_model():
+    """`aggregate_sync(participants=[j])` in an engine of several learners: the community model is learner j's model,
+    not example-count x model (the scalers return the raw count for a single participant)."""
+    import torch
+    cfg = EngineConfig(learners_per_gpu=3, model_dtype=torch.float32, use_cuda_graph=False)
+    e = FederationEngine(FashionMnistMLP, cfg, device="cpu", examples_per_learner=[100, 200, 300])
+    g = torch.Generator().manual_seed(0)
+    for j in range(3):
+        for v in e.slot_views[j]:
+            if v.is_floating_point():
+                v.copy_(torch.randn(v.shape, generator=g))
+    e.aggregate_sync(participants=[1])
+    for got, want in zip(e.community_views, e.slot_views[e.publish_slot(1)]):
+        if got.is_floating_point():
+            torch.testing.assert_close(got, want, atol=1e-6, rtol=0)
