@@ -446,11 +446,13 @@ ModelBytes Controller::ComputeCommunityModel(const std::vector<std::string>& sel
     stats.push_back(s);
   }
   auto weights = ComputeScalingFactors(params_.scaling, learners_.size(), stats);
-  if (params_.rule == "FedAvg" || params_.rule == "PWA") {
+  if (!single) {
     // A lone participant of a larger federation gets its RAW count from the scalers (train_dataset_size_scaler.cc:
-    // 7-49 - meant for the rolling rules, which divide by the running sum z).  The stateless rules multiply by the
-    // factor as it is, so a round that closes with one contributor (a sampled cohort of one, a first round that a
-    // late joiner missed) would publish count x model.  Their factors are normalised to sum 1 over the contributors.
+    // 7-49 - meant for the per-contribution rolling rules, which divide by the running sum z).  FedAvg / PWA - and
+    // FedStride on the device path, where the blocks are plain weighted sums - multiply by the factor as it is, so a
+    // round that closes with one contributor (a sampled cohort of one, a first round that a late joiner missed) would
+    // publish count x model.  The factors of a round are normalised to sum 1 over its contributors (for the host
+    // FedStride, which divides by z = sum of factors, this changes nothing).
     double total = 0;
     for (auto& kv : weights) total += kv.second;
     if (total > 0 && std::fabs(total - 1.0) > 1e-12)

@@ -571,3 +571,21 @@ def test_a_round_with_one_contributor_publishes_that_model_not_a_multiple_of_it(
         who = md[it]["completed_by_learner_id"]
         assert len(who) == 1 and abs((b - a) - delta_of[who[0]]) < 1e-5, (it, a, b, who)
     f.core.shutdown()
+
+
+@pytest.mark.parametrize("rule", ["FedAvg", "FedStride"])
+def test_device_command_for_a_lone_contributor_carries_weight_one(rule):
+    """On the device path the blocks are plain weighted sums (no division by z), so the lone contributor of a round
+    must be commanded with factor 1, not with its raw example count."""
+    f = FabricFederation(rule=rule, n=2, examples=[100, 300], participation=0.5)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(8, np.float32)])))
+    [f.join(i) for i in range(2)]
+    with f.lock:
+        joined_at = len(f.commands)
+    f.wait_commands(joined_at + 6)
+    f.core.wait_idle()
+    with f.lock:
+        later = f.commands[joined_at + 2:]
+    assert later and all(len(c["sources"]) == 1 for c in later)
+    assert all(abs(c["sources"][0]["weight"] - 1.0) < 1e-12 for c in later), [c["sources"][0]["weight"] for c in later]
+    f.core.shutdown()
