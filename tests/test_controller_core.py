@@ -47,6 +47,9 @@ class Federation:
             threading.Thread(target=self._complete, args=(lid, model, iteration, updates), daemon=True).start()
 
     def _complete(self, lid, model, iteration, updates):
+        t0 = time.time()
+        while lid not in self.tokens and time.time() - t0 < 5:   # the first task can arrive before join() has returned
+            time.sleep(0.002)
         x = model_arrays(model)[0]
         new = model_bytes([x + self.delta.get(lid, 0.0)])
         self.core.learner_completed_task(lid, self.tokens[lid], new, iteration, 1.0, updates, 10,
@@ -588,4 +591,30 @@ def test_device_command_for_a_lone_contributor_carries_weight_one(rule):
         later = f.commands[joined_at + 2:]
     assert later and all(len(c["sources"]) == 1 for c in later)
     assert all(abs(c["sources"][0]["weight"] - 1.0) < 1e-12 for c in later), [c["sources"][0]["weight"] for c in later]
+    f.core.shutdown()
+
+
+def test_first_round_that_a_late_joiner_missed_publishes_the_early_learners_model():
+    """No sampling: learner 0 finishes round 1 before learner 1 joins.  The barrier closes with one contributor in a
+    federation that by then may count two learners; the community model is that contributor's model (+1), and from
+    the round both take part in it moves by the weighted mean (0.25 * 1 + 0.75 * 3 = 2.5)."""
+    f = Federation(n=2, examples=[100, 300])
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    f.delta["127.0.0.1:9000"], f.delta["127.0.0.1:9001"] = 1.0, 3.0   # known before the first task can complete
+    a = f.join(0)
+    f.wait_rounds(2)
+    b = f.join(1)
+    assert (a, b) == ("127.0.0.1:9000", "127.0.0.1:9001")
+    f.wait_rounds(8)
+    f.mute.update([a, b])
+    time.sleep(0.1)
+    f.core.wait_idle()
+    md = {m["global_iteration"]: m for m in f.core.get_runtime_metadata_lineage(0)}
+    lineage = [_core.parse_federated_model(x) for x in f.core.get_community_model_lineage(0)]
+    vals = [(it, float(model_arrays(m)[0][0])) for _, it, m in lineage]
+    assert all(np.isfinite(v) and v < 100 for _, v in vals), vals
+    for (_, x0), (it, x1) in zip(vals, vals[1:]):
+        who = sorted(md[it]["completed_by_learner_id"])
+        want = 1.0 if who == [a] else 3.0 if who == [b] else 2.5
+        assert abs((x1 - x0) - want) < 1e-4, (it, x0, x1, who)
     f.core.shutdown()
