@@ -618,3 +618,24 @@ def test_first_round_that_a_late_joiner_missed_publishes_the_early_learners_mode
         want = 1.0 if who == [a] else 3.0 if who == [b] else 2.5
         assert abs((x1 - x0) - want) < 1e-4, (it, x0, x1, who)
     f.core.shutdown()
+
+
+def test_semi_synchronous_with_sampling_resizes_every_learners_task():
+    """Semi-synchronous + client sampling: the task sizes are recomputed from ALL active learners' timings (a learner
+    outside this round's cohort keeps a template that matches the slowest learner), and rounds keep closing."""
+    f = Federation(protocol=3, n=4, semi_lambda=2, auto=False, participation=0.5, sampling_seed=9)
+    f.core.replace_community_model(_core.build_federated_model(0, 0, model_bytes([np.zeros(4, np.float32)])))
+    ids = [f.join(i) for i in range(4)]
+    f.ms_per_batch = {ids[0]: 1.0, ids[1]: 4.0, ids[2]: 2.0, ids[3]: 1.0}   # slowest epoch 40 ms -> t_max = 80 ms
+    f.core.wait_idle()
+    f.release()
+    f.wait_rounds(5)
+    f.mute.update(ids)
+    time.sleep(0.1)
+    f.core.wait_idle()
+    want = {ids[0]: 80, ids[1]: 20, ids[2]: 40, ids[3]: 80}
+    later = [r for r in f.run_log if r[1] >= 2]
+    assert len(later) >= 4 and all(len(r[0]) == 2 for r in later)
+    for lids, _, updates in later:
+        assert dict(zip(lids, updates)) == {l: want[l] for l in lids}
+    f.core.shutdown()
