@@ -163,3 +163,41 @@ def test_split_bounds_the_number_of_records():
     with pytest.raises(ValueError):
         envelope.split(b"\x08\x01" * (envelope.MAX_TOP_LEVEL_RECORDS + 1))
     assert len(envelope.split(b"\x08\x01" * 100)[1]) == 100
+
+
+def test_mark_task_completed_also_takes_a_parsed_message():
+    """In-process callers hand the servicer a message object instead of bytes: same outcome."""
+    import grpc
+
+    from metisfl_b200.controller.service import ControllerServicer
+
+    class Ctx:
+        code = None
+
+        def abort(self, code, details):
+            self.code = code
+            raise RuntimeError(details)
+
+    p = metis_pb2.ControllerParams()
+    p.server_entity.hostname, p.server_entity.port = "127.0.0.1", 1
+    p.global_model_specs.aggregation_rule.fed_avg.SetInParent()
+    p.communication_specs.protocol = metis_pb2.CommunicationSpecs.SYNCHRONOUS
+    p.model_store_config.in_memory_store.SetInParent()
+    p.model_hyperparams.batch_size, p.model_hyperparams.epochs = 32, 1
+    ctrl = ControllerServicer(p)
+    try:
+        names, trainables, values = _weights()
+        model = ModelProtoMessages.construct_model_pb_from_np(values, names, trainables)
+        req = controller_pb2.MarkTaskCompletedRequest(
+            learner_id="nobody:1", auth_token="bad", task=metis_pb2.CompletedLearningTask(model=model))
+        for form in (req, req.SerializeToString()):
+            ctx = Ctx()
+            with pytest.raises(RuntimeError):
+                ctrl.MarkTaskCompleted(form, ctx)
+            assert ctx.code == grpc.StatusCode.UNAUTHENTICATED
+        ctx = Ctx()
+        with pytest.raises(RuntimeError):
+            ctrl.MarkTaskCompleted(b"\x07", ctx)
+        assert ctx.code == grpc.StatusCode.INVALID_ARGUMENT
+    finally:
+        ctrl.stop()
